@@ -1,0 +1,254 @@
+"""Model builders for the reference's validation cases and the synthetic ensembles of BASELINE.json.
+
+`single_zone_test_building` restates what `simple_test_models::get_single_zone_test_building` (un-vendored
+dev-dependency) produces, as far as the thermal path reads it: one space, one south-facing vertical wall whose
+front is Outdoor and whose back is the space, optionally a window (a fenestration of the same construction) —
+geometry (inferred) from tests/validate_wall_heat_transfer.rs:95-191,713-738 and the IDFs under tests/*/in.idf.
+"""
+from __future__ import annotations
+
+import math
+from typing import Sequence
+
+import numpy as np
+
+from . import desc as D
+
+# TestMat::{Concrete, Polyurethane} — tests/massive_full/in.idf:47-56, tests/mixed_full/in.idf:59-68,
+# src/surface.rs:1048-1075
+CONCRETE = dict(conductivity=0.816, density=1700.0, specific_heat=800.0)
+POLYURETHANE = dict(conductivity=0.0252, density=17.5, specific_heat=2400.0)
+# TestMat::Glass is not recoverable from the reference tree; soda-lime glass values, builder-defined.
+GLASS = dict(conductivity=1.0, density=2500.0, specific_heat=840.0)
+
+
+def concrete(thickness, emissivity=D.NAN, solar_abs=D.NAN):
+    return D.solid_layer(thickness, **CONCRETE, front_emissivity=emissivity, back_emissivity=emissivity,
+                         front_solar_abs=solar_abs, back_solar_abs=solar_abs)
+
+
+def polyurethane(thickness, emissivity=D.NAN, solar_abs=D.NAN):
+    return D.solid_layer(thickness, **POLYURETHANE, front_emissivity=emissivity, back_emissivity=emissivity,
+                         front_solar_abs=solar_abs, back_solar_abs=solar_abs)
+
+
+def glass(thickness, tau, emissivity=D.NAN, solar_abs=D.NAN):
+    return D.solid_layer(thickness, **GLASS, front_emissivity=emissivity, back_emissivity=emissivity,
+                         front_solar_abs=solar_abs, back_solar_abs=solar_abs, solar_transmittance=tau)
+
+
+def polygon_props(vertices: Sequence[Sequence[float]]):
+    """normal (unit), area, perimeter, centroid of a planar polygon (geometry3d, un-vendored; Newell's method)."""
+    v = np.asarray(vertices, float)
+    nxt = np.roll(v, -1, axis=0)
+    nvec = np.array([
+        np.sum((v[:, 1] - nxt[:, 1]) * (v[:, 2] + nxt[:, 2])),
+        np.sum((v[:, 2] - nxt[:, 2]) * (v[:, 0] + nxt[:, 0])),
+        np.sum((v[:, 0] - nxt[:, 0]) * (v[:, 1] + nxt[:, 1])),
+    ])
+    area = 0.5 * float(np.linalg.norm(nvec))
+    normal = nvec / np.linalg.norm(nvec)
+    perimeter = float(np.sum(np.linalg.norm(nxt - v, axis=1)))
+    centroid = v.mean(axis=0)
+    return normal, area, perimeter, centroid
+
+
+def single_zone_test_building(construction, *, zone_volume=40.0, surface_height=2.0, surface_width=2.0,
+                              window_height=0.0, window_width=0.0, emissivity=0.84, solar_absorbtance=0.7,
+                              steps_per_hour=20, front_hs=D.NAN, back_hs=D.NAN, back_emissivity_override=D.NAN):
+    """One space + one exterior wall (+ optional window). `construction`: list of ('concrete'|'polyurethane', th)."""
+    makers = {"concrete": concrete, "polyurethane": polyurethane}
+    layers = [makers[name](th, emissivity, solar_absorbtance) for name, th in construction]
+    win_area = window_height * window_width
+    normal = (0.0, -1.0, 0.0)
+    surfaces = [D.surface(0, surface_height * surface_width - win_area, 2.0 * (surface_height + surface_width), normal,
+                          surface_height / 2.0, front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0),
+                          front_hs=front_hs, back_hs=back_hs, back_emissivity=back_emissivity_override)]
+    if win_area > 0.0:
+        surfaces.append(D.surface(0, win_area, 2.0 * (window_height + window_width), normal, surface_height / 2.0,
+                                  front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0), is_fenestration=True))
+    return D.single_model([layers], [zone_volume], surfaces, steps_per_hour)
+
+
+def validation_case(name: str, steps_per_hour: int = 20) -> D.BatchDesc:
+    """The EnergyPlus-driven cases of tests/validate_wall_heat_transfer.rs:792-994 (+ the commented-out Trombe wall)."""
+    kind, _, variant = name.partition("_")
+    if kind in ("massive", "mixed", "nomass"):
+        eps = 0.9 if variant in ("full", "yes_ir_no_solar") else 0.0
+        alpha = 0.7 if variant in ("full", "no_ir_yes_solar") else 0.0
+        cons = {"massive": [("concrete", 0.2)], "nomass": [("polyurethane", 0.02)],
+                "mixed": [("polyurethane", 0.02), ("concrete", 0.2), ("polyurethane", 0.02)]}[kind]
+        # march_test_model (:713-738) + `thermal_model.surfaces[0].back_emissivity = 0.0` (:630)
+        return single_zone_test_building(cons, zone_volume=600.0, surface_height=3.0, surface_width=20.0,
+                                         emissivity=eps, solar_absorbtance=alpha, steps_per_hour=steps_per_hour,
+                                         back_emissivity_override=0.0)
+    if name in ("tilted", "horizontal"):
+        verts = {"tilted": [(0, 0, 0), (20, 0, 0), (20, 2.12132034357, 2.12132034357), (0, 2.12132034357, 2.12132034357)],
+                 "horizontal": [(10, 3, 14.9), (10, 0, 14.9), (30, 0, 14.9), (30, 3, 14.9)]}[name]
+        normal, area, perimeter, centroid = polygon_props(verts)  # tests/{tilted,horizontal}/back.spl
+        layers = [concrete(0.2, 0.9, 0.7)]
+        s = D.surface(0, area, perimeter, tuple(normal), float(centroid[2]), front=(D.BOUNDARY_OUTDOOR, 0),
+                      back=(D.BOUNDARY_SPACE, 0), back_emissivity=0.0)
+        return D.single_model([layers], [600.0], [s], steps_per_hour)
+    if name == "trombe_wall_full":
+        # validate_wall_heat_transfer.rs:1091-1099 (commented out in the reference; E+ columns are a missing blob)
+        layers = [concrete(0.2, 0.9, 0.08), D.gas_layer(0.05, D.GAS_AIR), glass(0.03, 0.82, 0.9, 0.08)]
+        s = D.surface(0, 60.0, 46.0, (0.0, -1.0, 0.0), 1.5, front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0),
+                      back_emissivity=0.0)
+        return D.single_model([layers], [600.0], [s], steps_per_hour)
+    raise KeyError(name)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Synthetic ensembles (BASELINE.json configs 3-5; distributions in SURVEY.md §8(d))
+# ------------------------------------------------------------------------------------------------------------------
+class SplitMix64:
+    """splitmix64 stream → uniform doubles; vectorised."""
+
+    def __init__(self, seed: int):
+        self.state = np.uint64(seed)
+
+    def next_u64(self, n: int) -> np.ndarray:
+        with np.errstate(over="ignore"):
+            idx = np.arange(1, n + 1, dtype=np.uint64)
+            z = self.state + idx * np.uint64(0x9E3779B97F4A7C15)
+            self.state = self.state + np.uint64(n) * np.uint64(0x9E3779B97F4A7C15)
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            return z ^ (z >> np.uint64(31))
+
+    def uniform(self, n: int, lo=0.0, hi=1.0) -> np.ndarray:
+        u = (self.next_u64(n) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+        return lo + (hi - lo) * u
+
+
+def _random_layers(rng: SplitMix64, n: int):
+    k = np.exp(rng.uniform(n, math.log(0.05), math.log(2.5)))
+    rho = rng.uniform(n, 300.0, 2500.0)
+    cp = rng.uniform(n, 700.0, 2000.0)
+    th = rng.uniform(n, 0.03, 0.30)
+    return k, rho, cp, th
+
+
+def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, steps_per_hour: int = 1,
+                  max_layers: int = 4) -> D.BatchDesc:
+    """`n_walls` independent models, each one exterior wall + its own zone (massive_full topology).
+
+    Massive walls: 1..max_layers random solid layers. Mixed walls (fraction `mixed_fraction`): polyurethane /
+    random solid / polyurethane, whose outer layers the reference's rule classifies as no-mass.
+    """
+    rng = SplitMix64(seed)
+    n_lay = 1 + (rng.next_u64(n_walls) % np.uint64(max_layers)).astype(np.int64)
+    is_mixed = rng.uniform(n_walls) < mixed_fraction
+    n_lay = np.where(is_mixed, 3, n_lay)
+    off = np.zeros(n_walls + 1, np.int64)
+    np.cumsum(n_lay, out=off[1:])
+    total = int(off[-1])
+    k, rho, cp, th = _random_layers(rng, total)
+    eps = rng.uniform(n_walls, 0.7, 0.95)
+    alpha = rng.uniform(n_walls, 0.2, 0.9)
+    azimuth = rng.uniform(n_walls, 0.0, 2.0 * math.pi)
+    volume = rng.uniform(n_walls, 50.0, 600.0)
+
+    layers = np.zeros(total, D.LAYER_DTYPE)
+    layers["kind"] = D.LAYER_SOLID
+    layers["thickness"], layers["conductivity"], layers["density"], layers["specific_heat"] = th, k, rho, cp
+    wall_of_layer = np.repeat(np.arange(n_walls), n_lay)
+    for f, v in (("front_emissivity", eps), ("back_emissivity", eps), ("front_solar_abs", alpha), ("back_solar_abs", alpha)):
+        layers[f] = v[wall_of_layer]
+    layers["solar_transmittance"] = D.NAN
+    # mixed walls: first and third layers become 2 cm polyurethane
+    first = off[:-1][is_mixed]
+    for idx in (first, first + 2):
+        layers["thickness"][idx] = 0.02
+        layers["conductivity"][idx] = POLYURETHANE["conductivity"]
+        layers["density"][idx] = POLYURETHANE["density"]
+        layers["specific_heat"][idx] = POLYURETHANE["specific_heat"]
+
+    surfaces = np.zeros(n_walls, D.SURFACE_DTYPE)
+    surfaces["construction"] = np.arange(n_walls)
+    surfaces["front_kind"], surfaces["back_kind"] = D.BOUNDARY_OUTDOOR, D.BOUNDARY_SPACE
+    surfaces["front_zone"], surfaces["back_zone"] = -1, 0
+    surfaces["area"], surfaces["perimeter"], surfaces["centroid_z"] = 60.0, 46.0, 1.5
+    surfaces["normal"][:, 0] = np.sin(azimuth)
+    surfaces["normal"][:, 1] = np.cos(azimuth)
+    for f in ("front_hs_override", "back_hs_override", "front_emissivity_override", "back_emissivity_override"):
+        surfaces[f] = D.NAN
+    ar = np.arange(n_walls + 1, dtype=np.int32)
+    return D.BatchDesc(layers, off.astype(np.int32), ar, ar, volume, surfaces, steps_per_hour)
+
+
+def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 1):
+    """`n_buildings` single-zone shoeboxes: 4 walls + roof (Outdoor ↔ Space), floor (AmbientTemperature front) and one
+    single-layer window, parametric sweep. Returns (BatchDesc, q_internal[n_buildings])."""
+    rng = SplitMix64(seed)
+    n = n_buildings
+    # one opaque construction per building (1-3 layers) + one glazing construction shared by all
+    n_lay = 1 + (rng.next_u64(n) % np.uint64(3)).astype(np.int64)
+    off = np.zeros(n + 2, np.int64)
+    np.cumsum(n_lay, out=off[1:n + 1])
+    total = int(off[n])
+    off[n + 1] = total + 1
+    k, rho, cp, th = _random_layers(rng, total)
+    eps = rng.uniform(n, 0.7, 0.95)
+    alpha = rng.uniform(n, 0.2, 0.9)
+    volume = rng.uniform(n, 50.0, 600.0)
+    gains = rng.uniform(n, 0.0, 500.0)
+    layers = np.zeros(total + 1, D.LAYER_DTYPE)
+    layers["kind"] = D.LAYER_SOLID
+    layers["thickness"][:total], layers["conductivity"][:total] = th, k
+    layers["density"][:total], layers["specific_heat"][:total] = rho, cp
+    b_of_layer = np.repeat(np.arange(n), n_lay)
+    for f, v in (("front_emissivity", eps), ("back_emissivity", eps), ("front_solar_abs", alpha), ("back_solar_abs", alpha)):
+        layers[f][:total] = v[b_of_layer]
+    layers["solar_transmittance"] = D.NAN
+    layers[total] = glass(0.006, 0.6, 0.84, 0.2)
+
+    height = 3.0
+    side = np.sqrt(volume / height)
+    surfaces = np.zeros((n, 7), D.SURFACE_DTYPE)
+    surfaces["construction"] = np.arange(n)[:, None]
+    surfaces["construction"][:, 6] = n
+    surfaces["is_fenestration"][:, 6] = 1
+    surfaces["front_kind"], surfaces["back_kind"] = D.BOUNDARY_OUTDOOR, D.BOUNDARY_SPACE
+    surfaces["front_zone"], surfaces["back_zone"] = -1, 0
+    normals = np.array([(0, -1, 0), (1, 0, 0), (0, 1, 0), (-1, 0, 0), (0, 0, 1), (0, 0, -1), (0, -1, 0)], float)
+    surfaces["normal"] = normals[None]
+    wall_area = side * height
+    win_area = 0.3 * wall_area
+    for j in range(4):
+        surfaces["area"][:, j] = wall_area - (win_area if j == 0 else 0.0)
+        surfaces["perimeter"][:, j] = 2.0 * (side + height)
+        surfaces["centroid_z"][:, j] = height / 2.0
+    surfaces["area"][:, 4] = side * side
+    surfaces["perimeter"][:, 4] = 4.0 * side
+    surfaces["centroid_z"][:, 4] = height
+    surfaces["area"][:, 5] = side * side
+    surfaces["perimeter"][:, 5] = 4.0 * side
+    surfaces["centroid_z"][:, 5] = 0.0
+    surfaces["front_kind"][:, 5] = D.BOUNDARY_AMBIENT       # floor: ground modelled as a fixed temperature
+    surfaces["front_ambient_t"][:, 5] = 15.0
+    surfaces["area"][:, 6] = win_area
+    surfaces["perimeter"][:, 6] = 2.0 * (np.sqrt(win_area) * 2.0)
+    surfaces["centroid_z"][:, 6] = height / 2.0
+    for f in ("front_hs_override", "back_hs_override", "front_emissivity_override", "back_emissivity_override"):
+        surfaces[f] = D.NAN
+    zo = np.arange(n + 1, dtype=np.int32)
+    so = (np.arange(n + 1, dtype=np.int64) * 7).astype(np.int32)
+    return D.BatchDesc(layers, off.astype(np.int32), zo, so, volume, surfaces.reshape(-1), steps_per_hour), gains
+
+
+def synthetic_weather(n_rows: int, seed: int = 7):
+    """Smooth annual + diurnal series: returns weather[n_rows][3] and inputs[n_rows][4]
+    (front solar, back solar, front IR, back IR), hourly rows."""
+    t = np.arange(n_rows, dtype=np.float64)
+    day = 2.0 * math.pi * t / 24.0
+    year = 2.0 * math.pi * t / 8760.0
+    t_out = 15.0 - 10.0 * np.cos(year) - 5.0 * np.cos(day - 0.6)
+    wind_speed = 3.0 + 3.0 * np.sin(year * 3.0 + 1.0) * np.cos(day * 0.5)
+    wind_dir = np.mod(t * 7.3 + 40.0 * np.sin(day), 360.0)
+    solar = np.maximum(0.0, 800.0 * np.sin(day - math.pi / 2.0)) * (0.6 + 0.4 * np.cos(year - math.pi))
+    ir = 5.670374419e-8 * (t_out + 263.15) ** 4
+    weather = np.stack([t_out, wind_dir, np.abs(wind_speed)], axis=1)
+    inputs = np.stack([solar, np.zeros_like(solar), ir, ir], axis=1)
+    return np.ascontiguousarray(weather), np.ascontiguousarray(inputs)

@@ -1,0 +1,722 @@
+// hb_capi.cu — the C ABI declared in include/heat_b200.h: handle, device buffers, launches.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "hb_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+#define HB_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            throw CudaError(std::string(#expr) + ": " + cudaGetErrorString(_e));                   \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        free();
+        n = count;
+        if (count) HB_CUDA(cudaMalloc(&p, count * sizeof(T)));
+    }
+    void upload(const std::vector<T>& h, cudaStream_t st) {
+        alloc(h.size());
+        if (!h.empty()) HB_CUDA(cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+    }
+    void free() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    ~DevBuf() { free(); }
+};
+
+}  // namespace
+
+struct hb_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    hb::BatchPlan plan;
+    int64_t launches = 0;
+
+    // device buffers
+    DevBuf<int32_t> n_nodes, flags, zone_f, zone_b, S, site, desc_index, nm_off, nm_pairs, cav_off;
+    DevBuf<hb::CavityDev> cav;
+    DevBuf<double> dt, area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b;
+    DevBuf<double> nodeT, mass, u, alpha_f, alpha_b, sc, energy_f, energy_b;
+    DevBuf<unsigned long long> nm_iters;
+    DevBuf<int32_t> status;
+    DevBuf<double> zoneT, zvol, zq, zinf_v, zinf_t, zvent_v, zvent_t, zdt;
+    DevBuf<int32_t> zS, z_surf_begin, z_surf_end;
+    DevBuf<hb::Tile> tiles;
+    DevBuf<double> red_out;
+    DevBuf<unsigned long long> red_iout;
+    DevBuf<double> flush;
+
+    struct Group {
+        int nmax_tier;
+        bool dist;
+        int n_tiles;
+        DevBuf<int32_t> ids;
+    };
+    std::vector<std::unique_ptr<Group>> groups;
+    std::vector<int32_t> host_site;  // per device surface slot (rebuilt when model_site changes)
+    std::vector<int32_t> model_site_cache;
+
+    hb::DevView view() {
+        hb::DevView V{};
+        V.n_nodes = n_nodes.p; V.flags = flags.p; V.zone_f = zone_f.p; V.zone_b = zone_b.p; V.S = S.p;
+        V.site = site.p; V.desc_index = desc_index.p; V.dt = dt.p; V.area = area.p; V.nx = nx.p; V.ny = ny.p;
+        V.cos_tilt = cos_tilt.p; V.forced_c = forced_c.p; V.eps_f = eps_f.p; V.eps_b = eps_b.p;
+        V.amb_f = amb_f.p; V.amb_b = amb_b.p; V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p;
+        V.nm_off = nm_off.p; V.nm_pairs = nm_pairs.p; V.cav_off = cav_off.p; V.cav = cav.p;
+        V.nodeT = nodeT.p; V.mass = mass.p; V.u = u.p; V.alpha_f = alpha_f.p; V.alpha_b = alpha_b.p;
+        V.sc = sc.p; V.n_dev_surfaces = plan.n_dev_surfaces; V.energy_f = energy_f.p; V.energy_b = energy_b.p;
+        V.nm_iters = nm_iters.p; V.status = status.p;
+        V.zoneT = zoneT.p; V.zvol = zvol.p; V.zq = zq.p; V.zinf_v = zinf_v.p; V.zinf_t = zinf_t.p;
+        V.zvent_v = zvent_v.p; V.zvent_t = zvent_t.p; V.zdt = zdt.p; V.zS = zS.p;
+        V.z_surf_begin = z_surf_begin.p; V.z_surf_end = z_surf_end.p; V.n_dev_zones = plan.n_dev_zones;
+        V.tiles = tiles.p;
+        return V;
+    }
+};
+
+namespace {
+
+using hb::kBlock;
+
+int tier_of(int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 48 ? 48 : 64; }
+
+template <class F>
+hb_status guarded(F&& f) {
+    try {
+        f();
+        return HB_OK;
+    } catch (const CudaError& e) {
+        g_err = e.what();
+        return HB_ERR_CUDA;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        const bool unsupported = g_err.find("not implemented") != std::string::npos;
+        return unsupported ? HB_ERR_UNSUPPORTED : HB_ERR_INVALID;
+    }
+}
+
+void build_device(hb_handle* h) {
+    const hb::BatchPlan& B = h->plan;
+    const int64_t NS = B.n_dev_surfaces, NZ = B.n_dev_zones;
+    std::vector<int32_t> n_nodes(NS, 0), flags(NS, 0), zone_f(NS, -1), zone_b(NS, -1), S(NS, 0), site(NS, 0),
+        desc_index(NS, 0), nm_off(NS + 1, 0), cav_off(NS + 1, 0), nm_pairs;
+    std::vector<hb::CavityDev> cav;
+    std::vector<double> dt(NS, 0.), area(NS, 0.), nx(NS, 0.), ny(NS, 0.), cos_tilt(NS, 0.), forced_c(NS, 0.),
+        eps_f(NS, 0.), eps_b(NS, 0.), amb_f(NS, 0.), amb_b(NS, 0.), ov_f(NS, NAN), ov_b(NS, NAN);
+    std::vector<double> nodeT(B.node_slab_len, 0.), mass(B.node_slab_len, 0.), u(B.node_slab_len, 0.),
+        alpha_f(B.node_slab_len, 0.), alpha_b(B.node_slab_len, 0.), sc(8 * NS, 0.);
+    std::vector<double> zoneT(NZ, 0.), zvol(NZ, 0.), zq(NZ, 0.), zinf_v(NZ, 0.), zinf_t(NZ, NAN), zvent_v(NZ, 0.),
+        zvent_t(NZ, NAN), zdt(NZ, 0.);
+    std::vector<int32_t> zS(NZ, 0), zsb(NZ, 0), zse(NZ, 0);
+
+    // inverse map device slot → descriptor surface
+    std::vector<int64_t> desc_of(NS, -1);
+    for (size_t gdesc = 0; gdesc < B.dev_surface_of.size(); ++gdesc) desc_of[B.dev_surface_of[gdesc]] = (int64_t)gdesc;
+
+    std::vector<int> tile_dist(B.tiles.size(), 0);
+    for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
+        const hb::Tile& tile = B.tiles[ti];
+        for (int t = 0; t < tile.n_surfaces; ++t) {
+            const int64_t g = (int64_t)tile.surface_begin + t;
+            const int64_t gd = desc_of[g];
+            const hb_surface& s = B.surfaces[gd];
+            const hb::SurfacePlan& P = B.plans[gd];
+            const hb::ModelPlan& M = B.models[B.surface_model[gd]];
+            n_nodes[g] = P.n_nodes;
+            flags[g] = (s.front_kind & 15) | ((s.back_kind & 15) << 4) | ((P.distributed_solar ? 1 : 0) << 8) |
+                       ((P.cavities.empty() ? 0 : 1) << 9);
+            if (P.distributed_solar) tile_dist[ti] = 1;
+            const int zone_local0 = B.dev_zone_of[M.zone_begin] - tile.zone_begin;  // model's first zone, tile-local
+            zone_f[g] = s.front_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.front_zone : -1;
+            zone_b[g] = s.back_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.back_zone : -1;
+            S[g] = M.dt_subdivisions;
+            desc_index[g] = (int32_t)gd;
+            dt[g] = M.dt;
+            area[g] = s.area;
+            nx[g] = s.normal[0];
+            ny[g] = s.normal[1];
+            cos_tilt[g] = P.cos_tilt;
+            forced_c[g] = 2.537 * 1.67 * std::sqrt(s.perimeter * P.wind_speed_modifier / s.area);
+            eps_f[g] = P.front_emissivity;
+            eps_b[g] = P.back_emissivity;
+            amb_f[g] = s.front_ambient_t;
+            amb_b[g] = s.back_ambient_t;
+            ov_f[g] = s.front_hs_override;
+            ov_b[g] = s.back_hs_override;
+            for (int i = 0; i < P.n_nodes; ++i) {
+                const int64_t o = tile.node_offset + (int64_t)i * kBlock + t;
+                nodeT[o] = hb::kInitialT;
+                mass[o] = P.mass[i];
+                u[o] = P.u[i];
+                alpha_f[o] = P.front_alpha[i];
+                alpha_b[o] = P.back_alpha[i];
+            }
+            sc[0 * NS + g] = hb::kInitialH;
+            sc[1 * NS + g] = hb::kInitialH;
+        }
+        for (int z = 0; z < tile.n_zones; ++z) zoneT[(int64_t)tile.zone_begin + z] = hb::kInitialT;
+    }
+    // CSR lists in device-slot order
+    for (int64_t g = 0; g < NS; ++g) {
+        nm_off[g] = (int32_t)(nm_pairs.size() / 2);
+        cav_off[g] = (int32_t)cav.size();
+        const int64_t gd = desc_of[g];
+        if (gd < 0) continue;
+        const hb::SurfacePlan& P = B.plans[gd];
+        nm_pairs.insert(nm_pairs.end(), P.nomass_chunks.begin(), P.nomass_chunks.end());
+        for (const auto& c : P.cavities) cav.push_back(hb::CavityDev{c.node, c.gas, c.thickness, c.height, c.angle, c.eout, c.ein});
+    }
+    nm_off[NS] = (int32_t)(nm_pairs.size() / 2);
+    cav_off[NS] = (int32_t)cav.size();
+    if (nm_pairs.empty()) nm_pairs.push_back(0);
+    if (cav.empty()) cav.push_back(hb::CavityDev{0, 0, 1., 1., 0., 1., 1.});
+    // zones
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const hb::ModelPlan& M = B.models[m];
+        if (M.n_zones == 0) continue;
+        const int64_t gz0 = B.dev_zone_of[M.zone_begin];
+        const int64_t tile_idx = gz0 / kBlock;
+        const hb::Tile& tile = B.tiles[tile_idx];
+        const int sb = M.n_surfaces ? B.dev_surface_of[M.surface_begin] - tile.surface_begin : 0;
+        for (int z = 0; z < M.n_zones; ++z) {
+            const int64_t gz = gz0 + z;
+            zvol[gz] = B.zone_volume[M.zone_begin + z];
+            zdt[gz] = M.dt;
+            zS[gz] = M.dt_subdivisions;
+            zsb[gz] = sb;
+            zse[gz] = sb + M.n_surfaces;
+        }
+    }
+
+    cudaStream_t st = h->stream;
+    h->n_nodes.upload(n_nodes, st); h->flags.upload(flags, st); h->zone_f.upload(zone_f, st);
+    h->zone_b.upload(zone_b, st); h->S.upload(S, st); h->site.upload(site, st);
+    h->desc_index.upload(desc_index, st); h->nm_off.upload(nm_off, st); h->nm_pairs.upload(nm_pairs, st);
+    h->cav_off.upload(cav_off, st); h->cav.upload(cav, st);
+    h->dt.upload(dt, st); h->area.upload(area, st); h->nx.upload(nx, st); h->ny.upload(ny, st);
+    h->cos_tilt.upload(cos_tilt, st); h->forced_c.upload(forced_c, st); h->eps_f.upload(eps_f, st);
+    h->eps_b.upload(eps_b, st); h->amb_f.upload(amb_f, st); h->amb_b.upload(amb_b, st);
+    h->hs_ov_f.upload(ov_f, st); h->hs_ov_b.upload(ov_b, st);
+    h->nodeT.upload(nodeT, st); h->mass.upload(mass, st); h->u.upload(u, st);
+    h->alpha_f.upload(alpha_f, st); h->alpha_b.upload(alpha_b, st); h->sc.upload(sc, st);
+    h->energy_f.upload(std::vector<double>(NS, 0.), st); h->energy_b.upload(std::vector<double>(NS, 0.), st);
+    h->nm_iters.upload(std::vector<unsigned long long>(NS, 0ull), st);
+    h->status.upload(std::vector<int32_t>(NS, 0), st);
+    h->zoneT.upload(zoneT, st); h->zvol.upload(zvol, st); h->zq.upload(zq, st); h->zinf_v.upload(zinf_v, st);
+    h->zinf_t.upload(zinf_t, st); h->zvent_v.upload(zvent_v, st); h->zvent_t.upload(zvent_t, st);
+    h->zdt.upload(zdt, st); h->zS.upload(zS, st); h->z_surf_begin.upload(zsb, st); h->z_surf_end.upload(zse, st);
+    h->tiles.upload(B.tiles, st);
+    h->red_out.alloc(8);
+    h->red_iout.alloc(4);
+    h->host_site.assign(NS, 0);
+
+    // launch groups: (register tier, distributed-solar variant)
+    std::map<std::pair<int, int>, std::vector<int32_t>> by;
+    for (size_t ti = 0; ti < B.tiles.size(); ++ti) by[{tier_of(B.tiles[ti].nmax), tile_dist[ti]}].push_back((int32_t)ti);
+    for (auto& kv : by) {
+        auto grp = std::make_unique<hb_handle::Group>();
+        grp->nmax_tier = kv.first.first;
+        grp->dist = kv.first.second != 0;
+        grp->n_tiles = (int)kv.second.size();
+        grp->ids.upload(kv.second, st);
+        h->groups.push_back(std::move(grp));
+    }
+    HB_CUDA(cudaStreamSynchronize(st));
+}
+
+template <int NMAX>
+void launch_tier(hb_handle* h, const hb_handle::Group& g, const hb::DevView& V, const hb::SeriesDev& P) {
+    if (g.dist)
+        hb::hb_march_kernel<NMAX, true><<<g.n_tiles, kBlock, 0, h->stream>>>(V, P, g.ids.p);
+    else
+        hb::hb_march_kernel<NMAX, false><<<g.n_tiles, kBlock, 0, h->stream>>>(V, P, g.ids.p);
+}
+
+void launch_series(hb_handle* h, const hb::SeriesDev& P) {
+    const hb::DevView V = h->view();
+    for (auto& gp : h->groups) {
+        const hb_handle::Group& g = *gp;
+        switch (g.nmax_tier) {
+            case 8: launch_tier<8>(h, g, V, P); break;
+            case 16: launch_tier<16>(h, g, V, P); break;
+            case 24: launch_tier<24>(h, g, V, P); break;
+            case 32: launch_tier<32>(h, g, V, P); break;
+            case 48: launch_tier<48>(h, g, V, P); break;
+            default: launch_tier<64>(h, g, V, P); break;
+        }
+        HB_CUDA(cudaGetLastError());
+        h->launches += 1;
+    }
+}
+
+void validate_series(const hb_handle* h, const hb_series* s) {
+    if (!s) throw std::runtime_error("null series");
+    if (s->n_steps < 0) throw std::runtime_error("n_steps must be >= 0");
+    if (s->n_sites < 1) throw std::runtime_error("n_sites must be >= 1");
+    if (!s->weather) throw std::runtime_error("Trying to march on Thermal Model, but dry bulb temperature was not provided");
+    const hb::BatchPlan& B = h->plan;
+    int64_t need = s->n_steps;
+    if (s->weather_mode == HB_WEATHER_LINEAR) need = (int64_t)s->n_steps + 1;
+    if (s->weather_mode == HB_WEATHER_PER_SUBSTEP) {
+        // all models of a site must share S
+        std::vector<int> site_S(s->n_sites, -1);
+        int64_t max_rows = 0;
+        for (size_t m = 0; m < B.models.size(); ++m) {
+            const int site = s->model_site ? s->model_site[m] : 0;
+            if (site < 0 || site >= s->n_sites) throw std::runtime_error("model_site out of range");
+            if (site_S[site] < 0) site_S[site] = B.models[m].dt_subdivisions;
+            else if (site_S[site] != B.models[m].dt_subdivisions)
+                throw std::runtime_error("HB_WEATHER_PER_SUBSTEP needs one dt_subdivisions per site");
+            max_rows = std::max<int64_t>(max_rows, (int64_t)s->n_steps * B.models[m].dt_subdivisions);
+        }
+        need = max_rows;
+    } else if (s->weather_mode != HB_WEATHER_STEP_CONSTANT && s->weather_mode != HB_WEATHER_LINEAR) {
+        throw std::runtime_error("unknown weather_mode");
+    }
+    if (s->weather_rows < need) throw std::runtime_error("weather table has too few rows for this series");
+    if (s->input_mode != HB_INPUT_STATE && !s->inputs) throw std::runtime_error("inputs missing for this input_mode");
+    if (s->input_mode < HB_INPUT_STATE || s->input_mode > HB_INPUT_PER_SURFACE) throw std::runtime_error("unknown input_mode");
+    if (s->model_site)
+        for (size_t m = 0; m < B.models.size(); ++m)
+            if (s->model_site[m] < 0 || s->model_site[m] >= s->n_sites) throw std::runtime_error("model_site out of range");
+}
+
+void update_sites(hb_handle* h, const hb_series* s) {
+    const hb::BatchPlan& B = h->plan;
+    std::vector<int32_t> ms(B.models.size(), 0);
+    if (s->model_site) ms.assign(s->model_site, s->model_site + B.models.size());
+    if (ms == h->model_site_cache) return;
+    h->model_site_cache = ms;
+    std::fill(h->host_site.begin(), h->host_site.end(), 0);
+    for (size_t gd = 0; gd < B.dev_surface_of.size(); ++gd) h->host_site[B.dev_surface_of[gd]] = ms[B.surface_model[gd]];
+    HB_CUDA(cudaMemcpyAsync(h->site.p, h->host_site.data(), h->host_site.size() * sizeof(int32_t),
+                            cudaMemcpyHostToDevice, h->stream));
+}
+
+int64_t input_count(const hb_handle* h, const hb_series* s) {
+    if (s->input_mode == HB_INPUT_SITE) return (int64_t)s->n_sites * s->n_steps * 4;
+    if (s->input_mode == HB_INPUT_PER_SURFACE) return (int64_t)s->n_steps * (int64_t)h->plan.surfaces.size() * 4;
+    return 0;
+}
+
+void check_status(hb_handle* h) {
+    // a non-zero per-surface status word is the reference's panic!
+    std::vector<int32_t> st(h->plan.n_dev_surfaces);
+    HB_CUDA(cudaMemcpyAsync(st.data(), h->status.p, st.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    HB_CUDA(cudaStreamSynchronize(h->stream));
+    for (size_t g = 0; g < st.size(); ++g) {
+        if (!st[g]) continue;
+        std::string what;
+        if (st[g] & hb::ST_NAN_H) what += " NaN convection coefficients;";
+        if (st[g] & hb::ST_NAN_ERR) what += " NaN no-mass error;";
+        if (st[g] & hb::ST_NAN_ZONE) what += " Future temperatures is NaN;";
+        if (st[g] & hb::ST_ITER_CAP) what += " Excessive number of iterations;";
+        if (st[g] & hb::ST_BAD_GAMMA) what += " cavity tilt out of range;";
+        throw std::domain_error("physics failure on device surface slot " + std::to_string(g) + ":" + what);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* hb_last_error(void) { return g_err.c_str(); }
+const char* hb_version(void) { return "heat_b200 0.1 (sm_100a)"; }
+
+hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) {
+    if (!out) return HB_ERR_INVALID;
+    *out = nullptr;
+    std::unique_ptr<hb_handle> h(new hb_handle());
+    hb_status rc = guarded([&] {
+        hb::plan_batch(desc, h->plan);
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count <= 0)
+            throw CudaError(std::string("no usable CUDA device (heat_b200 has no CPU fallback): ") +
+                            (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+        if (device < 0 || device >= count) throw CudaError("device index out of range");
+        h->device = device;
+        HB_CUDA(cudaSetDevice(device));
+        HB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        build_device(h.get());
+    });
+    if (rc == HB_OK) *out = h.release();
+    return rc;
+}
+
+void hb_destroy(hb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamDestroy(h->stream);
+    }
+    delete h;
+}
+
+int32_t hb_n_models(const hb_handle* h) { return (int32_t)h->plan.models.size(); }
+int64_t hb_n_surfaces_total(const hb_handle* h) { return (int64_t)h->plan.surfaces.size(); }
+int64_t hb_n_zones_total(const hb_handle* h) { return (int64_t)h->plan.zone_volume.size(); }
+int64_t hb_state_len_total(const hb_handle* h) { return h->plan.state_len_total; }
+int64_t hb_nodes_total(const hb_handle* h) { return h->plan.nodes_total; }
+int64_t hb_updates_per_step(const hb_handle* h) { return h->plan.updates_per_step; }
+int64_t hb_launch_count(const hb_handle* h) { return h->launches; }
+
+hb_status hb_get_model_info(const hb_handle* h, int32_t model, hb_model_info* out) {
+    return guarded([&] {
+        if (model < 0 || model >= (int32_t)h->plan.models.size()) throw std::runtime_error("model index out of range");
+        const hb::ModelPlan& M = h->plan.models[model];
+        out->n_zones = M.n_zones;
+        out->n_surfaces = M.n_surfaces;
+        out->zone_begin = M.zone_begin;
+        out->surface_begin = M.surface_begin;
+        out->dt_subdivisions = M.dt_subdivisions;
+        out->dt = M.dt;
+        out->state_offset = M.state_offset;
+        out->state_len = M.state_len;
+        out->nodes = M.nodes;
+    });
+}
+
+hb_status hb_get_surface_info(const hb_handle* h, int64_t s, hb_surface_info* out) {
+    return guarded([&] {
+        if (s < 0 || s >= (int64_t)h->plan.plans.size()) throw std::runtime_error("surface index out of range");
+        const hb::SurfacePlan& P = h->plan.plans[s];
+        out->n_nodes = P.n_nodes;
+        out->n_layers = (int32_t)P.n_elements.size();
+        out->tstep_subdivision = P.tstep_subdivision;
+        out->n_massive_chunks = (int32_t)P.massive_chunks.size() / 2;
+        out->n_nomass_chunks = (int32_t)P.nomass_chunks.size() / 2;
+        out->state_offset = h->plan.surface_state_offset[s];
+        out->front_emissivity = P.front_emissivity;
+        out->back_emissivity = P.back_emissivity;
+        out->wind_speed_modifier = P.wind_speed_modifier;
+        out->cos_tilt = P.cos_tilt;
+    });
+}
+
+hb_status hb_get_surface_arrays(const hb_handle* h, int64_t s, int32_t* n_elements, double* mass, double* u,
+                                double* front_alpha, double* back_alpha, int32_t* massive_chunks,
+                                int32_t* nomass_chunks) {
+    return guarded([&] {
+        if (s < 0 || s >= (int64_t)h->plan.plans.size()) throw std::runtime_error("surface index out of range");
+        const hb::SurfacePlan& P = h->plan.plans[s];
+        if (n_elements) std::copy(P.n_elements.begin(), P.n_elements.end(), n_elements);
+        if (mass) std::copy(P.mass.begin(), P.mass.end(), mass);
+        if (u) std::copy(P.u.begin(), P.u.end(), u);
+        if (front_alpha) std::copy(P.front_alpha.begin(), P.front_alpha.end(), front_alpha);
+        if (back_alpha) std::copy(P.back_alpha.begin(), P.back_alpha.end(), back_alpha);
+        if (massive_chunks) std::copy(P.massive_chunks.begin(), P.massive_chunks.end(), massive_chunks);
+        if (nomass_chunks) std::copy(P.nomass_chunks.begin(), P.nomass_chunks.end(), nomass_chunks);
+    });
+}
+
+// Scatter a reference-layout state vector into the SoA device buffers.
+hb_status hb_set_state(hb_handle* h, const double* state) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        const hb::BatchPlan& B = h->plan;
+        const int64_t NS = B.n_dev_surfaces;
+        std::vector<double> nodeT(B.node_slab_len, 0.), sc(8 * NS, 0.), zoneT(B.n_dev_zones, 0.);
+        for (size_t m = 0; m < B.models.size(); ++m) {
+            const hb::ModelPlan& M = B.models[m];
+            for (int z = 0; z < M.n_zones; ++z) zoneT[B.dev_zone_of[M.zone_begin + z]] = state[M.state_offset + z];
+        }
+        for (size_t gd = 0; gd < B.plans.size(); ++gd) {
+            const int64_t g = B.dev_surface_of[gd];
+            const hb::Tile& tile = B.tiles[g / kBlock];
+            const int t = (int)(g % kBlock);
+            const double* p = state + B.surface_state_offset[gd];
+            for (int k = 0; k < 8; ++k) sc[k * NS + g] = p[k];
+            for (int i = 0; i < B.plans[gd].n_nodes; ++i) nodeT[tile.node_offset + (int64_t)i * kBlock + t] = p[8 + i];
+        }
+        HB_CUDA(cudaMemcpyAsync(h->nodeT.p, nodeT.data(), nodeT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaMemcpyAsync(h->sc.p, sc.data(), sc.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaMemcpyAsync(h->zoneT.p, zoneT.data(), zoneT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+    });
+}
+
+static void gather_state(const hb::BatchPlan& B, const double* nodeT, const double* sc, const double* zoneT,
+                         double* state) {
+    const int64_t NS = B.n_dev_surfaces;
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const hb::ModelPlan& M = B.models[m];
+        for (int z = 0; z < M.n_zones; ++z) state[M.state_offset + z] = zoneT[B.dev_zone_of[M.zone_begin + z]];
+    }
+    for (size_t gd = 0; gd < B.plans.size(); ++gd) {
+        const int64_t g = B.dev_surface_of[gd];
+        const hb::Tile& tile = B.tiles[g / kBlock];
+        const int t = (int)(g % kBlock);
+        double* p = state + B.surface_state_offset[gd];
+        for (int k = 0; k < 8; ++k) p[k] = sc[k * NS + g];
+        for (int i = 0; i < B.plans[gd].n_nodes; ++i) p[8 + i] = nodeT[tile.node_offset + (int64_t)i * kBlock + t];
+    }
+}
+
+hb_status hb_get_state(hb_handle* h, double* state) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        const hb::BatchPlan& B = h->plan;
+        std::vector<double> nodeT(B.node_slab_len), sc(8 * B.n_dev_surfaces), zoneT(B.n_dev_zones);
+        HB_CUDA(cudaMemcpyAsync(nodeT.data(), h->nodeT.p, nodeT.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaMemcpyAsync(sc.data(), h->sc.p, sc.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaMemcpyAsync(zoneT.data(), h->zoneT.p, zoneT.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        gather_state(B, nodeT.data(), sc.data(), zoneT.data(), state);
+    });
+}
+
+hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const double* infiltration_volume,
+                             const double* infiltration_temperature, const double* ventilation_volume,
+                             const double* ventilation_temperature) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        const hb::BatchPlan& B = h->plan;
+        const int64_t NZ = B.n_dev_zones;
+        auto scatter = [&](const double* src, double dflt, DevBuf<double>& dst) {
+            std::vector<double> v(NZ, dflt);
+            if (src)
+                for (size_t z = 0; z < B.dev_zone_of.size(); ++z) v[B.dev_zone_of[z]] = src[z];
+            HB_CUDA(cudaMemcpyAsync(dst.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+            HB_CUDA(cudaStreamSynchronize(h->stream));
+        };
+        if ((infiltration_temperature && !infiltration_volume) || (ventilation_temperature && !ventilation_volume))
+            throw std::runtime_error("Space has infiltration/ventilation temperature but not volume");
+        scatter(q_internal, 0., h->zq);
+        scatter(infiltration_volume, 0., h->zinf_v);
+        scatter(infiltration_temperature, NAN, h->zinf_t);
+        scatter(ventilation_volume, 0., h->zvent_v);
+        scatter(ventilation_temperature, NAN, h->zvent_t);
+    });
+}
+
+hb_status hb_march_series(hb_handle* h, const hb_series* s) {
+    hb_status rc = guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        validate_series(h, s);
+        if (s->n_steps == 0) return;
+        update_sites(h, s);
+        const hb::BatchPlan& B = h->plan;
+        DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec;
+        const int64_t wcount = (int64_t)s->n_sites * s->weather_rows * 3;
+        d_weather.alloc(wcount);
+        HB_CUDA(cudaMemcpyAsync(d_weather.p, s->weather, wcount * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        const int64_t icount = input_count(h, s);
+        if (icount) {
+            d_inputs.alloc(icount);
+            HB_CUDA(cudaMemcpyAsync(d_inputs.p, s->inputs, icount * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        }
+        const int n_rec = s->record_every > 0 ? s->n_steps / s->record_every : 0;
+        hb::SeriesDev P{};
+        P.n_steps = s->n_steps;
+        P.weather_mode = s->weather_mode;
+        P.input_mode = s->input_mode;
+        P.ir_mode = s->ir_mode;
+        P.weather = d_weather.p;
+        P.weather_rows = s->weather_rows;
+        P.inputs = d_inputs.p;
+        P.n_desc_surfaces = (int64_t)B.surfaces.size();
+        P.record_every = n_rec > 0 && (s->zone_t_record || s->state_record) ? s->record_every : 0;
+        P.slab_len = B.node_slab_len;
+        if (P.record_every) {
+            d_zone_rec.alloc((size_t)n_rec * B.n_dev_zones);
+            P.zone_rec = d_zone_rec.p;
+            if (s->state_record) {
+                d_node_rec.alloc((size_t)n_rec * B.node_slab_len);
+                d_sc_rec.alloc((size_t)n_rec * 8 * B.n_dev_surfaces);
+                P.node_rec = d_node_rec.p;
+                P.sc_rec = d_sc_rec.p;
+            }
+        }
+        launch_series(h, P);
+        if (P.record_every) {
+            std::vector<double> zr((size_t)n_rec * B.n_dev_zones);
+            HB_CUDA(cudaMemcpyAsync(zr.data(), d_zone_rec.p, zr.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            std::vector<double> nr, sr;
+            if (s->state_record) {
+                nr.resize((size_t)n_rec * B.node_slab_len);
+                sr.resize((size_t)n_rec * 8 * B.n_dev_surfaces);
+                HB_CUDA(cudaMemcpyAsync(nr.data(), d_node_rec.p, nr.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+                HB_CUDA(cudaMemcpyAsync(sr.data(), d_sc_rec.p, sr.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+            }
+            HB_CUDA(cudaStreamSynchronize(h->stream));
+            const int64_t nz_total = (int64_t)B.zone_volume.size();
+            for (int r = 0; r < n_rec; ++r) {
+                const double* z = zr.data() + (size_t)r * B.n_dev_zones;
+                if (s->zone_t_record)
+                    for (int64_t k = 0; k < nz_total; ++k) s->zone_t_record[(int64_t)r * nz_total + k] = z[B.dev_zone_of[k]];
+                if (s->state_record)
+                    gather_state(B, nr.data() + (size_t)r * B.node_slab_len, sr.data() + (size_t)r * 8 * B.n_dev_surfaces, z,
+                                 s->state_record + (int64_t)r * B.state_len_total);
+            }
+        }
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        HB_CUDA(cudaGetLastError());
+    });
+    if (rc != HB_OK) return rc;
+    try {
+        check_status(h);
+    } catch (const CudaError& e) {
+        g_err = e.what();
+        return HB_ERR_CUDA;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return HB_ERR_PHYSICS;
+    }
+    return HB_OK;
+}
+
+hb_status hb_upload(hb_handle* h, const double* host, int64_t count, double** dev_out) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        double* p = nullptr;
+        HB_CUDA(cudaMalloc(&p, (size_t)std::max<int64_t>(count, 1) * sizeof(double)));
+        if (count) HB_CUDA(cudaMemcpyAsync(p, host, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        *dev_out = p;
+    });
+}
+
+hb_status hb_free_dev(hb_handle* h, double* dev) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        if (dev) HB_CUDA(cudaFree(dev));
+    });
+}
+
+hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_ms) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        validate_series(h, s);
+        update_sites(h, s);
+        hb::SeriesDev P{};
+        P.n_steps = s->n_steps;
+        P.weather_mode = s->weather_mode;
+        P.input_mode = s->input_mode;
+        P.ir_mode = s->ir_mode;
+        P.weather = s->weather;
+        P.weather_rows = s->weather_rows;
+        P.inputs = s->inputs;
+        P.n_desc_surfaces = (int64_t)h->plan.surfaces.size();
+        P.record_every = 0;
+        P.slab_len = h->plan.node_slab_len;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (elapsed_ms) {
+            HB_CUDA(cudaEventCreate(&e0));
+            HB_CUDA(cudaEventCreate(&e1));
+            HB_CUDA(cudaEventRecord(e0, h->stream));
+        }
+        if (s->n_steps > 0) launch_series(h, P);
+        if (elapsed_ms) {
+            HB_CUDA(cudaEventRecord(e1, h->stream));
+            HB_CUDA(cudaEventSynchronize(e1));
+            HB_CUDA(cudaEventElapsedTime(elapsed_ms, e0, e1));
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+        } else {
+            HB_CUDA(cudaStreamSynchronize(h->stream));
+        }
+        HB_CUDA(cudaGetLastError());
+    });
+}
+
+hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        const double init[8] = {0., INFINITY, -INFINITY, 0., INFINITY, -INFINITY, 0., 0.};
+        HB_CUDA(cudaMemcpyAsync(h->red_out.p, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaMemsetAsync(h->red_iout.p, 0, 4 * sizeof(unsigned long long), h->stream));
+        const int n_tiles = (int)h->plan.tiles.size();
+        const int grid = std::min(n_tiles, 148 * 8);
+        hb::hb_reduce_kernel<<<grid, kBlock, 0, h->stream>>>(h->view(), n_tiles, h->red_out.p, h->red_iout.p);
+        HB_CUDA(cudaGetLastError());
+        h->launches += 1;
+        double o[8];
+        unsigned long long io[4];
+        HB_CUDA(cudaMemcpyAsync(o, h->red_out.p, sizeof(o), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaMemcpyAsync(io, h->red_iout.p, sizeof(io), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        out->sum_zone_t = o[0]; out->min_zone_t = o[1]; out->max_zone_t = o[2];
+        out->sum_node_t = o[3]; out->min_node_t = o[4]; out->max_node_t = o[5];
+        out->front_conv_energy_j = o[6]; out->back_conv_energy_j = o[7];
+        out->n_zones = (int64_t)io[0]; out->n_nodes = (int64_t)io[1];
+        out->nomass_iterations = (int64_t)io[2]; out->status_flags = (int64_t)io[3];
+    });
+}
+
+hb_status hb_reset_energy(hb_handle* h) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        HB_CUDA(cudaMemsetAsync(h->energy_f.p, 0, h->energy_f.n * sizeof(double), h->stream));
+        HB_CUDA(cudaMemsetAsync(h->energy_b.p, 0, h->energy_b.n * sizeof(double), h->stream));
+        HB_CUDA(cudaMemsetAsync(h->nm_iters.p, 0, h->nm_iters.n * sizeof(unsigned long long), h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+    });
+}
+
+hb_status hb_measure_fp64_peak(int32_t device, double* tflops) {
+    return guarded([&] {
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) throw CudaError("no usable CUDA device");
+        HB_CUDA(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        HB_CUDA(cudaGetDeviceProperties(&prop, device));
+        const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+        double* out = nullptr;
+        HB_CUDA(cudaMalloc(&out, (size_t)blocks * threads * sizeof(double)));
+        cudaEvent_t e0, e1;
+        HB_CUDA(cudaEventCreate(&e0));
+        HB_CUDA(cudaEventCreate(&e1));
+        double best = 0.;
+        for (int rep = 0; rep < 5; ++rep) {
+            HB_CUDA(cudaEventRecord(e0));
+            hb::hb_dfma_probe_kernel<<<blocks, threads>>>(out, iters, 1.0 + rep);
+            HB_CUDA(cudaEventRecord(e1));
+            HB_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            HB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            const double flops = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+            if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaFree(out);
+        *tflops = best;
+    });
+}
+
+hb_status hb_flush_l2(hb_handle* h, int64_t bytes) {
+    return guarded([&] {
+        HB_CUDA(cudaSetDevice(h->device));
+        const size_t n = (size_t)bytes / sizeof(double);
+        if (h->flush.n < n) h->flush.alloc(n);
+        hb::hb_fill_kernel<<<148 * 4, 256, 0, h->stream>>>(h->flush.p, (int64_t)n, 1.0);
+        HB_CUDA(cudaGetLastError());
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+    });
+}
+
+}  // extern "C"

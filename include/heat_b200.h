@@ -1,0 +1,236 @@
+/*
+ * heat_b200.h — C ABI of the B200-native wall-conduction time-stepping path.
+ *
+ * Drop-in boundary for SIMPLE-BuildingSimulation/heat's `ThermalModel`
+ * (reference: src/model.rs:188-428, trait communication_protocols::SimulationModel):
+ *
+ *   reference                                           this ABI
+ *   ---------------------------------------------------------------------------------------
+ *   ThermalModel::new(meta, (), model, header, n)        hb_create()            model.rs:215-354
+ *   SimulationStateHeader::take_values()                 hb_get_state() after create (initial values)
+ *   ThermalModel::allocate_memory()                      (inside hb_create; scratch is device memory) :193-207
+ *   ThermalModel::march(date, weather, model, state, m)  hb_march_series(n_steps = 1)  model.rs:359-427
+ *   caller reads/writes SimulationState slots            hb_set_state()/hb_get_state(), same slot order
+ *   ThermalModel::dt_subdivisions(), .dt                 hb_model_info                  model.rs:73-76,434
+ *   Discretization {segments,tstep_subdivision,n_elements} hb_surface_info/_arrays      discretization.rs:71-87
+ *   Err(String) / panic!                                 hb_status != HB_OK + hb_last_error()
+ *
+ * plus the batched entry point the north star adds: one handle holds MANY independent models
+ * (walls with their own zone, shoebox buildings, ...) and hb_march_series() advances all of them over
+ * many main time steps in one persistent kernel launch.
+ *
+ * Host work that stays on the host (discretization.rs:95-544 — massive/no-mass classification, element
+ * counts, tstep_subdivision; surface.rs:463-540 — chunks, solar alphas, wind modifier) is done inside
+ * hb_create() in C++; the results are packed into SoA device buffers.  All compute after that runs in
+ * hand-written CUDA for sm_100a.  There is NO CPU fallback: every entry point that needs the device
+ * fails with HB_ERR_CUDA when no CUDA device is usable.
+ *
+ * Conventions: plain pointers and sizes only; all `double*` are HOST pointers unless the name ends in
+ * `_dev`; a handle is not re-entrant; no global state except the thread-local last-error string.
+ */
+#ifndef HEAT_B200_H
+#define HEAT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t hb_status;
+enum {
+    HB_OK = 0,
+    HB_ERR_INVALID = 1,     /* bad descriptor / argument (reference: Err(String)) */
+    HB_ERR_CUDA = 2,        /* CUDA runtime error or no device */
+    HB_ERR_PHYSICS = 3,     /* a wall reported NaN / unsupported boundary (reference: panic!) */
+    HB_ERR_UNSUPPORTED = 4  /* e.g. Boundary::Ground (reference: unimplemented!, model.rs:92) */
+};
+
+/* simple_model::Boundary as matched at surface.rs:611-702 */
+enum { HB_BOUNDARY_OUTDOOR = 0, HB_BOUNDARY_SPACE = 1, HB_BOUNDARY_AMBIENT = 2, HB_BOUNDARY_GROUND = 3 };
+/* simple_model::Substance::{Normal, Gas} */
+enum { HB_LAYER_SOLID = 0, HB_LAYER_GAS = 1 };
+/* gas.rs:45-74 */
+enum { HB_GAS_AIR = 0, HB_GAS_ARGON = 1, HB_GAS_KRYPTON = 2, HB_GAS_XENON = 3 };
+/* simple_model::TerrainClass, surface.rs:151-163 (NONE: no SiteDetails → Urban; UNSET: details without terrain) */
+enum { HB_TERRAIN_NONE = -1, HB_TERRAIN_COUNTRY = 0, HB_TERRAIN_SUBURBS = 1, HB_TERRAIN_CITY = 2,
+       HB_TERRAIN_OCEAN = 3, HB_TERRAIN_URBAN = 4, HB_TERRAIN_UNSET = 5 };
+
+/* One material layer = simple_model Material + its Substance. NaN in an optional field = "not set". */
+typedef struct {
+    int32_t kind;                 /* HB_LAYER_* */
+    int32_t gas;                  /* HB_GAS_* when kind == HB_LAYER_GAS */
+    double thickness;             /* [m] */
+    double conductivity;          /* [W/m.K] */
+    double density;               /* [kg/m3] */
+    double specific_heat;         /* [J/kg.K] */
+    double front_emissivity;      /* default 0.84 (surface.rs:449) */
+    double back_emissivity;       /* default 0.84 */
+    double front_solar_abs;       /* default 0.84 (glazing.rs:86) */
+    double back_solar_abs;        /* default 0.84 (glazing.rs:87) */
+    double solar_transmittance;   /* default 0    (glazing.rs:85) */
+} hb_layer;
+
+/* One simple_model Surface or Fenestration with what ThermalModel::new derives from its geometry
+ * (model.rs:248-256).  Zone indices are LOCAL to the surface's model. */
+typedef struct {
+    int32_t construction;
+    int32_t is_fenestration;      /* within a model: all surfaces first, then all fenestrations */
+    int32_t front_kind, back_kind;
+    int32_t front_zone, back_zone;
+    double front_ambient_t, back_ambient_t;
+    double area, perimeter;
+    double centroid_z;
+    double normal[3];
+    double front_hs_override;     /* NaN = none; mirrors the debug-only `front_hs: Option<Float>` (surface.rs:372-380) */
+    double back_hs_override;
+    double front_emissivity_override; /* NaN = none; mirrors writes to the pub field (validate_wall_heat_transfer.rs:630) */
+    double back_emissivity_override;
+} hb_surface;
+
+/* A batch of independent models sharing one pool of constructions. */
+typedef struct {
+    int32_t n_layers;
+    const hb_layer* layers;
+    int32_t n_constructions;
+    const int32_t* construction_offset;   /* n_constructions + 1 */
+    int32_t n_models;
+    const int32_t* model_zone_offset;     /* n_models + 1 */
+    const int32_t* model_surface_offset;  /* n_models + 1 */
+    const double* zone_volume;            /* [total zones] */
+    const hb_surface* surfaces;           /* [total surfaces] */
+    const int32_t* model_terrain;         /* [n_models] HB_TERRAIN_* or NULL (= NONE) */
+    int32_t steps_per_hour;               /* `n` of ThermalModel::new */
+} hb_batch_desc;
+
+typedef struct hb_handle hb_handle;
+
+const char* hb_last_error(void);
+const char* hb_version(void);
+
+/* ThermalModel::new for every model of the batch, on CUDA device `device`. */
+hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out);
+void hb_destroy(hb_handle* h);
+
+/* ---- layout / discretization queries ---- */
+typedef struct {
+    int32_t n_zones, n_surfaces;          /* of this model (surfaces + fenestrations) */
+    int32_t zone_begin, surface_begin;    /* global indices */
+    int32_t dt_subdivisions;              /* substeps per main step, model.rs:331 */
+    double dt;                            /* [s] model.rs:326-330 */
+    int64_t state_offset;                 /* into the concatenated state vector */
+    int32_t state_len;                    /* reference SimulationState length for this model */
+    int64_t nodes;                        /* Σ n_nodes over its surfaces */
+} hb_model_info;
+
+typedef struct {
+    int32_t n_nodes;
+    int32_t n_layers;
+    int32_t tstep_subdivision;            /* discretization.rs:83 */
+    int32_t n_massive_chunks, n_nomass_chunks;
+    int64_t state_offset;                 /* index of the front-h slot in the concatenated state vector */
+    double front_emissivity, back_emissivity;
+    double wind_speed_modifier;
+    double cos_tilt;
+} hb_surface_info;
+
+int32_t hb_n_models(const hb_handle* h);
+int64_t hb_n_surfaces_total(const hb_handle* h);
+int64_t hb_n_zones_total(const hb_handle* h);
+int64_t hb_state_len_total(const hb_handle* h);
+int64_t hb_nodes_total(const hb_handle* h);
+/* Σ over surfaces of n_nodes × dt_subdivisions(model): node-substep updates done by ONE main step */
+int64_t hb_updates_per_step(const hb_handle* h);
+hb_status hb_get_model_info(const hb_handle* h, int32_t model, hb_model_info* out);
+hb_status hb_get_surface_info(const hb_handle* h, int64_t surface, hb_surface_info* out);
+/* arrays of the surface: n_elements[n_layers]; mass[n_nodes]; u[n_nodes] (solid k/dx, cavity -1, last 0);
+ * front_alpha/back_alpha[n_nodes]; massive/nomass chunks as [ini,fin] pairs. Any pointer may be NULL. */
+hb_status hb_get_surface_arrays(const hb_handle* h, int64_t surface, int32_t* n_elements, double* mass, double* u,
+                                double* front_alpha, double* back_alpha, int32_t* massive_chunks,
+                                int32_t* nomass_chunks);
+
+/* ---- state: reference slot order, models concatenated ----
+ * per model: [zone T × n_zones] then per surface (surfaces, then fenestrations):
+ * front h, back h, front conv. flow, back conv. flow, front solar irr., back solar irr., front IR irr.,
+ * back IR irr., node T × n_nodes   (zone.rs:43-50, surface.rs:428-442) */
+hb_status hb_set_state(hb_handle* h, const double* state);
+hb_status hb_get_state(hb_handle* h, double* state);
+
+/* Per-zone inputs that are SimulationState elements in the reference (model.rs:502-544):
+ * Σ HVAC+luminaire power, infiltration / ventilation volume flow and temperature (NaN temperature = absent).
+ * Arrays over all zones of the batch; NULL = none. */
+hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const double* infiltration_volume,
+                             const double* infiltration_temperature, const double* ventilation_volume,
+                             const double* ventilation_temperature);
+
+/* ---- marching ---- */
+enum {
+    HB_WEATHER_STEP_CONSTANT = 0, /* row t holds for every substep of main step t (validate driver, :676-679) */
+    HB_WEATHER_LINEAR = 1,        /* substep s of step t samples row[t] + (row[t+1]-row[t])·(s+1)/S; n_steps+1 rows */
+    HB_WEATHER_PER_SUBSTEP = 2    /* rows [t][s], s < S; all models of a site must share S (arbitrary `Weather` impl) */
+};
+enum {
+    HB_INPUT_STATE = 0,           /* keep the irradiance slots as they are in the state */
+    HB_INPUT_SITE = 1,            /* per site rows [t][4] = front solar, back solar, front IR, back IR, written
+                                     into every surface of the site's models at the start of main step t */
+    HB_INPUT_PER_SURFACE = 2      /* rows [t][surface][4] */
+};
+enum {
+    HB_IR_IRRADIANCE = 0,         /* IR columns are irradiances [W/m2] */
+    HB_IR_NET_GAIN = 1            /* IR columns are net thermal radiation gains [W]: irradiance =
+                                     gain/area/ε + σ(T_face+273.15)^4 evaluated at the start of the main step,
+                                     skipped when ε ≤ 1e-3 (validate_wall_heat_transfer.rs:689-699) */
+};
+
+typedef struct {
+    int32_t n_steps;              /* main time steps to advance */
+    int32_t weather_mode;         /* HB_WEATHER_* */
+    int32_t n_sites;              /* number of weather tables (≥ 1) */
+    const int32_t* model_site;    /* [n_models] or NULL (all models on site 0) */
+    const double* weather;        /* [site][row][3]: dry bulb [C], wind direction [deg], wind speed [m/s] */
+    int64_t weather_rows;         /* rows per site */
+    int32_t input_mode;           /* HB_INPUT_* */
+    int32_t ir_mode;              /* HB_IR_* */
+    const double* inputs;         /* per mode above; NULL for HB_INPUT_STATE */
+    int32_t record_every;         /* 0: no recording; k: record after every k-th main step */
+    double* zone_t_record;        /* [n_steps/record_every][total zones] or NULL */
+    double* state_record;         /* [n_steps/record_every][state_len_total] or NULL (small batches only) */
+} hb_series;
+
+/* Advance every model by series->n_steps main steps (each = dt_subdivisions substeps, model.rs:369-424).
+ * Host buffers in, host buffers out; the state stays resident on the device between calls. */
+hb_status hb_march_series(hb_handle* h, const hb_series* series);
+
+/* Same, with inputs already resident on the device (weather_dev/inputs_dev uploaded once with hb_upload) and
+ * no recording; `elapsed_ms` (may be NULL) receives the CUDA-event time of the kernel(s) on the handle's stream. */
+hb_status hb_upload(hb_handle* h, const double* host, int64_t count, double** dev_out);
+hb_status hb_free_dev(hb_handle* h, double* dev);
+hb_status hb_march_series_dev(hb_handle* h, const hb_series* series_with_dev_pointers, float* elapsed_ms);
+
+/* Number of kernel launches issued by this handle so far (bench.py's gpu_launches). */
+int64_t hb_launch_count(const hb_handle* h);
+
+/* ---- ensemble reductions (K3): Σ front/back convective energy is integrated in-kernel ---- */
+typedef struct {
+    double sum_zone_t, min_zone_t, max_zone_t;
+    double sum_node_t, min_node_t, max_node_t;
+    double front_conv_energy_j;   /* Σ_surfaces Σ_substeps flow_front·A·dt since create/reset (model.rs:161) */
+    double back_conv_energy_j;
+    int64_t n_zones, n_nodes;
+    int64_t nomass_iterations;    /* total fixed-point iterations (surface.rs:808-896), branch-parity diagnostic */
+    int64_t status_flags;         /* OR of per-surface status words (non-zero = HB_ERR_PHYSICS) */
+} hb_ensemble_stats;
+/* Local (this handle / this GPU) statistics; cross-GPU combination is a NCCL all-reduce done by the host layer. */
+hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out);
+hb_status hb_reset_energy(hb_handle* h);
+
+/* ---- device probes used by bench.py ---- */
+/* Dependent-free DFMA micro-benchmark: returns measured FP64 TFLOP/s (FMA = 2 FLOP) on `device`. */
+hb_status hb_measure_fp64_peak(int32_t device, double* tflops);
+/* Writes `bytes` of device memory (L2 flush between timed iterations). */
+hb_status hb_flush_l2(hb_handle* h, int64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
