@@ -131,12 +131,53 @@ def _random_layers(rng: SplitMix64, n: int):
 
 
 def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, steps_per_hour: int = 1,
-                  max_layers: int = 4) -> D.BatchDesc:
+                  max_layers: int = 4, max_nodes: int = 128) -> D.BatchDesc:
     """`n_walls` independent models, each one exterior wall + its own zone (massive_full topology).
 
     Massive walls: 1..max_layers random solid layers. Mixed walls (fraction `mixed_fraction`): polyurethane /
     random solid / polyurethane, whose outer layers the reference's rule classifies as no-mass.
+    Walls that the reference's discretization rule cuts into more than `max_nodes` nodes (thick layers of very low
+    diffusivity) are re-drawn, up to 8 times, then replaced by a 20 cm concrete wall.
     """
+    d = _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers)
+    if not max_nodes:
+        return d
+    from .model import ThermalBatch
+    for attempt in range(1, 10):
+        plan = ThermalBatch(d, device=-1)  # host-only planning handle (discretization runs on the host anyway)
+        n_nodes = np.array([plan.surface_info(s).n_nodes for s in range(n_walls)]) if n_walls <= 2000 else \
+            _bulk_n_nodes(plan, n_walls)
+        plan.close()
+        bad = np.nonzero(n_nodes > max_nodes)[0]
+        if bad.size == 0:
+            return d
+        # the layers to re-draw: every layer of a bad wall except the fixed polyurethane skins of mixed walls
+        idx = np.concatenate([np.arange(d.construction_offset[w], d.construction_offset[w + 1]) for w in bad])
+        skin = (d.layers["thickness"][idx] == 0.02) & (d.layers["conductivity"][idx] == POLYURETHANE["conductivity"])
+        idx = idx[~skin]
+        if attempt < 9:
+            k, rho, cp, th = _random_layers(SplitMix64(seed + 7919 * attempt), idx.size)
+        else:
+            k, rho, cp = (np.full(idx.size, CONCRETE[f]) for f in ("conductivity", "density", "specific_heat"))
+            th = np.full(idx.size, 0.05)
+        d.layers["conductivity"][idx], d.layers["density"][idx] = k, rho
+        d.layers["specific_heat"][idx], d.layers["thickness"][idx] = cp, th
+    return d
+
+
+def _bulk_n_nodes(plan, n: int) -> np.ndarray:
+    import ctypes as C
+    from . import _lib
+    out = np.empty(n, np.int64)
+    info = _lib.SurfaceInfoC()
+    fn, h = plan._lib.hb_get_surface_info, plan._h
+    for s in range(n):
+        fn(h, s, C.byref(info))
+        out[s] = info.n_nodes
+    return out
+
+
+def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers) -> D.BatchDesc:
     rng = SplitMix64(seed)
     n_lay = 1 + (rng.next_u64(n_walls) % np.uint64(max_layers)).astype(np.int64)
     is_mixed = rng.uniform(n_walls) < mixed_fraction

@@ -8,7 +8,9 @@
 #include <string>
 #include <vector>
 
-#include "hb_kernels.cuh"
+#include <cuda_runtime.h>
+
+#include "hb_dev.hpp"
 
 namespace {
 
@@ -100,7 +102,13 @@ namespace {
 
 using hb::kBlock;
 
-int tier_of(int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 48 ? 48 : 64; }
+int tier_of(int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 64 ? 64 : 256; }
+
+void need_device(const hb_handle* h) {
+    if (h->device < 0)
+        throw CudaError("handle was created with HB_DEVICE_NONE (host planning only); heat_b200 has no CPU fallback");
+    HB_CUDA(cudaSetDevice(h->device));
+}
 
 template <class F>
 hb_status guarded(F&& f) {
@@ -246,25 +254,32 @@ void build_device(hb_handle* h) {
     HB_CUDA(cudaStreamSynchronize(st));
 }
 
-template <int NMAX>
-void launch_tier(hb_handle* h, const hb_handle::Group& g, const hb::DevView& V, const hb::SeriesDev& P) {
-    if (g.dist)
-        hb::hb_march_kernel<NMAX, true><<<g.n_tiles, kBlock, 0, h->stream>>>(V, P, g.ids.p);
-    else
-        hb::hb_march_kernel<NMAX, false><<<g.n_tiles, kBlock, 0, h->stream>>>(V, P, g.ids.p);
-}
+}  // namespace
+
+namespace hb {
+// one translation unit per register tier (hb_march_tier.cu compiled with -DHB_TIER=N) so they build in parallel
+#define HB_DECL_TIER(N) \
+    void launch_march_##N(bool dist, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(24) HB_DECL_TIER(32) HB_DECL_TIER(64) HB_DECL_TIER(256)
+#undef HB_DECL_TIER
+void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
+void launch_dfma_probe(int blocks, int threads, double* out, int iters, double seed);
+void launch_fill(cudaStream_t st, double* p, int64_t n, double v);
+}  // namespace hb
+
+namespace {
 
 void launch_series(hb_handle* h, const hb::SeriesDev& P) {
     const hb::DevView V = h->view();
     for (auto& gp : h->groups) {
         const hb_handle::Group& g = *gp;
         switch (g.nmax_tier) {
-            case 8: launch_tier<8>(h, g, V, P); break;
-            case 16: launch_tier<16>(h, g, V, P); break;
-            case 24: launch_tier<24>(h, g, V, P); break;
-            case 32: launch_tier<32>(h, g, V, P); break;
-            case 48: launch_tier<48>(h, g, V, P); break;
-            default: launch_tier<64>(h, g, V, P); break;
+            case 8: hb::launch_march_8(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+            case 16: hb::launch_march_16(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+            case 24: hb::launch_march_24(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+            case 32: hb::launch_march_32(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+            case 64: hb::launch_march_64(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+            default: hb::launch_march_256(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
         }
         HB_CUDA(cudaGetLastError());
         h->launches += 1;
@@ -351,6 +366,12 @@ hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) 
     std::unique_ptr<hb_handle> h(new hb_handle());
     hb_status rc = guarded([&] {
         hb::plan_batch(desc, h->plan);
+        if (device == HB_DEVICE_NONE) {  // host-only planning handle: layout queries work, marching does not
+            h->device = HB_DEVICE_NONE;
+            return;
+        }
+        for (const auto& P : h->plan.plans)
+            if (P.n_nodes > hb::kMaxNodes) throw std::runtime_error("surface has more nodes than the supported maximum (256)");
         int count = 0;
         cudaError_t e = cudaGetDeviceCount(&count);
         if (e != cudaSuccess || count <= 0)
@@ -368,6 +389,10 @@ hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) 
 
 void hb_destroy(hb_handle* h) {
     if (!h) return;
+    if (h->device < 0) {
+        delete h;
+        return;
+    }
     cudaSetDevice(h->device);
     if (h->stream) {
         cudaStreamSynchronize(h->stream);
@@ -436,7 +461,7 @@ hb_status hb_get_surface_arrays(const hb_handle* h, int64_t s, int32_t* n_elemen
 // Scatter a reference-layout state vector into the SoA device buffers.
 hb_status hb_set_state(hb_handle* h, const double* state) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         const hb::BatchPlan& B = h->plan;
         const int64_t NS = B.n_dev_surfaces;
         std::vector<double> nodeT(B.node_slab_len, 0.), sc(8 * NS, 0.), zoneT(B.n_dev_zones, 0.);
@@ -478,7 +503,7 @@ static void gather_state(const hb::BatchPlan& B, const double* nodeT, const doub
 
 hb_status hb_get_state(hb_handle* h, double* state) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         const hb::BatchPlan& B = h->plan;
         std::vector<double> nodeT(B.node_slab_len), sc(8 * B.n_dev_surfaces), zoneT(B.n_dev_zones);
         HB_CUDA(cudaMemcpyAsync(nodeT.data(), h->nodeT.p, nodeT.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -493,7 +518,7 @@ hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const doubl
                              const double* infiltration_temperature, const double* ventilation_volume,
                              const double* ventilation_temperature) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         const hb::BatchPlan& B = h->plan;
         const int64_t NZ = B.n_dev_zones;
         auto scatter = [&](const double* src, double dflt, DevBuf<double>& dst) {
@@ -515,7 +540,7 @@ hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const doubl
 
 hb_status hb_march_series(hb_handle* h, const hb_series* s) {
     hb_status rc = guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         validate_series(h, s);
         if (s->n_steps == 0) return;
         update_sites(h, s);
@@ -591,7 +616,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
 
 hb_status hb_upload(hb_handle* h, const double* host, int64_t count, double** dev_out) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         double* p = nullptr;
         HB_CUDA(cudaMalloc(&p, (size_t)std::max<int64_t>(count, 1) * sizeof(double)));
         if (count) HB_CUDA(cudaMemcpyAsync(p, host, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -602,14 +627,14 @@ hb_status hb_upload(hb_handle* h, const double* host, int64_t count, double** de
 
 hb_status hb_free_dev(hb_handle* h, double* dev) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         if (dev) HB_CUDA(cudaFree(dev));
     });
 }
 
 hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_ms) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         validate_series(h, s);
         update_sites(h, s);
         hb::SeriesDev P{};
@@ -645,13 +670,13 @@ hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_m
 
 hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         const double init[8] = {0., INFINITY, -INFINITY, 0., INFINITY, -INFINITY, 0., 0.};
         HB_CUDA(cudaMemcpyAsync(h->red_out.p, init, sizeof(init), cudaMemcpyHostToDevice, h->stream));
         HB_CUDA(cudaMemsetAsync(h->red_iout.p, 0, 4 * sizeof(unsigned long long), h->stream));
         const int n_tiles = (int)h->plan.tiles.size();
         const int grid = std::min(n_tiles, 148 * 8);
-        hb::hb_reduce_kernel<<<grid, kBlock, 0, h->stream>>>(h->view(), n_tiles, h->red_out.p, h->red_iout.p);
+        hb::launch_reduce(grid, h->stream, h->view(), n_tiles, h->red_out.p, h->red_iout.p);
         HB_CUDA(cudaGetLastError());
         h->launches += 1;
         double o[8];
@@ -669,7 +694,7 @@ hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out) {
 
 hb_status hb_reset_energy(hb_handle* h) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         HB_CUDA(cudaMemsetAsync(h->energy_f.p, 0, h->energy_f.n * sizeof(double), h->stream));
         HB_CUDA(cudaMemsetAsync(h->energy_b.p, 0, h->energy_b.n * sizeof(double), h->stream));
         HB_CUDA(cudaMemsetAsync(h->nm_iters.p, 0, h->nm_iters.n * sizeof(unsigned long long), h->stream));
@@ -693,7 +718,7 @@ hb_status hb_measure_fp64_peak(int32_t device, double* tflops) {
         double best = 0.;
         for (int rep = 0; rep < 5; ++rep) {
             HB_CUDA(cudaEventRecord(e0));
-            hb::hb_dfma_probe_kernel<<<blocks, threads>>>(out, iters, 1.0 + rep);
+            hb::launch_dfma_probe(blocks, threads, out, iters, 1.0 + rep);
             HB_CUDA(cudaEventRecord(e1));
             HB_CUDA(cudaEventSynchronize(e1));
             float ms = 0.f;
@@ -710,10 +735,10 @@ hb_status hb_measure_fp64_peak(int32_t device, double* tflops) {
 
 hb_status hb_flush_l2(hb_handle* h, int64_t bytes) {
     return guarded([&] {
-        HB_CUDA(cudaSetDevice(h->device));
+        need_device(h);
         const size_t n = (size_t)bytes / sizeof(double);
         if (h->flush.n < n) h->flush.alloc(n);
-        hb::hb_fill_kernel<<<148 * 4, 256, 0, h->stream>>>(h->flush.p, (int64_t)n, 1.0);
+        hb::launch_fill(h->stream, h->flush.p, (int64_t)n, 1.0);
         HB_CUDA(cudaGetLastError());
         HB_CUDA(cudaStreamSynchronize(h->stream));
     });

@@ -317,7 +317,6 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B) {
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2)
                 if (P.nomass_chunks[c + 1] - P.nomass_chunks[c] > kMaxNomassChunk)
                     fail("no-mass chunk longer than the supported maximum");
-            if (P.n_nodes > kMaxNodes) fail("surface has more nodes than the supported maximum");
             tsub = std::max(tsub, P.tstep_subdivision);  // model.rs:261-263
             B.surface_state_offset[g] = state;
             B.surface_model[g] = m;
@@ -353,7 +352,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B) {
     B.tiles.clear();
     Tile cur{0, 0, 0, 0, 0, 0, 0};
     int64_t node_off = 0;
-    auto tier_of = [](int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 48 ? 48 : 64; };
+    auto tier_of = [](int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 64 ? 64 : 256; };
     auto close_tile = [&]() {
         if (cur.n_surfaces == 0 && cur.n_zones == 0) return;
         cur.node_offset = node_off;

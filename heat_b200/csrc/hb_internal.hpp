@@ -10,7 +10,7 @@ namespace hb {
 
 constexpr int kBlock = 128;          // threads per tile (= CUDA block); one thread per surface
 constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
-constexpr int kMaxNodes = 64;        // largest register/local tier
+constexpr int kMaxNodes = 256;       // largest tier (tiers > 32 keep node arrays in local memory)
 
 // Constants of the reference (kept in one place; cited where used)
 constexpr double kSigma = 5.670374419e-8;  // lib.rs:49

@@ -1,6 +1,6 @@
 // hb_kernels.cuh — hand-written CUDA (sm_100a) for the wall-conduction time-stepping path.
 //
-// K1/K2  hb_march_kernel<NMAX, DIST>: persistent over all main steps and sub-steps of a series.
+// K1/K2  hb_march_kernel<NMAX, DIST, LOCAL>: persistent over all main steps and sub-steps of a series.
 //        One CUDA block = one tile of independent models; one thread = one surface (wall, roof, window…),
 //        whose node temperatures stay in registers across sub-steps; the first n_zones threads also own the
 //        tile's zones (shared memory).  Per sub-step (reference call stack):
@@ -23,100 +23,30 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
-#include "hb_internal.hpp"
+#include "hb_dev.hpp"
 
 namespace hb {
-
-struct CavityDev {
-    int32_t node, gas;
-    double thickness, height, angle, eout, ein;
-};
-
-struct DevView {
-    // per device surface slot
-    const int32_t* n_nodes;
-    const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity
-    const int32_t* zone_f;    // tile-local zone index or -1
-    const int32_t* zone_b;
-    const int32_t* S;         // dt_subdivisions of the surface's model
-    const int32_t* site;
-    const int32_t* desc_index;  // descriptor-order surface index (for per-surface inputs)
-    const double* dt;
-    const double* area;
-    const double* nx;
-    const double* ny;
-    const double* cos_tilt;
-    const double* forced_c;   // 2.537·1.67·sqrt(perimeter·wind_modifier/area)  (convection.rs:157-163)
-    const double* eps_f;
-    const double* eps_b;
-    const double* amb_f;
-    const double* amb_b;
-    const double* hs_ov_f;
-    const double* hs_ov_b;
-    const int32_t* nm_off;    // CSR over no-mass chunks: pairs (ini, fin)
-    const int32_t* nm_pairs;
-    const int32_t* cav_off;   // CSR over cavity links
-    const CavityDev* cav;
-    // [node][kBlock] slabs per tile
-    double* nodeT;
-    const double* mass;
-    const double* u;
-    const double* alpha_f;
-    const double* alpha_b;
-    // state scalars [8][n_dev_surfaces]: h_f, h_b, flow_f, flow_b, solar_f, solar_b, ir_f, ir_b
-    double* sc;
-    int64_t n_dev_surfaces;
-    double* energy_f;
-    double* energy_b;
-    unsigned long long* nm_iters;
-    int32_t* status;
-    // zones
-    double* zoneT;
-    const double* zvol;
-    const double* zq;
-    const double* zinf_v;
-    const double* zinf_t;
-    const double* zvent_v;
-    const double* zvent_t;
-    const double* zdt;
-    const int32_t* zS;
-    const int32_t* z_surf_begin;  // tile-local thread range of the zone's model
-    const int32_t* z_surf_end;
-    int64_t n_dev_zones;
-    const Tile* tiles;
-};
-
-struct SeriesDev {
-    int32_t n_steps;
-    int32_t weather_mode;
-    int32_t input_mode;
-    int32_t ir_mode;
-    const double* weather;   // [site][rows][3]
-    int64_t weather_rows;
-    const double* inputs;
-    int64_t n_desc_surfaces;
-    int32_t record_every;
-    double* zone_rec;        // [rec][n_dev_zones]
-    double* node_rec;        // [rec][slab_len]
-    double* sc_rec;          // [rec][8][n_dev_surfaces]
-    int64_t slab_len;
-};
-
-enum { ST_NAN_H = 1, ST_NAN_ERR = 2, ST_NAN_ZONE = 4, ST_ITER_CAP = 8, ST_BAD_GAMMA = 16 };
 
 // ----------------------------------------------------------------------------------------------------
 // small device helpers
 // ----------------------------------------------------------------------------------------------------
-template <int NMAX>
+// Register-resident arrays may only be indexed with compile-time constants: dynamic reads/writes go through a
+// fully unrolled select chain.  LOCAL tiers (large walls) keep their arrays in local memory and index directly.
+template <int NMAX, bool LOCAL>
 __device__ __forceinline__ double reg_get(const double (&A)[NMAX], int idx) {
+    if constexpr (LOCAL) return A[idx];
     double v = 0.0;
 #pragma unroll
     for (int i = 0; i < NMAX; ++i)
         if (i == idx) v = A[i];
     return v;
 }
-template <int NMAX>
+template <int NMAX, bool LOCAL>
 __device__ __forceinline__ void reg_set(double (&A)[NMAX], int idx, double v) {
+    if constexpr (LOCAL) {
+        A[idx] = v;
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < NMAX; ++i)
         if (i == idx) A[i] = v;
@@ -152,7 +82,7 @@ __device__ __forceinline__ GasDev gas_of(int id) {
 }
 
 // gas.rs:285-309
-__device__ double nu_90(double ra, double a_gi) {
+static __device__ double nu_90(double ra, double a_gi) {
     double nu1;
     if (ra <= 1e4)
         nu1 = 1. + 1.7596678 * 1e-10 * pow(ra, 2.2984755);
@@ -164,7 +94,7 @@ __device__ double nu_90(double ra, double a_gi) {
     return nu1 > nu2 ? nu1 : nu2;
 }
 // gas.rs:249-264
-__device__ double nu_60(double ra, double a_gi) {
+static __device__ double nu_60(double ra, double a_gi) {
     const double g = 0.5 / pow(1. + pow(ra / 3160., 20.6), 0.1);
     const double base = 0.0936 * pow(ra, 0.314) / (1. + g);
     const double b2 = base * base, b4 = b2 * b2;
@@ -173,7 +103,7 @@ __device__ double nu_60(double ra, double a_gi) {
     return nu1 > nu2 ? nu1 : nu2;
 }
 // gas.rs:197-315
-__device__ double nusselt(double ra, double gamma_in, double a_gi, int& status) {
+static __device__ double nusselt(double ra, double gamma_in, double a_gi, int& status) {
     const double PI = 3.14159265358979323846;
     const double THIRTY = 30. * PI / 180.;
     const double EPS = 0.5 * PI / 180.;
@@ -200,7 +130,7 @@ __device__ double nusselt(double ra, double gamma_in, double a_gi, int& status) 
     return CUDART_NAN;
 }
 // cavity.rs:59-69 + gas.rs:82-152
-__device__ double cavity_u(const CavityDev& c, double t_front, double t_back, int& status) {
+static __device__ double cavity_u(const CavityDev& c, double t_front, double t_back, int& status) {
     const double PI = 3.14159265358979323846;
     const GasDev g = gas_of(c.gas);
     double gamma = c.angle;
@@ -234,7 +164,7 @@ struct Face {
 // ----------------------------------------------------------------------------------------------------
 // K1/K2
 // ----------------------------------------------------------------------------------------------------
-template <int NMAX, bool DIST>
+template <int NMAX, bool DIST, bool LOCAL>
 __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     const double PI = 3.14159265358979323846;
     const Tile tile = V.tiles[tile_ids[blockIdx.x]];
@@ -278,8 +208,8 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
     double T[NMAX], A[NMAX], B[NMAX];
     double af0 = 0., abL = 0.;      // solar absorptance of the two end nodes
     double v0 = 0., vL = 0.;        // dt/C of the two end nodes (0 when no-mass)
-#pragma unroll
-    for (int i = 0; i < NMAX; ++i) {
+#pragma unroll(LOCAL ? 1 : NMAX)
+    for (int i = 0; i < (LOCAL ? n : NMAX); ++i) {
         T[i] = 0.;
         A[i] = 0.;
         B[i] = 0.;
@@ -396,7 +326,7 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
 
                 // ---- border conditions with the OLD surface temperatures (surface.rs:939-948) ----
                 const double ts_f_old = T[0];
-                const double ts_b_old = reg_get<NMAX>(T, n - 1);
+                const double ts_b_old = reg_get<NMAX, LOCAL>(T, n - 1);
                 Face F, Bk;
                 auto border = [&](double ts_f, double ts_b) {
                     if (kind_f == HB_BOUNDARY_OUTDOOR) {
@@ -438,7 +368,7 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                     int cavl[kMaxNomassChunk + 1];
                     for (int j = 0; j < m + 2; ++j) {
                         const int node = ini - 1 + j;
-                        tl[j] = (node >= 0 && node < n) ? reg_get<NMAX>(T, node) : 0.;
+                        tl[j] = (node >= 0 && node < n) ? reg_get<NMAX, LOCAL>(T, node) : 0.;
                     }
                     for (int j = 0; j < m + 1; ++j) {
                         const int link = ini - 1 + j;
@@ -519,7 +449,7 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                         ++count;
                         if (count > 100000) { status |= ST_ITER_CAP; break; }
                     }
-                    for (int j = 0; j < m; ++j) reg_set<NMAX>(T, ini + j, tl[j + 1]);
+                    for (int j = 0; j < m; ++j) reg_set<NMAX, LOCAL>(T, ini + j, tl[j + 1]);
                 }
 
                 // ---- cavity links between massive nodes: conductance at the assembly temperatures ----
@@ -527,10 +457,10 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                     for (int q = cav_begin; q < cav_end; ++q) {
                         const CavityDev cv = V.cav[q];
                         const int i = cv.node;
-                        const double uu = cavity_u(cv, reg_get<NMAX>(T, i), reg_get<NMAX>(T, i + 1), status);
+                        const double uu = cavity_u(cv, reg_get<NMAX, LOCAL>(T, i), reg_get<NMAX, LOCAL>(T, i + 1), status);
                         const double mi = slab_mass[(int64_t)i * kBlock], mj = slab_mass[(int64_t)(i + 1) * kBlock];
-                        reg_set<NMAX>(A, i, uu * (mi >= kMassiveThreshold ? dt / mi : 0.));
-                        reg_set<NMAX>(B, i + 1, uu * (mj >= kMassiveThreshold ? dt / mj : 0.));
+                        reg_set<NMAX, LOCAL>(A, i, uu * (mi >= kMassiveThreshold ? dt / mi : 0.));
+                        reg_set<NMAX, LOCAL>(B, i + 1, uu * (mj >= kMassiveThreshold ? dt / mj : 0.));
                     }
                 }
 
@@ -538,7 +468,7 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                 {
                     // film coefficients as links to virtual nodes at the equivalent air temperature
                     const double t0_asm = T[0];
-                    const double tL_asm = reg_get<NMAX>(T, n - 1);
+                    const double tL_asm = reg_get<NMAX, LOCAL>(T, n - 1);
                     const double hf_s = hf > 1e-300 ? hf : 1e-300, hb_s = hb_ > 1e-300 ? hb_ : 1e-300;
                     const double xf = F.air + (rad_f * (F.trad - t0_asm) + q_sol0) / hf_s;
                     const double xb = Bk.air + (rad_b * (Bk.trad - tL_asm) + q_solL) / hb_s;
@@ -546,8 +476,8 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                     const double aL = hb_s * vL;
                     double X[NMAX], ACC[NMAX];
                     double Q[DIST ? NMAX : 1];
-#pragma unroll
-                    for (int i = 0; i < NMAX; ++i) {
+#pragma unroll(LOCAL ? 1 : NMAX)
+                    for (int i = 0; i < (LOCAL ? n : NMAX); ++i) {
                         X[i] = T[i];
                         ACC[i] = T[i];
                         if constexpr (DIST) {
@@ -569,8 +499,8 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                     }
                     auto stage = [&](const double cx, const double w, const bool last) {
                         double dleft = X[0] - xf;
-#pragma unroll
-                        for (int i = 0; i < NMAX; ++i) {
+#pragma unroll(LOCAL ? 1 : NMAX)
+                        for (int i = 0; i < (LOCAL ? n : NMAX); ++i) {
                             if (i < n) {
                                 const bool end = i + 1 >= n;
                                 const double xr = end ? xb : X[i + 1 < NMAX ? i + 1 : i];
@@ -589,13 +519,13 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
                     stage(0.5, 1. / 3., false);
                     stage(1.0, 1. / 3., false);
                     stage(0.0, 1. / 6., true);
-#pragma unroll
-                    for (int i = 0; i < NMAX; ++i) T[i] = ACC[i];
+#pragma unroll(LOCAL ? 1 : NMAX)
+                    for (int i = 0; i < (LOCAL ? n : NMAX); ++i) T[i] = ACC[i];
                 }
 
                 // ---- new film coefficients and convective flows (model.rs:145-169) ----
                 const double ts_f = T[0];
-                const double ts_b = reg_get<NMAX>(T, n - 1);
+                const double ts_b = reg_get<NMAX, LOCAL>(T, n - 1);
                 border(ts_f, ts_b);
                 h_f = F.h;
                 h_b = Bk.h;
@@ -646,8 +576,8 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
         if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
             if (P.zone_rec && zthread) P.zone_rec[(int64_t)rec * V.n_dev_zones + gz] = s_zT[t];
             if (P.node_rec && surf) {
-#pragma unroll
-                for (int i = 0; i < NMAX; ++i)
+#pragma unroll(LOCAL ? 1 : NMAX)
+                for (int i = 0; i < (LOCAL ? n : NMAX); ++i)
                     if (i < n) P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * kBlock + t] = T[i];
                 double* r = P.sc_rec + (int64_t)rec * 8 * NS;
                 r[0 * NS + g] = h_f; r[1 * NS + g] = h_b; r[2 * NS + g] = flow_f; r[3 * NS + g] = flow_b;
@@ -659,8 +589,8 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
 
     // ---- write the state back ----
     if (surf) {
-#pragma unroll
-        for (int i = 0; i < NMAX; ++i)
+#pragma unroll(LOCAL ? 1 : NMAX)
+        for (int i = 0; i < (LOCAL ? n : NMAX); ++i)
             if (i < n) slab_T[(int64_t)i * kBlock] = T[i];
         V.sc[0 * NS + g] = h_f; V.sc[1 * NS + g] = h_b; V.sc[2 * NS + g] = flow_f; V.sc[3 * NS + g] = flow_b;
         V.sc[4 * NS + g] = sol_f; V.sc[5 * NS + g] = sol_b; V.sc[6 * NS + g] = ir_f; V.sc[7 * NS + g] = ir_b;
@@ -672,6 +602,7 @@ __global__ void __launch_bounds__(kBlock) hb_march_kernel(DevView V, SeriesDev P
     if (zthread) V.zoneT[gz] = s_zT[t];
 }
 
+#ifdef HB_AUX_KERNELS
 // ----------------------------------------------------------------------------------------------------
 // K3: ensemble reduction. out[0..8): Σzone, min zone, max zone, Σnode, min node, max node, E_f, E_b;
 // iout[0..4): n_zones, n_nodes, no-mass iterations, status OR.
@@ -775,5 +706,7 @@ __global__ void hb_dfma_probe_kernel(double* out, int iters, double seed) {
 __global__ void hb_fill_kernel(double* p, int64_t n, double v) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
+
+#endif  // HB_AUX_KERNELS
 
 }  // namespace hb

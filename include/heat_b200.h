@@ -108,7 +108,10 @@ typedef struct hb_handle hb_handle;
 const char* hb_last_error(void);
 const char* hb_version(void);
 
-/* ThermalModel::new for every model of the batch, on CUDA device `device`. */
+/* ThermalModel::new for every model of the batch, on CUDA device `device`.
+ * device == HB_DEVICE_NONE builds a host-only planning handle: the discretization/layout queries below work,
+ * every entry point that touches the device returns HB_ERR_CUDA (there is no CPU fallback). */
+#define HB_DEVICE_NONE (-1)
 hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out);
 void hb_destroy(hb_handle* h);
 

@@ -1,0 +1,120 @@
+"""Host side of ThermalModel::new (product code in heat_b200/csrc/hb_host.cc) against the oracle:
+0 mismatches allowed in tstep_subdivision, n_elements, node counts, chunk ranges and state offsets
+(BASELINE.json north_star); masses / conductances / alphas bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_py as O
+from heat_b200 import _lib, cases, desc as D
+from heat_b200.model import ThermalBatch
+
+HB_DEVICE_NONE = -1
+
+
+def plan(desc):
+    return ThermalBatch(desc, device=HB_DEVICE_NONE)
+
+
+def compare_model(b, d, m, surface_base):
+    om = O.OracleModel(d, m)
+    info = b.model_info(m)
+    assert info.dt_subdivisions == om.dt_subdivisions
+    assert info.dt == om.dt
+    assert info.state_len == om.state_len
+    for s in range(om.n_surfaces):
+        g = surface_base + s
+        mine = b.surface_arrays(g)
+        c0 = d.construction_offset[d.surfaces[g]["construction"]]
+        c1 = d.construction_offset[d.surfaces[g]["construction"] + 1]
+        ref = om.surface_arrays(s, c1 - c0)
+        assert mine["tstep_subdivision"] == ref["tstep_subdivision"]
+        assert mine["n_nodes"] == ref["n_nodes"]
+        assert np.array_equal(mine["n_elements"], ref["n_elements"])
+        assert np.array_equal(mine["massive_chunks"], ref["massive_chunks"])
+        assert np.array_equal(mine["nomass_chunks"], ref["nomass_chunks"])
+        assert np.array_equal(mine["mass"], ref["mass"])
+        assert np.array_equal(mine["u"], ref["u"])
+        assert np.array_equal(mine["front_alpha"], ref["front_alpha"])
+        assert np.array_equal(mine["back_alpha"], ref["back_alpha"])
+        si = b.surface_info(g)
+        assert si.state_offset - info.state_offset == om.state_offset(s)
+        assert si.wind_speed_modifier == ref["wind_speed_modifier"]
+        assert si.front_emissivity == ref["front_emissivity"] and si.back_emissivity == ref["back_emissivity"]
+    return om.n_surfaces
+
+
+@pytest.mark.parametrize("name", ["massive_full", "mixed_full", "nomass_full", "trombe_wall_full", "tilted",
+                                  "horizontal", "massive_no_ir_no_solar"])
+@pytest.mark.parametrize("n", [1, 2, 4, 6, 20, 60])
+def test_validation_cases(name, n):
+    d = cases.validation_case(name, n)
+    compare_model(plan(d), d, 0, 0)
+
+
+def test_reference_sizes_table():
+    """BASELINE.md §2 table (rule at discretization.rs:410-544, model.rs:236-240,326-331)."""
+    expect = {("massive_full", 20): (2, 90.0, [12], 13), ("nomass_full", 20): (4, 45.0, [0], 2),
+              ("mixed_full", 20): (4, 45.0, [0, 18, 0], 21), ("massive_full", 1): (10, 360.0, [5], 6),
+              ("mixed_full", 1): (118, 3600.0 / 118, [0, 22, 0], 25)}
+    for (name, n), (S, dt, el, N) in expect.items():
+        b = plan(cases.validation_case(name, n))
+        info = b.model_info(0)
+        a = b.surface_arrays(0)
+        assert info.dt_subdivisions == S and abs(info.dt - dt) < 1e-12
+        assert a["n_elements"].tolist() == el and a["n_nodes"] == N
+
+
+def test_random_wall_ensemble_zero_mismatches():
+    d = cases.wall_ensemble(1500, seed=123, mixed_fraction=0.4)
+    b = plan(d)
+    for m in range(d.n_models):
+        compare_model(b, d, m, m)
+    assert b.updates_per_step == sum(b.model_info(m).nodes * b.model_info(m).dt_subdivisions for m in range(d.n_models))
+
+
+def test_shoebox_ensemble_zero_mismatches():
+    d, _ = cases.shoebox_ensemble(60, seed=77, steps_per_hour=2)
+    b = plan(d)
+    for m in range(d.n_models):
+        assert compare_model(b, d, m, 7 * m) == 7
+
+
+def test_glazing_stack_alphas():
+    """glass | argon | glass fenestration: ISO 9050 absorptances distributed over the panes' nodes."""
+    g1 = cases.glass(0.006, 0.7, 0.84, 0.1)
+    g2 = cases.glass(0.004, 0.8, 0.84, 0.05)
+    s = D.surface(0, 2.0, 6.0, (0, -1, 0), 1.0, front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0),
+                  is_fenestration=True)
+    d = D.single_model([[g1, D.gas_layer(0.012, D.GAS_ARGON), g2]], [30.0], [s], 4)
+    compare_model(plan(d), d, 0, 0)
+
+
+def test_errors_mirror_reference():
+    lay = cases.concrete(0.2)
+    gas = D.gas_layer(0.05)
+    s = D.surface(0, 1.0, 4.0, (0, -1, 0), 1.0)
+    for layers, msg in (([gas, lay], "first layer"), ([lay, gas], "last layer"), ([lay, gas, gas, lay], "two gases")):
+        with pytest.raises(Exception) as e:
+            plan(D.single_model([layers], [10.0], [s], 4))
+        assert msg in str(e.value)
+    ground = D.surface(0, 1.0, 4.0, (0, -1, 0), 1.0, front=(D.BOUNDARY_GROUND, 0))
+    with pytest.raises(Exception) as e:
+        plan(D.single_model([[lay]], [10.0], [ground], 4))
+    assert e.value.status == 4  # HB_ERR_UNSUPPORTED (reference: unimplemented!(), model.rs:92)
+    bad_zone = D.surface(0, 1.0, 4.0, (0, -1, 0), 1.0, back=(D.BOUNDARY_SPACE, 3))
+    with pytest.raises(Exception) as e:
+        plan(D.single_model([[lay]], [10.0], [bad_zone], 4))
+    assert "Space not found" in str(e.value)
+
+
+def test_no_cpu_fallback():
+    """A planning handle cannot march; there is no CPU path behind the C ABI."""
+    from heat_b200 import HeatB200Error
+    b = plan(cases.validation_case("massive_full"))
+    with pytest.raises(HeatB200Error) as e:
+        b.march_series(1, np.array([[20.0, 0.0, 1.0]]))
+    assert e.value.status == 2  # HB_ERR_CUDA
+    with pytest.raises(HeatB200Error):
+        b.get_state()

@@ -1,0 +1,171 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle and the committed golden vectors.
+
+Tolerance (BASELINE.json north_star): node and zone temperatures within 1e-6 °C absolute at every main step.
+"""
+import numpy as np
+import pytest
+
+import parity_cases as pc
+
+TOL = 1e-6
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", pc.GOLDEN_CASES)
+def test_series_against_golden(name):
+    """Whole series (21 days × 20/h E+ cases, full-year hourly EPW cases, theoretical cases) vs committed oracle output."""
+    zone_g, final_g = pc.golden(name)
+    zone, final = pc.run_gpu(name)
+    assert zone.shape == zone_g.shape
+    assert np.all(np.isfinite(final))
+    dz = np.abs(zone - zone_g).max()
+    df = np.abs(final - final_g).max()
+    assert dz <= TOL, f"{name}: zone temperature differs by {dz:.3e}"
+    # final state holds node T, zone T, film coefficients and flows; irradiance slots are inputs
+    assert df <= 1e-5, f"{name}: final state differs by {df:.3e}"
+
+
+@pytest.mark.parametrize("name", ["eplus/massive_full", "eplus/mixed_full", "eplus/nomass_full", "eplus/tilted",
+                                  "eplus/trombe_wall_full", "epw/massive_full", "epw/mixed_full"])
+def test_every_node_every_step_against_live_oracle(name):
+    """All node temperatures at every main step against the oracle run live on the same arrays."""
+    steps = 2000
+    zone_o, final_o, states_o, m = pc.run_oracle(name, steps, record_state=True)
+    zone, final, states, b = pc.run_gpu(name, steps, record_state=True)
+    assert states.shape == states_o.shape
+    n_z = m.n_zones
+    off = m.state_offset(0)
+    nodes = slice(off + 8, off + 8 + m.n_nodes(0))
+    d_nodes = np.abs(states[:, nodes] - states_o[:, nodes]).max()
+    d_zone = np.abs(states[:, :n_z] - states_o[:, :n_z]).max()
+    assert d_nodes <= TOL and d_zone <= TOL, (d_nodes, d_zone)
+    # film coefficients and flows: relative
+    d_h = np.abs(states[:, off:off + 4] - states_o[:, off:off + 4]).max()
+    assert d_h <= 1e-5, d_h
+    # branch parity of the no-mass fixed point: identical iteration counts
+    assert b.reduce().nomass_iterations == m.nomass_iterations
+
+
+def test_drop_in_march_matches_series_and_oracle():
+    """ThermalModel.new/march (one call per main step, caller-owned state) == series launch == oracle."""
+    from heat_b200 import model as M
+    from heat_b200 import cases
+    import oracle_py as O
+
+    c = pc.make_case("eplus/mixed_full", 50)
+    header = M.SimulationStateHeader()
+    tm = M.ThermalModel.new(None, (), c.desc, header, 20)
+    mem = tm.allocate_memory()
+    state = header.take_values()
+    om = O.OracleModel(c.desc)
+    so = om.initial_state()
+    assert np.array_equal(state, so)
+    assert tm.dt_subdivisions == om.dt_subdivisions and tm.dt == om.dt
+    state[tm.zone_index(0)] = so[0] = c.zone_t0
+    date = M.Date(1, 1, 0.0)
+    sigma = 5.670374419e-8
+    for i in range(c.n_steps):
+        w = M.ConstantWeather(*[c.weather[i, k] for k in (0, 1, 2)])
+        for st in (state, so):
+            st[tm.surface_slot(0, 4)] = c.inputs[i, 0]
+            ts = st[tm.node_index(0, 0)]
+            st[tm.surface_slot(0, 6)] = c.inputs[i, 2] / 60.0 / 0.9 + sigma * (ts + 273.15) ** 4
+        tm.march(date, w, c.desc, state, mem)
+        om.march(so, np.tile(c.weather[i], (om.dt_subdivisions, 1)))
+        date.add_hours(1.0 / 20)
+    off = om.state_offset(0)
+    assert np.abs(state[off + 8:] - so[off + 8:]).max() <= TOL
+    assert abs(state[0] - so[0]) <= TOL
+
+
+def test_batch_of_heterogeneous_models_matches_per_model_oracle():
+    """A batch mixing constructions / sub-step counts / tiers: every model equals its own oracle run."""
+    import oracle_py as O
+    from heat_b200 import cases
+    from heat_b200.model import ThermalBatch
+    from heat_b200 import _lib
+
+    d = cases.wall_ensemble(300, seed=5, mixed_fraction=0.5, steps_per_hour=1)
+    weather, inputs = cases.synthetic_weather(49)
+    n_steps = 48
+    b = ThermalBatch(d)
+    b.march_series(n_steps, weather, weather_mode=_lib.WEATHER_LINEAR, inputs=inputs[:n_steps],
+                   input_mode=_lib.INPUT_SITE)
+    got = b.get_state()
+    worst = 0.0
+    for m in range(0, d.n_models, 7):
+        om = O.OracleModel(d, m)
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        info = b.model_info(m)
+        mine = got[info.state_offset:info.state_offset + info.state_len]
+        off = om.state_offset(0)
+        worst = max(worst, np.abs(mine[off + 8:] - so[off + 8:]).max(), abs(mine[0] - so[0]))
+    assert worst <= TOL, worst
+
+
+def test_shoebox_buildings_match_oracle():
+    """6 surfaces + window per zone: zone a/b/c sums over the building's surfaces."""
+    import oracle_py as O
+    from heat_b200 import cases
+    from heat_b200.model import ThermalBatch
+    from heat_b200 import _lib
+
+    d, gains = cases.shoebox_ensemble(40, seed=9, steps_per_hour=2)
+    weather, inputs = cases.synthetic_weather(25)
+    n_steps = 24
+    b = ThermalBatch(d)
+    b.set_zone_inputs(q_internal=gains)
+    b.march_series(n_steps, weather, weather_mode=_lib.WEATHER_LINEAR, inputs=inputs[:n_steps],
+                   input_mode=_lib.INPUT_SITE)
+    got = b.get_state()
+    worst = 0.0
+    for m in range(0, d.n_models, 3):
+        om = O.OracleModel(d, m)
+        om.set_zone_inputs(q_internal=gains[m:m + 1])
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        info = b.model_info(m)
+        mine = got[info.state_offset:info.state_offset + info.state_len]
+        for s in range(om.n_surfaces):
+            off = om.state_offset(s)
+            n = om.n_nodes(s)
+            worst = max(worst, np.abs(mine[off + 8:off + 8 + n] - so[off + 8:off + 8 + n]).max())
+        worst = max(worst, abs(mine[0] - so[0]))
+    assert worst <= TOL, worst
+
+
+def test_reduce_matches_state():
+    from heat_b200 import cases
+    from heat_b200.model import ThermalBatch
+
+    d = cases.wall_ensemble(500, seed=11, mixed_fraction=0.3)
+    weather, inputs = cases.synthetic_weather(13)
+    b = ThermalBatch(d)
+    b.march_series(12, weather, weather_mode=1, inputs=inputs[:12], input_mode=1)
+    st = b.reduce()
+    state = b.get_state()
+    zone_t, node_t = [], []
+    for m in range(d.n_models):
+        info = b.model_info(m)
+        s = state[info.state_offset:info.state_offset + info.state_len]
+        zone_t.append(s[0])
+        node_t.append(s[1 + 8:])
+    node_t = np.concatenate(node_t)
+    assert st.n_zones == d.n_models and st.n_nodes == node_t.size == b.nodes
+    assert abs(st.sum_zone_t - np.sum(zone_t)) <= 1e-9 * abs(np.sum(zone_t))
+    assert abs(st.sum_node_t - node_t.sum()) <= 1e-9 * abs(node_t.sum())
+    assert st.min_node_t == node_t.min() and st.max_node_t == node_t.max()
+    assert st.status_flags == 0
+
+
+def test_physics_failure_is_reported_not_hidden():
+    """NaN inputs: the reference panics (surface.rs:704-707); the C ABI returns HB_ERR_PHYSICS."""
+    from heat_b200 import cases, HeatB200Error
+    from heat_b200.model import ThermalBatch
+
+    b = ThermalBatch(cases.validation_case("massive_full"))
+    with pytest.raises(HeatB200Error) as e:
+        b.march_series(1, np.array([[float("nan"), 0.0, 1.0]]))
+    assert e.value.status == 3
