@@ -215,6 +215,11 @@ def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layer
     surfaces["normal"][:, 1] = np.cos(azimuth)
     for f in ("front_hs_override", "back_hs_override", "front_emissivity_override", "back_emissivity_override"):
         surfaces[f] = D.NAN
+    # Mixed walls end in a no-mass node facing the zone.  The reference's damped fixed point for such a node
+    # (surface.rs:790-898) is not contractive once 4εσT³ > 3(u + h): its result is then chaotic at the 0.1 °C level
+    # (tests/test_reference_sensitivity.py).  The reference's own validation driver sets the
+    # zone-facing emissivity to 0 (validate_wall_heat_transfer.rs:630); the ensembles do the same for mixed walls.
+    surfaces["back_emissivity_override"][is_mixed] = 0.0
     ar = np.arange(n_walls + 1, dtype=np.int32)
     return D.BatchDesc(layers, off.astype(np.int32), ar, ar, volume, surfaces, steps_per_hour)
 

@@ -4,7 +4,7 @@
 
 namespace hb {
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout) {
-    hb_reduce_kernel<<<grid, kBlock, 0, st>>>(V, n_tiles, out, iout);
+    hb_reduce_kernel<<<grid, kReduceBlock, 0, st>>>(V, n_tiles, out, iout);
 }
 void launch_dfma_probe(int blocks, int threads, double* out, int iters, double seed) {
     hb_dfma_probe_kernel<<<blocks, threads>>>(out, iters, seed);

@@ -1,4 +1,5 @@
 // hb_capi.cu — the C ABI declared in include/heat_b200.h: handle, device buffers, launches.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -56,42 +57,47 @@ struct hb_handle {
     hb::BatchPlan plan;
     int64_t launches = 0;
 
-    // device buffers
-    DevBuf<int32_t> n_nodes, flags, zone_f, zone_b, S, site, desc_index, nm_off, nm_pairs, cav_off;
+    // device buffers (uploaded verbatim from hb::HostArrays)
+    DevBuf<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     DevBuf<hb::CavityDev> cav;
-    DevBuf<double> dt, area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b;
-    DevBuf<double> nodeT, mass, u, alpha_f, alpha_b, sc, energy_f, energy_b;
+    DevBuf<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL;
+    DevBuf<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     DevBuf<unsigned long long> nm_iters;
     DevBuf<int32_t> status;
-    DevBuf<double> zoneT, zvol, zq, zinf_v, zinf_t, zvent_v, zvent_t, zdt;
-    DevBuf<int32_t> zS, z_surf_begin, z_surf_end;
+    DevBuf<double> zoneT, zvol, zq, zinf_v, zinf_t, zvent_v, zvent_t;
+    DevBuf<int32_t> z_surf_begin, z_surf_end;
     DevBuf<hb::Tile> tiles;
     DevBuf<double> red_out;
     DevBuf<unsigned long long> red_iout;
     DevBuf<double> flush;
 
+    // one launch per (lanes-per-wall, kernel variant); each on its own stream so that small groups overlap
     struct Group {
-        int nmax_tier;
-        bool dist;
+        int G, var;
         int n_tiles;
-        DevBuf<int32_t> ids;
+        DevBuf<int32_t> ids;   // tile ids, heaviest first
+        cudaStream_t stream = nullptr;
+        cudaEvent_t done = nullptr;
     };
     std::vector<std::unique_ptr<Group>> groups;
+    cudaEvent_t fork = nullptr;
     std::vector<int32_t> host_site;  // per device surface slot (rebuilt when model_site changes)
     std::vector<int32_t> model_site_cache;
+    bool single_site = true;
 
     hb::DevView view() {
         hb::DevView V{};
-        V.n_nodes = n_nodes.p; V.flags = flags.p; V.zone_f = zone_f.p; V.zone_b = zone_b.p; V.S = S.p;
-        V.site = site.p; V.desc_index = desc_index.p; V.dt = dt.p; V.area = area.p; V.nx = nx.p; V.ny = ny.p;
-        V.cos_tilt = cos_tilt.p; V.forced_c = forced_c.p; V.eps_f = eps_f.p; V.eps_b = eps_b.p;
-        V.amb_f = amb_f.p; V.amb_b = amb_b.p; V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p;
+        V.n_nodes = n_nodes.p; V.flags = flags.p; V.zone_f = zone_f.p; V.zone_b = zone_b.p; V.site = site.p;
+        V.desc_index = desc_index.p; V.area = area.p; V.nx = nx.p; V.ny = ny.p; V.cos_tilt = cos_tilt.p;
+        V.forced_c = forced_c.p; V.eps_f = eps_f.p; V.eps_b = eps_b.p; V.amb_f = amb_f.p; V.amb_b = amb_b.p;
+        V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p; V.af0 = af0.p; V.abL = abL.p; V.v0 = v0.p; V.vL = vL.p;
         V.nm_off = nm_off.p; V.nm_pairs = nm_pairs.p; V.cav_off = cav_off.p; V.cav = cav.p;
-        V.nodeT = nodeT.p; V.mass = mass.p; V.u = u.p; V.alpha_f = alpha_f.p; V.alpha_b = alpha_b.p;
+        V.nodeT = nodeT.p; V.coefA = coefA.p; V.coefB = coefB.p;
+        V.ext_u = ext_u.p; V.ext_mass = ext_mass.p; V.ext_af = ext_af.p; V.ext_ab = ext_ab.p;
         V.sc = sc.p; V.n_dev_surfaces = plan.n_dev_surfaces; V.energy_f = energy_f.p; V.energy_b = energy_b.p;
         V.nm_iters = nm_iters.p; V.status = status.p;
         V.zoneT = zoneT.p; V.zvol = zvol.p; V.zq = zq.p; V.zinf_v = zinf_v.p; V.zinf_t = zinf_t.p;
-        V.zvent_v = zvent_v.p; V.zvent_t = zvent_t.p; V.zdt = zdt.p; V.zS = zS.p;
+        V.zvent_v = zvent_v.p; V.zvent_t = zvent_t.p;
         V.z_surf_begin = z_surf_begin.p; V.z_surf_end = z_surf_end.p; V.n_dev_zones = plan.n_dev_zones;
         V.tiles = tiles.p;
         return V;
@@ -100,9 +106,6 @@ struct hb_handle {
 
 namespace {
 
-using hb::kBlock;
-
-int tier_of(int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 64 ? 64 : 256; }
 
 void need_device(const hb_handle* h) {
     if (h->device < 0)
@@ -127,128 +130,49 @@ hb_status guarded(F&& f) {
 
 void build_device(hb_handle* h) {
     const hb::BatchPlan& B = h->plan;
-    const int64_t NS = B.n_dev_surfaces, NZ = B.n_dev_zones;
-    std::vector<int32_t> n_nodes(NS, 0), flags(NS, 0), zone_f(NS, -1), zone_b(NS, -1), S(NS, 0), site(NS, 0),
-        desc_index(NS, 0), nm_off(NS + 1, 0), cav_off(NS + 1, 0), nm_pairs;
-    std::vector<hb::CavityDev> cav;
-    std::vector<double> dt(NS, 0.), area(NS, 0.), nx(NS, 0.), ny(NS, 0.), cos_tilt(NS, 0.), forced_c(NS, 0.),
-        eps_f(NS, 0.), eps_b(NS, 0.), amb_f(NS, 0.), amb_b(NS, 0.), ov_f(NS, NAN), ov_b(NS, NAN);
-    std::vector<double> nodeT(B.node_slab_len, 0.), mass(B.node_slab_len, 0.), u(B.node_slab_len, 0.),
-        alpha_f(B.node_slab_len, 0.), alpha_b(B.node_slab_len, 0.), sc(8 * NS, 0.);
-    std::vector<double> zoneT(NZ, 0.), zvol(NZ, 0.), zq(NZ, 0.), zinf_v(NZ, 0.), zinf_t(NZ, NAN), zvent_v(NZ, 0.),
-        zvent_t(NZ, NAN), zdt(NZ, 0.);
-    std::vector<int32_t> zS(NZ, 0), zsb(NZ, 0), zse(NZ, 0);
-
-    // inverse map device slot → descriptor surface
-    std::vector<int64_t> desc_of(NS, -1);
-    for (size_t gdesc = 0; gdesc < B.dev_surface_of.size(); ++gdesc) desc_of[B.dev_surface_of[gdesc]] = (int64_t)gdesc;
-
-    std::vector<int> tile_dist(B.tiles.size(), 0);
-    for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
-        const hb::Tile& tile = B.tiles[ti];
-        for (int t = 0; t < tile.n_surfaces; ++t) {
-            const int64_t g = (int64_t)tile.surface_begin + t;
-            const int64_t gd = desc_of[g];
-            const hb_surface& s = B.surfaces[gd];
-            const hb::SurfacePlan& P = B.plans[gd];
-            const hb::ModelPlan& M = B.models[B.surface_model[gd]];
-            n_nodes[g] = P.n_nodes;
-            flags[g] = (s.front_kind & 15) | ((s.back_kind & 15) << 4) | ((P.distributed_solar ? 1 : 0) << 8) |
-                       ((P.cavities.empty() ? 0 : 1) << 9);
-            if (P.distributed_solar) tile_dist[ti] = 1;
-            const int zone_local0 = B.dev_zone_of[M.zone_begin] - tile.zone_begin;  // model's first zone, tile-local
-            zone_f[g] = s.front_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.front_zone : -1;
-            zone_b[g] = s.back_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.back_zone : -1;
-            S[g] = M.dt_subdivisions;
-            desc_index[g] = (int32_t)gd;
-            dt[g] = M.dt;
-            area[g] = s.area;
-            nx[g] = s.normal[0];
-            ny[g] = s.normal[1];
-            cos_tilt[g] = P.cos_tilt;
-            forced_c[g] = 2.537 * 1.67 * std::sqrt(s.perimeter * P.wind_speed_modifier / s.area);
-            eps_f[g] = P.front_emissivity;
-            eps_b[g] = P.back_emissivity;
-            amb_f[g] = s.front_ambient_t;
-            amb_b[g] = s.back_ambient_t;
-            ov_f[g] = s.front_hs_override;
-            ov_b[g] = s.back_hs_override;
-            for (int i = 0; i < P.n_nodes; ++i) {
-                const int64_t o = tile.node_offset + (int64_t)i * kBlock + t;
-                nodeT[o] = hb::kInitialT;
-                mass[o] = P.mass[i];
-                u[o] = P.u[i];
-                alpha_f[o] = P.front_alpha[i];
-                alpha_b[o] = P.back_alpha[i];
-            }
-            sc[0 * NS + g] = hb::kInitialH;
-            sc[1 * NS + g] = hb::kInitialH;
-        }
-        for (int z = 0; z < tile.n_zones; ++z) zoneT[(int64_t)tile.zone_begin + z] = hb::kInitialT;
-    }
-    // CSR lists in device-slot order
-    for (int64_t g = 0; g < NS; ++g) {
-        nm_off[g] = (int32_t)(nm_pairs.size() / 2);
-        cav_off[g] = (int32_t)cav.size();
-        const int64_t gd = desc_of[g];
-        if (gd < 0) continue;
-        const hb::SurfacePlan& P = B.plans[gd];
-        nm_pairs.insert(nm_pairs.end(), P.nomass_chunks.begin(), P.nomass_chunks.end());
-        for (const auto& c : P.cavities) cav.push_back(hb::CavityDev{c.node, c.gas, c.thickness, c.height, c.angle, c.eout, c.ein});
-    }
-    nm_off[NS] = (int32_t)(nm_pairs.size() / 2);
-    cav_off[NS] = (int32_t)cav.size();
-    if (nm_pairs.empty()) nm_pairs.push_back(0);
-    if (cav.empty()) cav.push_back(hb::CavityDev{0, 0, 1., 1., 0., 1., 1.});
-    // zones
-    for (size_t m = 0; m < B.models.size(); ++m) {
-        const hb::ModelPlan& M = B.models[m];
-        if (M.n_zones == 0) continue;
-        const int64_t gz0 = B.dev_zone_of[M.zone_begin];
-        const int64_t tile_idx = gz0 / kBlock;
-        const hb::Tile& tile = B.tiles[tile_idx];
-        const int sb = M.n_surfaces ? B.dev_surface_of[M.surface_begin] - tile.surface_begin : 0;
-        for (int z = 0; z < M.n_zones; ++z) {
-            const int64_t gz = gz0 + z;
-            zvol[gz] = B.zone_volume[M.zone_begin + z];
-            zdt[gz] = M.dt;
-            zS[gz] = M.dt_subdivisions;
-            zsb[gz] = sb;
-            zse[gz] = sb + M.n_surfaces;
-        }
-    }
-
+    hb::HostArrays H;
+    hb::pack_arrays(B, H);
     cudaStream_t st = h->stream;
-    h->n_nodes.upload(n_nodes, st); h->flags.upload(flags, st); h->zone_f.upload(zone_f, st);
-    h->zone_b.upload(zone_b, st); h->S.upload(S, st); h->site.upload(site, st);
-    h->desc_index.upload(desc_index, st); h->nm_off.upload(nm_off, st); h->nm_pairs.upload(nm_pairs, st);
-    h->cav_off.upload(cav_off, st); h->cav.upload(cav, st);
-    h->dt.upload(dt, st); h->area.upload(area, st); h->nx.upload(nx, st); h->ny.upload(ny, st);
-    h->cos_tilt.upload(cos_tilt, st); h->forced_c.upload(forced_c, st); h->eps_f.upload(eps_f, st);
-    h->eps_b.upload(eps_b, st); h->amb_f.upload(amb_f, st); h->amb_b.upload(amb_b, st);
-    h->hs_ov_f.upload(ov_f, st); h->hs_ov_b.upload(ov_b, st);
-    h->nodeT.upload(nodeT, st); h->mass.upload(mass, st); h->u.upload(u, st);
-    h->alpha_f.upload(alpha_f, st); h->alpha_b.upload(alpha_b, st); h->sc.upload(sc, st);
-    h->energy_f.upload(std::vector<double>(NS, 0.), st); h->energy_b.upload(std::vector<double>(NS, 0.), st);
-    h->nm_iters.upload(std::vector<unsigned long long>(NS, 0ull), st);
-    h->status.upload(std::vector<int32_t>(NS, 0), st);
-    h->zoneT.upload(zoneT, st); h->zvol.upload(zvol, st); h->zq.upload(zq, st); h->zinf_v.upload(zinf_v, st);
-    h->zinf_t.upload(zinf_t, st); h->zvent_v.upload(zvent_v, st); h->zvent_t.upload(zvent_t, st);
-    h->zdt.upload(zdt, st); h->zS.upload(zS, st); h->z_surf_begin.upload(zsb, st); h->z_surf_end.upload(zse, st);
+    h->n_nodes.upload(H.n_nodes, st); h->flags.upload(H.flags, st); h->zone_f.upload(H.zone_f, st);
+    h->zone_b.upload(H.zone_b, st); h->site.upload(H.site, st); h->desc_index.upload(H.desc_index, st);
+    h->nm_off.upload(H.nm_off, st); h->nm_pairs.upload(H.nm_pairs, st); h->cav_off.upload(H.cav_off, st);
+    h->cav.upload(H.cav, st);
+    h->area.upload(H.area, st); h->nx.upload(H.nx, st); h->ny.upload(H.ny, st); h->cos_tilt.upload(H.cos_tilt, st);
+    h->forced_c.upload(H.forced_c, st); h->eps_f.upload(H.eps_f, st); h->eps_b.upload(H.eps_b, st);
+    h->amb_f.upload(H.amb_f, st); h->amb_b.upload(H.amb_b, st); h->hs_ov_f.upload(H.hs_ov_f, st);
+    h->hs_ov_b.upload(H.hs_ov_b, st); h->af0.upload(H.af0, st); h->abL.upload(H.abL, st); h->v0.upload(H.v0, st);
+    h->vL.upload(H.vL, st);
+    h->nodeT.upload(H.nodeT, st); h->coefA.upload(H.coefA, st); h->coefB.upload(H.coefB, st);
+    h->ext_u.upload(H.ext_u, st); h->ext_mass.upload(H.ext_mass, st); h->ext_af.upload(H.ext_af, st);
+    h->ext_ab.upload(H.ext_ab, st); h->sc.upload(H.sc, st);
+    h->energy_f.upload(H.energy_f, st); h->energy_b.upload(H.energy_b, st);
+    h->nm_iters.upload(H.nm_iters, st); h->status.upload(H.status, st);
+    h->zoneT.upload(H.zoneT, st); h->zvol.upload(H.zvol, st); h->zq.upload(H.zq, st); h->zinf_v.upload(H.zinf_v, st);
+    h->zinf_t.upload(H.zinf_t, st); h->zvent_v.upload(H.zvent_v, st); h->zvent_t.upload(H.zvent_t, st);
+    h->z_surf_begin.upload(H.z_surf_begin, st); h->z_surf_end.upload(H.z_surf_end, st);
     h->tiles.upload(B.tiles, st);
     h->red_out.alloc(8);
     h->red_iout.alloc(4);
-    h->host_site.assign(NS, 0);
+    h->host_site.assign(B.n_dev_surfaces, 0);
 
-    // launch groups: (register tier, distributed-solar variant)
+    // launch groups: (lanes per wall, kernel variant); inside a group the heaviest tiles are scheduled first
     std::map<std::pair<int, int>, std::vector<int32_t>> by;
-    for (size_t ti = 0; ti < B.tiles.size(); ++ti) by[{tier_of(B.tiles[ti].nmax), tile_dist[ti]}].push_back((int32_t)ti);
+    for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
+        const hb::Tile& t = B.tiles[ti];
+        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : 0;
+        by[{-t.G, var}].push_back((int32_t)ti);   // largest walls first
+    }
+    HB_CUDA(cudaEventCreateWithFlags(&h->fork, cudaEventDisableTiming));
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
-        grp->nmax_tier = kv.first.first;
-        grp->dist = kv.first.second != 0;
+        grp->G = -kv.first.first;
+        grp->var = kv.first.second;
+        std::stable_sort(kv.second.begin(), kv.second.end(),
+                         [&](int32_t a, int32_t b) { return B.tiles[a].S > B.tiles[b].S; });
         grp->n_tiles = (int)kv.second.size();
         grp->ids.upload(kv.second, st);
+        HB_CUDA(cudaStreamCreateWithFlags(&grp->stream, cudaStreamNonBlocking));
+        HB_CUDA(cudaEventCreateWithFlags(&grp->done, cudaEventDisableTiming));
         h->groups.push_back(std::move(grp));
     }
     HB_CUDA(cudaStreamSynchronize(st));
@@ -257,10 +181,10 @@ void build_device(hb_handle* h) {
 }  // namespace
 
 namespace hb {
-// one translation unit per register tier (hb_march_tier.cu compiled with -DHB_TIER=N) so they build in parallel
+// one translation unit per lanes-per-wall tier (hb_march_tier.cu compiled with -DHB_TIER=G) so they build in parallel
 #define HB_DECL_TIER(N) \
-    void launch_march_##N(bool dist, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
-HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(24) HB_DECL_TIER(32) HB_DECL_TIER(64) HB_DECL_TIER(256)
+    cudaError_t launch_march_##N(int var, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+HB_DECL_TIER(1) HB_DECL_TIER(2) HB_DECL_TIER(4) HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(32)
 #undef HB_DECL_TIER
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
 void launch_dfma_probe(int blocks, int threads, double* out, int iters, double seed);
@@ -269,20 +193,28 @@ void launch_fill(cudaStream_t st, double* p, int64_t n, double v);
 
 namespace {
 
-void launch_series(hb_handle* h, const hb::SeriesDev& P) {
+// Fork the handle's stream into one stream per launch group, join back: the groups run concurrently and the
+// handle's stream (and CUDA events recorded on it) sees the whole series.
+void launch_series(hb_handle* h, hb::SeriesDev P) {
     const hb::DevView V = h->view();
+    P.single_site = h->single_site ? 1 : 0;
+    HB_CUDA(cudaEventRecord(h->fork, h->stream));
     for (auto& gp : h->groups) {
-        const hb_handle::Group& g = *gp;
-        switch (g.nmax_tier) {
-            case 8: hb::launch_march_8(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
-            case 16: hb::launch_march_16(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
-            case 24: hb::launch_march_24(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
-            case 32: hb::launch_march_32(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
-            case 64: hb::launch_march_64(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
-            default: hb::launch_march_256(g.dist, g.n_tiles, h->stream, V, P, g.ids.p); break;
+        hb_handle::Group& g = *gp;
+        HB_CUDA(cudaStreamWaitEvent(g.stream, h->fork, 0));
+        cudaError_t e;
+        switch (g.G) {
+            case 1: e = hb::launch_march_1(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 2: e = hb::launch_march_2(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 4: e = hb::launch_march_4(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 8: e = hb::launch_march_8(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 16: e = hb::launch_march_16(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            default: e = hb::launch_march_32(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
         }
-        HB_CUDA(cudaGetLastError());
+        HB_CUDA(e);
         h->launches += 1;
+        HB_CUDA(cudaEventRecord(g.done, g.stream));
+        HB_CUDA(cudaStreamWaitEvent(h->stream, g.done, 0));
     }
 }
 
@@ -292,6 +224,8 @@ void validate_series(const hb_handle* h, const hb_series* s) {
     if (s->n_sites < 1) throw std::runtime_error("n_sites must be >= 1");
     if (!s->weather) throw std::runtime_error("Trying to march on Thermal Model, but dry bulb temperature was not provided");
     const hb::BatchPlan& B = h->plan;
+    for (const auto& t : B.tiles)
+        if (t.S > hb::kMaxSubsteps) throw std::runtime_error("more sub-steps per main step than the supported maximum (128)");
     int64_t need = s->n_steps;
     if (s->weather_mode == HB_WEATHER_LINEAR) need = (int64_t)s->n_steps + 1;
     if (s->weather_mode == HB_WEATHER_PER_SUBSTEP) {
@@ -324,6 +258,7 @@ void update_sites(hb_handle* h, const hb_series* s) {
     if (s->model_site) ms.assign(s->model_site, s->model_site + B.models.size());
     if (ms == h->model_site_cache) return;
     h->model_site_cache = ms;
+    h->single_site = std::all_of(ms.begin(), ms.end(), [](int32_t v) { return v == 0; });
     std::fill(h->host_site.begin(), h->host_site.end(), 0);
     for (size_t gd = 0; gd < B.dev_surface_of.size(); ++gd) h->host_site[B.dev_surface_of[gd]] = ms[B.surface_model[gd]];
     HB_CUDA(cudaMemcpyAsync(h->site.p, h->host_site.data(), h->host_site.size() * sizeof(int32_t),
@@ -370,8 +305,6 @@ hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) 
             h->device = HB_DEVICE_NONE;
             return;
         }
-        for (const auto& P : h->plan.plans)
-            if (P.n_nodes > hb::kMaxNodes) throw std::runtime_error("surface has more nodes than the supported maximum (256)");
         int count = 0;
         cudaError_t e = cudaGetDeviceCount(&count);
         if (e != cudaSuccess || count <= 0)
@@ -394,6 +327,14 @@ void hb_destroy(hb_handle* h) {
         return;
     }
     cudaSetDevice(h->device);
+    for (auto& g : h->groups) {
+        if (g->stream) {
+            cudaStreamSynchronize(g->stream);
+            cudaStreamDestroy(g->stream);
+        }
+        if (g->done) cudaEventDestroy(g->done);
+    }
+    if (h->fork) cudaEventDestroy(h->fork);
     if (h->stream) {
         cudaStreamSynchronize(h->stream);
         cudaStreamDestroy(h->stream);
@@ -463,20 +404,9 @@ hb_status hb_set_state(hb_handle* h, const double* state) {
     return guarded([&] {
         need_device(h);
         const hb::BatchPlan& B = h->plan;
-        const int64_t NS = B.n_dev_surfaces;
-        std::vector<double> nodeT(B.node_slab_len, 0.), sc(8 * NS, 0.), zoneT(B.n_dev_zones, 0.);
-        for (size_t m = 0; m < B.models.size(); ++m) {
-            const hb::ModelPlan& M = B.models[m];
-            for (int z = 0; z < M.n_zones; ++z) zoneT[B.dev_zone_of[M.zone_begin + z]] = state[M.state_offset + z];
-        }
-        for (size_t gd = 0; gd < B.plans.size(); ++gd) {
-            const int64_t g = B.dev_surface_of[gd];
-            const hb::Tile& tile = B.tiles[g / kBlock];
-            const int t = (int)(g % kBlock);
-            const double* p = state + B.surface_state_offset[gd];
-            for (int k = 0; k < 8; ++k) sc[k * NS + g] = p[k];
-            for (int i = 0; i < B.plans[gd].n_nodes; ++i) nodeT[tile.node_offset + (int64_t)i * kBlock + t] = p[8 + i];
-        }
+        // ghost / padding slots keep whatever they hold: start from the device image
+        std::vector<double> nodeT(B.node_slab_len, 0.), sc(8 * B.n_dev_surfaces, 0.), zoneT(B.n_dev_zones, 0.);
+        hb::scatter_state(B, state, nodeT.data(), sc.data(), zoneT.data());
         HB_CUDA(cudaMemcpyAsync(h->nodeT.p, nodeT.data(), nodeT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         HB_CUDA(cudaMemcpyAsync(h->sc.p, sc.data(), sc.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         HB_CUDA(cudaMemcpyAsync(h->zoneT.p, zoneT.data(), zoneT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -484,22 +414,7 @@ hb_status hb_set_state(hb_handle* h, const double* state) {
     });
 }
 
-static void gather_state(const hb::BatchPlan& B, const double* nodeT, const double* sc, const double* zoneT,
-                         double* state) {
-    const int64_t NS = B.n_dev_surfaces;
-    for (size_t m = 0; m < B.models.size(); ++m) {
-        const hb::ModelPlan& M = B.models[m];
-        for (int z = 0; z < M.n_zones; ++z) state[M.state_offset + z] = zoneT[B.dev_zone_of[M.zone_begin + z]];
-    }
-    for (size_t gd = 0; gd < B.plans.size(); ++gd) {
-        const int64_t g = B.dev_surface_of[gd];
-        const hb::Tile& tile = B.tiles[g / kBlock];
-        const int t = (int)(g % kBlock);
-        double* p = state + B.surface_state_offset[gd];
-        for (int k = 0; k < 8; ++k) p[k] = sc[k * NS + g];
-        for (int i = 0; i < B.plans[gd].n_nodes; ++i) p[8 + i] = nodeT[tile.node_offset + (int64_t)i * kBlock + t];
-    }
-}
+using hb::gather_state;
 
 hb_status hb_get_state(hb_handle* h, double* state) {
     return guarded([&] {

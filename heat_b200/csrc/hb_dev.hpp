@@ -1,6 +1,7 @@
-// hb_dev.hpp — device-side views of the SoA buffers (shared by the launchers and the kernels).
+// hb_dev.hpp — views of the packed SoA buffers (shared by the host packer, the launchers and the kernels).
 #pragma once
 #include <cstdint>
+#include <vector>
 
 #include "hb_internal.hpp"
 
@@ -11,16 +12,15 @@ struct CavityDev {
     double thickness, height, angle, eout, ein;
 };
 
+// Pointers into the packed buffers.  On the GPU they are device pointers (hb_capi.cu uploads HostArrays verbatim).
 struct DevView {
-    // per device surface slot
-    const int32_t* n_nodes;
+    // ---- per device surface slot (tile.surface_begin + wall) ----
+    const int32_t* n_nodes;   // 0 on padding slots
     const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity
     const int32_t* zone_f;    // tile-local zone index or -1
     const int32_t* zone_b;
-    const int32_t* S;         // dt_subdivisions of the surface's model
     const int32_t* site;
     const int32_t* desc_index;  // descriptor-order surface index (for per-surface inputs)
-    const double* dt;
     const double* area;
     const double* nx;
     const double* ny;
@@ -32,24 +32,31 @@ struct DevView {
     const double* amb_b;
     const double* hs_ov_f;
     const double* hs_ov_b;
+    const double* af0;        // front solar absorptance of node 0
+    const double* abL;        // back solar absorptance of node n-1
+    const double* v0;         // dt/C of node 0 (0 when it has no mass)
+    const double* vL;         // dt/C of node n-1
     const int32_t* nm_off;    // CSR over no-mass chunks: pairs (ini, fin)
     const int32_t* nm_pairs;
     const int32_t* cav_off;   // CSR over cavity links
     const CavityDev* cav;
-    // [node][kBlock] slabs per tile
-    double* nodeT;
-    const double* mass;
-    const double* u;
-    const double* alpha_f;
-    const double* alpha_b;
-    // state scalars [8][n_dev_surfaces]: h_f, h_b, flow_f, flow_b, solar_f, solar_b, ir_f, ir_b
+    // ---- [kNL][G*W] slabs per tile (tile.node_offset) ----
+    double* nodeT;            // slot temperatures (ghost/padding slots hold scratch values)
+    const double* coefA;      // u_i·dt/C_i   towards slot+1 (0 on ghosts, padding, no-mass nodes and the last node)
+    const double* coefB;      // u_{i-1}·dt/C_i towards slot-1 (0 on …, and the first node)
+    // ---- [node][W] wall-major arrays of TILE_EXT tiles (tile.ext_offset) ----
+    const double* ext_u;
+    const double* ext_mass;
+    const double* ext_af;
+    const double* ext_ab;
+    // ---- state scalars [8][n_dev_surfaces]: h_f, h_b, flow_f, flow_b, solar_f, solar_b, ir_f, ir_b ----
     double* sc;
     int64_t n_dev_surfaces;
     double* energy_f;
     double* energy_b;
     unsigned long long* nm_iters;
     int32_t* status;
-    // zones
+    // ---- zones (tile.zone_begin + local zone) ----
     double* zoneT;
     const double* zvol;
     const double* zq;
@@ -57,13 +64,28 @@ struct DevView {
     const double* zinf_t;
     const double* zvent_v;
     const double* zvent_t;
-    const double* zdt;
-    const int32_t* zS;
-    const int32_t* z_surf_begin;  // tile-local thread range of the zone's model
+    const int32_t* z_surf_begin;  // tile-local wall range of the zone's model
     const int32_t* z_surf_end;
     int64_t n_dev_zones;
     const Tile* tiles;
 };
+
+// Host image of every packed buffer (what hb_create uploads).
+struct HostArrays {
+    std::vector<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
+    std::vector<CavityDev> cav;
+    std::vector<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL;
+    std::vector<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
+    std::vector<unsigned long long> nm_iters;
+    std::vector<int32_t> status;
+    std::vector<double> zoneT, zvol, zq, zinf_v, zinf_t, zvent_v, zvent_t;
+    std::vector<int32_t> z_surf_begin, z_surf_end;
+    DevView view(const BatchPlan& B);   // pointers into the host vectors (used by the test emulator)
+};
+void pack_arrays(const BatchPlan& B, HostArrays& H);
+// scatter / gather between the reference-layout state vector and the packed buffers
+void scatter_state(const BatchPlan& B, const double* state, double* nodeT, double* sc, double* zoneT);
+void gather_state(const BatchPlan& B, const double* nodeT, const double* sc, const double* zoneT, double* state);
 
 struct SeriesDev {
     int32_t n_steps;
@@ -75,6 +97,7 @@ struct SeriesDev {
     const double* inputs;
     int64_t n_desc_surfaces;
     int32_t record_every;
+    int32_t single_site;     // every model is on site 0: tiles share one weather table per main step
     double* zone_rec;        // [rec][n_dev_zones]
     double* node_rec;        // [rec][slab_len]
     double* sc_rec;          // [rec][8][n_dev_surfaces]

@@ -12,8 +12,9 @@
 #include <cmath>
 #include <numeric>
 #include <stdexcept>
+#include <tuple>
 
-#include "hb_internal.hpp"
+#include "hb_dev.hpp"
 
 namespace hb {
 namespace {
@@ -332,50 +333,251 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B) {
         M.state_len = (int32_t)(state - M.state_offset);
         B.nodes_total += M.nodes;
         B.updates_per_step += M.nodes * (int64_t)M.dt_subdivisions;
-        if (M.n_surfaces > kBlock || M.n_zones > kBlock) fail("model larger than one tile (128 surfaces / zones)");
     }
     B.state_len_total = state;
 
-    // ---- device ordering: sort models so that a warp sees similar node counts and sub-step counts ----
+    // ---- device ordering --------------------------------------------------------------------------------
+    // Every model goes, whole, into one tile (its surfaces couple through its zones every sub-step).  Tiles are
+    // uniform in lanes-per-wall G (from the model's largest wall), kernel variant and sub-step count S, so a block
+    // runs one loop shape; models are sorted by (G, variant, S) and packed greedily.
+    for (int m = 0; m < d->n_models; ++m) {
+        ModelPlan& M = B.models[m];
+        if (M.nmax > kMaxNodes) fail("surface has more nodes than the supported maximum (254)");
+        M.variant = 0;
+        for (int k = 0; k < M.n_surfaces; ++k) {
+            const SurfacePlan& P = B.plans[M.surface_begin + k];
+            if (!P.nomass_chunks.empty() || !P.cavities.empty()) M.variant |= TILE_EXT;
+            if (!P.cavities.empty()) M.variant |= TILE_CAV;
+            if (P.distributed_solar) M.variant |= TILE_EXT | TILE_DIST;
+        }
+        const int W = walls_of_group(group_of_nodes(M.nmax));
+        if (M.n_surfaces > W || M.n_zones > W)
+            fail("model larger than one tile (" + std::to_string(W) + " surfaces / zones at this wall size)");
+    }
     B.model_order.resize(d->n_models);
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
-    if (d->n_models > 1) {
-        std::stable_sort(B.model_order.begin(), B.model_order.end(), [&](int a, int b) {
-            const ModelPlan &A = B.models[a], &C = B.models[b];
-            if (A.n_surfaces != C.n_surfaces) return A.n_surfaces < C.n_surfaces;
-            if (A.nmax != C.nmax) return A.nmax < C.nmax;
-            return A.dt_subdivisions < C.dt_subdivisions;
-        });
-    }
+    auto key = [&](int m) {
+        const ModelPlan& M = B.models[m];
+        return std::make_tuple(group_of_nodes(M.nmax), M.variant & (TILE_EXT | TILE_DIST), M.dt_subdivisions);
+    };
+    if (d->n_models > 1)
+        std::stable_sort(B.model_order.begin(), B.model_order.end(), [&](int a, int b) { return key(a) < key(b); });
+
     B.dev_surface_of.assign(n_surf, -1);
     B.dev_zone_of.assign(n_zone, -1);
+    B.surface_tile.assign(n_surf, -1);
+    B.zone_tile.assign(n_zone, -1);
     B.tiles.clear();
-    Tile cur{0, 0, 0, 0, 0, 0, 0};
-    int64_t node_off = 0;
-    auto tier_of = [](int n) { return n <= 8 ? 8 : n <= 16 ? 16 : n <= 24 ? 24 : n <= 32 ? 32 : n <= 64 ? 64 : 256; };
+    int64_t node_off = 0, ext_off = 0;
+    int32_t surf_slots = 0, zone_slots = 0;
+    Tile cur{};
+    bool open = false;
     auto close_tile = [&]() {
-        if (cur.n_surfaces == 0 && cur.n_zones == 0) return;
+        if (!open) return;
         cur.node_offset = node_off;
-        node_off += (int64_t)tier_of(cur.nmax) * kBlock;
+        node_off += (int64_t)kNL * cur.G * cur.W;
+        cur.ext_offset = -1;
+        if (cur.flags & TILE_EXT) {
+            cur.ext_offset = ext_off;
+            ext_off += (int64_t)cur.nmax * cur.W;
+        }
+        surf_slots += cur.W;
+        zone_slots += cur.W;
         B.tiles.push_back(cur);
-        const int32_t t = (int32_t)B.tiles.size();
-        cur = Tile{t * kBlock, 0, t * kBlock, 0, 0, 0, 0};
+        open = false;
     };
     for (int pos = 0; pos < d->n_models; ++pos) {
-        const ModelPlan& M = B.models[B.model_order[pos]];
-        const bool tier_change = cur.n_surfaces > 0 && tier_of(M.nmax) != tier_of(cur.nmax);
-        if (cur.n_surfaces + M.n_surfaces > kBlock || cur.n_zones + M.n_zones > kBlock || tier_change) close_tile();
-        for (int k = 0; k < M.n_surfaces; ++k) B.dev_surface_of[M.surface_begin + k] = cur.surface_begin + cur.n_surfaces + k;
-        for (int k = 0; k < M.n_zones; ++k) B.dev_zone_of[M.zone_begin + k] = cur.zone_begin + cur.n_zones + k;
+        const int m = B.model_order[pos];
+        const ModelPlan& M = B.models[m];
+        const int G = group_of_nodes(M.nmax);
+        const int W = walls_of_group(G);
+        const int variant = M.variant & (TILE_EXT | TILE_DIST);
+        if (open && (cur.G != G || (cur.flags & (TILE_EXT | TILE_DIST)) != variant || cur.S != M.dt_subdivisions ||
+                     cur.n_surfaces + M.n_surfaces > W || cur.n_zones + M.n_zones > W))
+            close_tile();
+        if (!open) {
+            cur = Tile{};
+            cur.surface_begin = surf_slots;
+            cur.zone_begin = zone_slots;
+            cur.G = G;
+            cur.W = W;
+            cur.S = M.dt_subdivisions;
+            cur.dt = M.dt;
+            cur.flags = variant;
+            open = true;
+        }
+        const int32_t ti = (int32_t)B.tiles.size();
+        for (int k = 0; k < M.n_surfaces; ++k) {
+            B.dev_surface_of[M.surface_begin + k] = cur.surface_begin + cur.n_surfaces + k;
+            B.surface_tile[M.surface_begin + k] = ti;
+        }
+        for (int k = 0; k < M.n_zones; ++k) {
+            B.dev_zone_of[M.zone_begin + k] = cur.zone_begin + cur.n_zones + k;
+            B.zone_tile[M.zone_begin + k] = ti;
+        }
         cur.n_surfaces += M.n_surfaces;
         cur.n_zones += M.n_zones;
         cur.nmax = std::max(cur.nmax, M.nmax);
-        cur.smax = std::max(cur.smax, M.dt_subdivisions);
+        cur.flags |= M.variant;
     }
     close_tile();
     B.node_slab_len = node_off;
-    B.n_dev_surfaces = (int64_t)B.tiles.size() * kBlock;
-    B.n_dev_zones = (int64_t)B.tiles.size() * kBlock;
+    B.ext_len = ext_off;
+    B.n_dev_surfaces = surf_slots;
+    B.n_dev_zones = zone_slots;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Packing: descriptor-order plans → the SoA buffers the kernels read (DevView layout, hb_dev.hpp).
+// ------------------------------------------------------------------------------------------------------------
+void pack_arrays(const BatchPlan& B, HostArrays& H) {
+    const int64_t NS = B.n_dev_surfaces, NZ = B.n_dev_zones;
+    H.n_nodes.assign(NS, 0); H.flags.assign(NS, 0); H.zone_f.assign(NS, -1); H.zone_b.assign(NS, -1);
+    H.site.assign(NS, 0); H.desc_index.assign(NS, 0); H.nm_off.assign(NS + 1, 0); H.cav_off.assign(NS + 1, 0);
+    H.nm_pairs.clear(); H.cav.clear();
+    for (auto* v : {&H.area, &H.nx, &H.ny, &H.cos_tilt, &H.forced_c, &H.eps_f, &H.eps_b, &H.amb_f, &H.amb_b, &H.af0,
+                    &H.abL, &H.v0, &H.vL, &H.energy_f, &H.energy_b})
+        v->assign(NS, 0.);
+    H.hs_ov_f.assign(NS, NAN); H.hs_ov_b.assign(NS, NAN);
+    H.nodeT.assign(B.node_slab_len, 0.); H.coefA.assign(B.node_slab_len, 0.); H.coefB.assign(B.node_slab_len, 0.);
+    for (auto* v : {&H.ext_u, &H.ext_mass, &H.ext_af, &H.ext_ab}) v->assign(std::max<int64_t>(B.ext_len, 1), 0.);
+    H.sc.assign(8 * NS, 0.);
+    H.nm_iters.assign(NS, 0ull); H.status.assign(NS, 0);
+    H.zoneT.assign(NZ, 0.); H.zvol.assign(NZ, 0.); H.zq.assign(NZ, 0.); H.zinf_v.assign(NZ, 0.); H.zinf_t.assign(NZ, NAN);
+    H.zvent_v.assign(NZ, 0.); H.zvent_t.assign(NZ, NAN);
+    H.z_surf_begin.assign(NZ, 0); H.z_surf_end.assign(NZ, 0);
+
+    std::vector<int64_t> desc_of(NS, -1);
+    for (size_t gd = 0; gd < B.dev_surface_of.size(); ++gd) desc_of[B.dev_surface_of[gd]] = (int64_t)gd;
+
+    for (size_t gd = 0; gd < B.plans.size(); ++gd) {
+        const int64_t g = B.dev_surface_of[gd];
+        const Tile& tile = B.tiles[B.surface_tile[gd]];
+        const int wl = (int)(g - tile.surface_begin);
+        const hb_surface& s = B.surfaces[gd];
+        const SurfacePlan& P = B.plans[gd];
+        const ModelPlan& M = B.models[B.surface_model[gd]];
+        const int n = P.n_nodes;
+        H.n_nodes[g] = n;
+        H.flags[g] = (s.front_kind & 15) | ((s.back_kind & 15) << 4) | ((P.distributed_solar ? 1 : 0) << 8) |
+                     ((P.cavities.empty() ? 0 : 1) << 9);
+        const int zone_local0 = M.n_zones ? B.dev_zone_of[M.zone_begin] - tile.zone_begin : 0;
+        H.zone_f[g] = s.front_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.front_zone : -1;
+        H.zone_b[g] = s.back_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.back_zone : -1;
+        H.desc_index[g] = (int32_t)gd;
+        H.area[g] = s.area;
+        H.nx[g] = s.normal[0];
+        H.ny[g] = s.normal[1];
+        H.cos_tilt[g] = P.cos_tilt;
+        H.forced_c[g] = 2.537 * 1.67 * std::sqrt(s.perimeter * P.wind_speed_modifier / s.area);
+        H.eps_f[g] = P.front_emissivity;
+        H.eps_b[g] = P.back_emissivity;
+        H.amb_f[g] = s.front_ambient_t;
+        H.amb_b[g] = s.back_ambient_t;
+        H.hs_ov_f[g] = s.front_hs_override;
+        H.hs_ov_b[g] = s.back_hs_override;
+        // scaled tridiagonal coefficients: row i of K times dt/C_i (surface.rs:168-187); no-mass rows are zero
+        auto vof = [&](int i) { return P.mass[i] >= kMassiveThreshold ? M.dt / P.mass[i] : 0.0; };
+        for (int i = 0; i < n; ++i) {
+            const int64_t o = B.slab_index((int64_t)gd, i);
+            const double vi = vof(i);
+            const double ui = P.u[i];                       // link i → i+1 (−1: cavity, filled in per sub-step)
+            const double um = i > 0 ? P.u[i - 1] : 0.0;     // link i−1 → i
+            H.nodeT[o] = kInitialT;
+            H.coefA[o] = (i + 1 < n && ui > 0. ? ui : 0.) * vi;
+            H.coefB[o] = (um > 0. ? um : 0.) * vi;
+            if (tile.ext_offset >= 0) {
+                const int64_t e = tile.ext_offset + (int64_t)i * tile.W + wl;
+                H.ext_u[e] = P.u[i];
+                H.ext_mass[e] = P.mass[i];
+                H.ext_af[e] = P.front_alpha[i];
+                H.ext_ab[e] = P.back_alpha[i];
+            }
+        }
+        H.v0[g] = vof(0);
+        H.vL[g] = vof(n - 1);
+        if (!P.distributed_solar) {  // distributed: every absorptance goes through the per-node source term
+            H.af0[g] = P.front_alpha[0];
+            H.abL[g] = P.back_alpha[n - 1];
+        }
+        H.sc[0 * NS + g] = kInitialH;
+        H.sc[1 * NS + g] = kInitialH;
+    }
+    // CSR lists in device-slot order
+    for (int64_t g = 0; g < NS; ++g) {
+        H.nm_off[g] = (int32_t)(H.nm_pairs.size() / 2);
+        H.cav_off[g] = (int32_t)H.cav.size();
+        const int64_t gd = desc_of[g];
+        if (gd < 0) continue;
+        const SurfacePlan& P = B.plans[gd];
+        H.nm_pairs.insert(H.nm_pairs.end(), P.nomass_chunks.begin(), P.nomass_chunks.end());
+        for (const auto& c : P.cavities)
+            H.cav.push_back(CavityDev{c.node, c.gas, c.thickness, c.height, c.angle, c.eout, c.ein});
+    }
+    H.nm_off[NS] = (int32_t)(H.nm_pairs.size() / 2);
+    H.cav_off[NS] = (int32_t)H.cav.size();
+    if (H.nm_pairs.empty()) H.nm_pairs.push_back(0);
+    if (H.cav.empty()) H.cav.push_back(CavityDev{0, 0, 1., 1., 0., 1., 1.});
+    // zones
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const ModelPlan& M = B.models[m];
+        if (M.n_zones == 0) continue;
+        const Tile& tile = B.tiles[B.zone_tile[M.zone_begin]];
+        const int sb = M.n_surfaces ? B.dev_surface_of[M.surface_begin] - tile.surface_begin : 0;
+        for (int z = 0; z < M.n_zones; ++z) {
+            const int64_t gz = B.dev_zone_of[M.zone_begin + z];
+            H.zoneT[gz] = kInitialT;
+            H.zvol[gz] = B.zone_volume[M.zone_begin + z];
+            H.z_surf_begin[gz] = sb;
+            H.z_surf_end[gz] = sb + M.n_surfaces;
+        }
+    }
+}
+
+DevView HostArrays::view(const BatchPlan& B) {
+    DevView V{};
+    V.n_nodes = n_nodes.data(); V.flags = flags.data(); V.zone_f = zone_f.data(); V.zone_b = zone_b.data();
+    V.site = site.data(); V.desc_index = desc_index.data(); V.area = area.data(); V.nx = nx.data(); V.ny = ny.data();
+    V.cos_tilt = cos_tilt.data(); V.forced_c = forced_c.data(); V.eps_f = eps_f.data(); V.eps_b = eps_b.data();
+    V.amb_f = amb_f.data(); V.amb_b = amb_b.data(); V.hs_ov_f = hs_ov_f.data(); V.hs_ov_b = hs_ov_b.data();
+    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data();
+    V.nm_off = nm_off.data(); V.nm_pairs = nm_pairs.data(); V.cav_off = cav_off.data(); V.cav = cav.data();
+    V.nodeT = nodeT.data(); V.coefA = coefA.data(); V.coefB = coefB.data();
+    V.ext_u = ext_u.data(); V.ext_mass = ext_mass.data(); V.ext_af = ext_af.data(); V.ext_ab = ext_ab.data();
+    V.sc = sc.data(); V.n_dev_surfaces = B.n_dev_surfaces; V.energy_f = energy_f.data(); V.energy_b = energy_b.data();
+    V.nm_iters = nm_iters.data(); V.status = status.data();
+    V.zoneT = zoneT.data(); V.zvol = zvol.data(); V.zq = zq.data(); V.zinf_v = zinf_v.data(); V.zinf_t = zinf_t.data();
+    V.zvent_v = zvent_v.data(); V.zvent_t = zvent_t.data(); V.z_surf_begin = z_surf_begin.data();
+    V.z_surf_end = z_surf_end.data(); V.n_dev_zones = B.n_dev_zones; V.tiles = B.tiles.data();
+    return V;
+}
+
+void scatter_state(const BatchPlan& B, const double* state, double* nodeT, double* sc, double* zoneT) {
+    const int64_t NS = B.n_dev_surfaces;
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const ModelPlan& M = B.models[m];
+        for (int z = 0; z < M.n_zones; ++z) zoneT[B.dev_zone_of[M.zone_begin + z]] = state[M.state_offset + z];
+    }
+    for (size_t gd = 0; gd < B.plans.size(); ++gd) {
+        const int64_t g = B.dev_surface_of[gd];
+        const double* p = state + B.surface_state_offset[gd];
+        for (int k = 0; k < 8; ++k) sc[k * NS + g] = p[k];
+        for (int i = 0; i < B.plans[gd].n_nodes; ++i) nodeT[B.slab_index((int64_t)gd, i)] = p[8 + i];
+    }
+}
+
+void gather_state(const BatchPlan& B, const double* nodeT, const double* sc, const double* zoneT, double* state) {
+    const int64_t NS = B.n_dev_surfaces;
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const ModelPlan& M = B.models[m];
+        for (int z = 0; z < M.n_zones; ++z) state[M.state_offset + z] = zoneT[B.dev_zone_of[M.zone_begin + z]];
+    }
+    for (size_t gd = 0; gd < B.plans.size(); ++gd) {
+        const int64_t g = B.dev_surface_of[gd];
+        double* p = state + B.surface_state_offset[gd];
+        for (int k = 0; k < 8; ++k) p[k] = sc[k * NS + g];
+        for (int i = 0; i < B.plans[gd].n_nodes; ++i) p[8 + i] = nodeT[B.slab_index((int64_t)gd, i)];
+    }
 }
 
 }  // namespace hb

@@ -8,9 +8,25 @@
 
 namespace hb {
 
-constexpr int kBlock = 128;          // threads per tile (= CUDA block); one thread per surface
+// ---- device geometry of a tile (= one CUDA block) -----------------------------------------------------------
+// A wall (surface) is marched by a LANE GROUP of G consecutive lanes, each lane holding kNL consecutive "slots" of
+// the wall in registers.  Slot 0 is the front ghost node (equivalent outdoor/indoor air temperature), slots
+// 1..n hold the n nodes, slot n+1 is the back ghost node, the rest is padding: n + 2 <= G * kNL.
+// A tile holds W walls -> G*W threads.  One warp of the block additionally plays the SCALAR role: lane j of that
+// warp evaluates the per-wall scalar physics (film coefficients, no-mass chunks, zone update) of wall j.
+constexpr int kNL = 8;               // slots per lane
+constexpr int kMaxG = 32;            // lanes per wall: 1, 2, 4, 8, 16, 32
+constexpr int kMaxNodes = kMaxG * kNL - 2;  // 254
+constexpr int kMaxWalls = 32;        // walls (and zones) per tile; == warp size (scalar role)
 constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
-constexpr int kMaxNodes = 256;       // largest tier (tiers > 32 keep node arrays in local memory)
+constexpr int kMaxSubsteps = 128;    // shared weather table rows (S <= 120 for n >= 1 step/hour)
+
+inline constexpr int walls_of_group(int G) { return G <= 8 ? 32 : G == 16 ? 16 : 8; }
+inline int group_of_nodes(int n) {
+    int G = 1;
+    while (G * kNL < n + 2) G *= 2;
+    return G;
+}
 
 // Constants of the reference (kept in one place; cited where used)
 constexpr double kSigma = 5.670374419e-8;  // lib.rs:49
@@ -54,17 +70,30 @@ struct ModelPlan {
     int32_t state_len = 0;
     int64_t nodes = 0;
     int32_t nmax = 0;
+    int32_t variant = 0;             // TILE_* flags needed by its surfaces
 };
 
-// A tile = the models one CUDA block marches. Threads ↔ surfaces, first n_zones threads ↔ zones.
+enum : int32_t {
+    TILE_EXT = 1,    // some wall has no-mass chunks or cavities: node temperatures are mirrored in shared memory
+    TILE_DIST = 2,   // some wall absorbs solar radiation on inner nodes (transparent layers)
+    TILE_CAV = 4,    // some wall has a gas cavity (temperature-dependent link)
+};
+
+// A tile = the models one CUDA block marches.
 struct Tile {
-    int32_t surface_begin;   // index into the DEVICE ordering of surfaces
+    int32_t surface_begin;   // index into the DEVICE ordering of surfaces (tile owns W consecutive slots)
     int32_t n_surfaces;
-    int32_t zone_begin;      // index into the DEVICE ordering of zones
+    int32_t zone_begin;      // index into the DEVICE ordering of zones (tile owns W consecutive slots)
     int32_t n_zones;
     int32_t nmax;            // max n_nodes in the tile
-    int32_t smax;            // max dt_subdivisions in the tile
-    int64_t node_offset;     // offset (in doubles) of the tile's [node][kBlock] slabs
+    int32_t S;               // dt_subdivisions (uniform over the tile)
+    int32_t G;               // lanes per wall
+    int32_t W;               // wall slots
+    int32_t flags;           // TILE_*
+    int32_t pad_;
+    int64_t node_offset;     // offset (doubles) of the tile's [kNL][G*W] slabs (node T, coefficient A, coefficient B)
+    int64_t ext_offset;      // offset (doubles) of the tile's [nmax][W] wall-major arrays (TILE_EXT only, else -1)
+    double dt;               // sub-step length [s] (uniform over the tile)
 };
 
 struct BatchPlan {
@@ -86,10 +115,21 @@ struct BatchPlan {
     std::vector<int32_t> model_order;      // device position → descriptor model index
     std::vector<int32_t> dev_surface_of;   // descriptor surface → device surface slot
     std::vector<int32_t> dev_zone_of;      // descriptor zone → device zone slot
+    std::vector<int32_t> surface_tile;     // descriptor surface → tile index
+    std::vector<int32_t> zone_tile;        // descriptor zone → tile index
     std::vector<Tile> tiles;
-    int64_t node_slab_len = 0;             // total doubles in one [node][thread] slab array
-    int64_t n_dev_surfaces = 0;            // tiles.size() * kBlock (padded)
+    int64_t node_slab_len = 0;             // total doubles in one slab array
+    int64_t ext_len = 0;                   // total doubles in one wall-major ext array
+    int64_t n_dev_surfaces = 0;            // Σ W over tiles (padded)
     int64_t n_dev_zones = 0;
+
+    // position of node i of descriptor surface gd inside the slab arrays
+    int64_t slab_index(int64_t gd, int node) const {
+        const Tile& t = tiles[surface_tile[gd]];
+        const int wl = dev_surface_of[gd] - t.surface_begin;
+        const int slot = node + 1;
+        return t.node_offset + (int64_t)(slot % kNL) * (t.G * t.W) + (int64_t)wl * t.G + slot / kNL;
+    }
 };
 
 // Host discretization + planning (hb_host.cc). Throws std::runtime_error with the reference-style message.

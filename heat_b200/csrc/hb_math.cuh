@@ -1,0 +1,476 @@
+// hb_math.cuh — scalar physics of the wall march, callable from the CUDA kernels (and, for the test emulator in
+// tests/emu, from host code: every function is HB_HD).  All f64.
+//
+//   tarp_natural      convection.rs:87-110
+//   cavity_u/nusselt  cavity.rs:59-69, gas.rs:45-74,82-315
+//   border            surface.rs:596-717 (calc_border_conditions)
+//   solve_nomass      surface.rs:790-898 around discretization.rs:596-700 (get_k_q) for one no-mass chunk
+//   zone_update       model.rs:489-597 (calculate_zones_abc), zone.rs:59-65 (mcp), model.rs:650-674
+//
+// pow(x,1/3) is evaluated as cbrt(x) and pow(x,1/4) as sqrt(sqrt(x)) (≤ 1 ulp apart from libm pow).
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#include "hb_dev.hpp"
+
+#if defined(__CUDACC__)
+#define HB_HD __host__ __device__ __forceinline__
+#define HB_HD_NOINLINE static __host__ __device__ __noinline__
+#else
+#define HB_HD inline
+#define HB_HD_NOINLINE static inline
+#endif
+
+namespace hb {
+
+constexpr double kPi = 3.14159265358979323846;
+
+HB_HD double hb_nan() {
+#if defined(__CUDA_ARCH__)
+    return __longlong_as_double(0x7ff8000000000000LL);
+#else
+    return NAN;
+#endif
+}
+
+// Per-wall constants (shared memory in the kernel).
+struct WallC {
+    double area, cos_tilt, c_same, c_opp, forced_c, eps_f, eps_b, amb_f, amb_b, ov_f, ov_b, nx, ny, af0, abL, v0, vL;
+    int32_t n, kind_f, kind_b, zf, zb, site, nm_begin, nm_end, cav_begin, cav_end, flags, desc_index;
+    int32_t pad_[2];   // sizeof == 17*8 + 14*4 = 192 … keep 8-byte multiples
+};
+
+// Per-wall dynamic scalar state (registers of the scalar lane).
+struct WallS {
+    double h_f, h_b, flow_f, flow_b, sol_f, sol_b, ir_f, ir_b;   // the 8 SimulationState slots (surface.rs:428-442)
+    double e_f, e_b;                 // ∫ flow·A dt
+    double ts_f, ts_b;               // temperatures of the two end nodes
+    double solar_front, solar_back;  // clamped irradiances of this main step (surface.rs:916-923)
+    double trad_out_f, trad_out_b;   // outdoor radiant temperatures of this main step (surface.rs:647,692)
+    double t_front, t_back, forced;  // carried from the pre- to the post-march phase of a sub-step
+    unsigned long long nm_iters;
+    int32_t status;
+};
+
+// What the scalar lane hands to the lanes that march the nodes.
+struct BoundaryLinks {
+    double ghost_f, bf;   // front ghost temperature and its link coefficient h_f·dt/C_0
+    double ghost_b, ab;   // back ghost temperature and h_b·dt/C_{n-1}
+};
+
+struct SubWeather {
+    double t_out, sqrt_ws, sin_wd, cos_wd;
+};
+
+HB_HD void sub_weather(double t_out, double wdir_deg, double wspeed, SubWeather& w) {
+    w.t_out = t_out;
+    w.sqrt_ws = sqrt(wspeed);
+    const double a = wdir_deg * (kPi / 180.0);
+#if defined(__CUDA_ARCH__)
+    sincos(a, &w.sin_wd, &w.cos_wd);
+#else
+    w.sin_wd = sin(a);
+    w.cos_wd = cos(a);
+#endif
+}
+
+// convection.rs:87-110 with the per-surface constants 9.482/(7.238-|cosΣ|) and 1.81/(1.382+|cosΣ|) hoisted.
+HB_HD double tarp_natural(double t_air, double t_surf, double tilt, double c_same, double c_opp) {
+    const double d = t_air - t_surf;
+    const double ad = fabs(d);
+    const double r = cbrt(ad);
+    double h;
+    if (ad < 1e-3 || fabs(tilt) < 1e-3)
+        h = 1.31 * r;
+    else if ((d < 0. && tilt < 0.) || (d > 0. && tilt > 0.))
+        h = c_same * r;
+    else
+        h = c_opp * r;
+    return h < 0.1 ? 0.1 : h;  // MIN_H, convection.rs:22; NaN propagates and is flagged by the caller
+}
+
+// gas.rs:45-74 — ascending-power polynomials in T[K]
+struct GasDev {
+    double l0, l1, m0, m1, c0, c1, mass;
+};
+HB_HD GasDev gas_of(int id) {
+    switch (id) {
+        case HB_GAS_ARGON: return GasDev{2.285e-3, 5.149e-5, 3.379e-6, 6.451e-8, 521.9285, 0., 39.948};
+        case HB_GAS_KRYPTON: return GasDev{9.443e-4, 2.826e-5, 2.213e-6, 7.777e-8, 248.0907, 0., 83.8};
+        case HB_GAS_XENON: return GasDev{4.538e-4, 1.723e-5, 1.069e-6, 7.414e-8, 158.3397, 0., 131.30};
+        default: return GasDev{2.873e-3, 7.760e-5, 3.723e-6, 4.94e-8, 1002.7370, 1.2324e-2, 28.97};
+    }
+}
+
+// gas.rs:285-309
+HB_HD_NOINLINE double nu_90(double ra, double a_gi) {
+    double nu1;
+    if (ra <= 1e4)
+        nu1 = 1. + 1.7596678 * 1e-10 * pow(ra, 2.2984755);
+    else if (ra < 5e4)
+        nu1 = 0.028154 * pow(ra, 0.4134);
+    else
+        nu1 = 0.0673838 * cbrt(ra);
+    const double nu2 = 0.242 * pow(ra / a_gi, 0.272);
+    return nu1 > nu2 ? nu1 : nu2;
+}
+// gas.rs:249-264
+HB_HD_NOINLINE double nu_60(double ra, double a_gi) {
+    const double g = 0.5 / pow(1. + pow(ra / 3160., 20.6), 0.1);
+    const double base = 0.0936 * pow(ra, 0.314) / (1. + g);
+    const double b2 = base * base, b4 = b2 * b2;
+    const double nu1 = pow(1. + b4 * b2 * base, 1. / 7.);
+    const double nu2 = (0.104 + 0.175 / a_gi) * pow(ra, 0.283);
+    return nu1 > nu2 ? nu1 : nu2;
+}
+// gas.rs:197-315
+HB_HD_NOINLINE double nusselt(double ra, double gamma_in, double a_gi, int& status) {
+    const double THIRTY = 30. * kPi / 180.;
+    const double EPS = 0.5 * kPi / 180.;
+    const double gamma = fmod(gamma_in, kPi);
+    if (gamma >= 0.0 && gamma < 2. * THIRTY - EPS) {
+        const double cg = cos(gamma);
+        const double x1 = 1. - 1708. / (ra * cg);
+        const double a = (x1 + fabs(x1)) / 2.;
+        const double b = 1. - 1708. * pow(sin(1.8 * gamma), 1.6) / (ra * cg);
+        const double c = cbrt(ra * cg / 5830.) - 1.;
+        return 1. + 1.44 * a * b + (c + fabs(c)) / 2.;
+    } else if (gamma < 2. * THIRTY + EPS) {
+        return nu_60(ra, a_gi);
+    } else if (gamma < 3. * THIRTY - EPS) {
+        const double n60 = nu_60(ra, a_gi), n90 = nu_90(ra, a_gi);
+        const double x = (gamma - kPi / 3.) / (kPi / 2. - kPi / 3.);
+        return n60 + (n90 - n60) * x;
+    } else if (gamma < 3. * THIRTY + EPS) {
+        return nu_90(ra, a_gi);
+    } else if (gamma < 6. * THIRTY) {
+        return 1. + (nu_90(ra, a_gi) - 1.) * sin(gamma);
+    }
+    status |= ST_BAD_GAMMA;
+    return hb_nan();
+}
+// cavity.rs:59-69 + gas.rs:82-152
+HB_HD_NOINLINE double cavity_u(const CavityDev& c, double t_front, double t_back, int& status) {
+    const GasDev g = gas_of(c.gas);
+    double gamma = c.angle;
+    if (t_front > t_back) gamma = 180. * (kPi / 180.0) - gamma;
+    const double a_gi = c.height / c.thickness;
+    const double temp = ((t_front + 273.15) + (t_back + 273.15)) / 2.;
+    const double lambda = g.l0 + g.l1 * temp;
+    double ra;
+    if (fabs(t_front - t_back) < 1e-10) {
+        ra = 0.0000001;
+    } else {
+        const double beta = 1. / temp;
+        const double cp = g.c1 == 0. ? g.c0 : g.c0 + g.c1 * temp;
+        const double mu = g.m0 + g.m1 * temp;
+        const double rho = 101325. * g.mass / (8314.46261815324 * temp);
+        ra = (rho * rho) * ((c.thickness * c.thickness) * c.thickness) * 9.81 * beta * cp * fabs(t_front - t_back) /
+             (mu * lambda);
+    }
+    const double nu = nusselt(ra, gamma, a_gi, status);
+    const double conv = nu * lambda / c.thickness;
+    const double tm = (t_back + t_front) / 2. + 273.15;
+    const double rad = 4. * ((tm * tm) * tm) * kSigma * c.ein * c.eout / (1. - (1. - c.ein) * (1. - c.eout));
+    return rad + conv;
+}
+
+struct Face {
+    double air, trad, ts_env;  // ConvectionParams.air_temperature / rad_temperature / surface_temperature
+    double h;
+};
+
+// surface.rs:596-717: environment and film coefficient of both faces for given end-node temperatures.
+HB_HD void border(const WallC& c, const WallS& w, double ts_f, double ts_b, Face& F, Face& Bk, int& status) {
+    const double t_front = w.t_front, t_back = w.t_back;
+    if (c.kind_f == HB_BOUNDARY_OUTDOOR) {
+        F.air = t_front; F.trad = w.trad_out_f; F.ts_env = ts_f;
+        F.h = w.forced + tarp_natural(t_front, ts_f, -c.cos_tilt, c.c_same, c.c_opp);  // tilt flipped, surface.rs:652
+    } else {
+        F.air = c.kind_f == HB_BOUNDARY_SPACE ? t_front : c.amb_f; F.trad = t_front; F.ts_env = ts_f;
+        F.h = tarp_natural(F.air, ts_f, c.cos_tilt, c.c_same, c.c_opp);
+    }
+    if (c.kind_b == HB_BOUNDARY_OUTDOOR) {
+        Bk.air = t_back; Bk.trad = w.trad_out_b; Bk.ts_env = ts_b;
+        Bk.h = w.forced + tarp_natural(t_back, ts_b, c.cos_tilt, c.c_same, c.c_opp);
+    } else if (c.kind_b == HB_BOUNDARY_SPACE) {
+        Bk.air = t_back; Bk.trad = t_back; Bk.ts_env = ts_b;
+        Bk.h = tarp_natural(t_back, ts_b, c.cos_tilt, c.c_same, c.c_opp);
+    } else {
+        // surface.rs:672-685: the back AmbientTemperature arm is built from FRONT values
+        Bk.air = c.amb_b; Bk.trad = t_front; Bk.ts_env = ts_f;
+        Bk.h = tarp_natural(c.amb_b, ts_f, c.cos_tilt, c.c_same, c.c_opp);
+    }
+    if (F.h != F.h || Bk.h != Bk.h) status |= ST_NAN_H;  // surface.rs:704-707 (panic in the reference)
+    if (c.ov_f == c.ov_f) F.h = c.ov_f;                  // surface.rs:708-714 (debug-only overrides)
+    if (c.ov_b == c.ov_b) Bk.h = c.ov_b;
+}
+
+// Access to one wall's node temperatures and wall-major constant arrays from the scalar lane (TILE_EXT tiles).
+struct ExtWall {
+    double* t;           // this wall's row of the shared-memory temperature mirror: slot s at t[(s % kNL) * G + s / kNL]
+    double* a;           // same layout: coefficient A mirror (tiles with cavities)
+    double* b;
+    const double* u;     // wall-major: element of node i at [i * W]
+    const double* mass;
+    const double* af;
+    const double* ab;
+    int G, W;
+    HB_HD int at(int node) const { const int s = node + 1; return (s % kNL) * G + s / kNL; }
+    HB_HD double T(int node) const { return t[at(node)]; }
+    HB_HD void setT(int node, double v) const { t[at(node)] = v; }
+    HB_HD double link(int node) const { return u[(int64_t)node * W]; }
+    HB_HD double m(int node) const { return mass[(int64_t)node * W]; }
+};
+
+// One no-mass chunk [ini, fin): damped fixed point around a tridiagonal solve (surface.rs:790-898).
+// F/Bk are the border conditions evaluated with the previous sub-step's surface temperatures, hf/hb/rad_f/rad_b
+// the film and radiative coefficients derived from them.
+HB_HD_NOINLINE void solve_nomass(const WallC& c, WallS& w, const ExtWall& X, const CavityDev* cavs, int ini, int fin,
+                                 const Face& F, const Face& Bk, double hf, double hb, double rad_f, double rad_b,
+                                 double dt) {
+    (void)dt;
+    const int n = c.n;
+    const int m = fin - ini;
+    double tl[kMaxNomassChunk + 2];   // T[ini-1 .. fin]
+    double ul[kMaxNomassChunk + 1];   // links ini-1 .. fin-1
+    double sl[kMaxNomassChunk];       // absorbed solar per node
+    int cavl[kMaxNomassChunk + 1];
+    for (int j = 0; j < m + 2; ++j) {
+        const int node = ini - 1 + j;
+        tl[j] = (node >= 0 && node < n) ? X.T(node) : 0.;
+    }
+    for (int j = 0; j < m + 1; ++j) {
+        const int link = ini - 1 + j;
+        ul[j] = (link >= 0 && link < n - 1) ? X.link(link) : 0.;
+        cavl[j] = -1;
+        if (ul[j] < 0.)
+            for (int q = c.cav_begin; q < c.cav_end; ++q)
+                if (cavs[q].node == link) cavl[j] = q;
+    }
+    const bool dist = (c.flags >> 8) & 1;
+    for (int j = 0; j < m; ++j) {
+        const int node = ini + j;
+        if (dist)
+            sl[j] = X.af[(int64_t)node * X.W] * w.solar_front + X.ab[(int64_t)node * X.W] * w.solar_back;
+        else
+            sl[j] = (node == 0 ? c.af0 * w.solar_front : 0.) + (node == n - 1 ? c.abL * w.solar_back : 0.);
+    }
+    double old_err = 99999.;
+    int count = 0;
+    while (true) {
+        ++w.nm_iters;
+        // assemble (discretization.rs:622-697)
+        double dl[kMaxNomassChunk], dd[kMaxNomassChunk], du[kMaxNomassChunk], rhs[kMaxNomassChunk];
+        for (int j = 0; j < m; ++j) { dl[j] = 0.; dd[j] = 0.; du[j] = 0.; rhs[j] = 0.; }
+        for (int j = 0; j + 1 < m; ++j) {
+            double uu = ul[j + 1];
+            if (uu < 0.) uu = cavity_u(cavs[cavl[j + 1]], tl[j + 1], tl[j + 2], w.status);
+            dd[j] += -uu;
+            dd[j + 1] = dd[j + 1] - uu;
+            du[j] = du[j] + uu;
+            dl[j + 1] = dl[j + 1] + uu;
+        }
+        double hs_front, front_q;
+        if (ini == 0) {
+            front_q = F.air * hf + rad_f * (F.trad - tl[1]);
+            hs_front = hf;
+        } else {
+            double uu = ul[0];
+            if (uu < 0.) uu = cavity_u(cavs[cavl[0]], tl[0], tl[1], w.status);
+            hs_front = uu;
+            front_q = uu * tl[0];
+        }
+        rhs[0] += front_q;
+        dd[0] += -hs_front;
+        double hs_back, back_q;
+        if (fin == n) {
+            back_q = Bk.air * hb + rad_b * (Bk.trad - tl[m]);
+            hs_back = hb;
+        } else {
+            double uu = ul[m];
+            if (uu < 0.) uu = cavity_u(cavs[cavl[m]], tl[m], tl[m + 1], w.status);
+            hs_back = uu;
+            back_q = uu * tl[m + 1];
+        }
+        rhs[m - 1] += back_q;
+        dd[m - 1] += -hs_back;
+        for (int j = 0; j < m; ++j) rhs[j] = -(rhs[j] + sl[j]);  // surface.rs:828-832
+        // 3-diagonal Gaussian elimination without pivoting (surface.rs:834)
+        for (int j = 0; j + 1 < m; ++j) {
+            const double f = dl[j + 1] / dd[j];
+            dd[j + 1] -= f * du[j];
+            rhs[j + 1] -= f * rhs[j];
+        }
+        for (int j = m - 1; j >= 0; --j) {
+            double vv = rhs[j];
+            if (j + 1 < m) vv -= du[j] * rhs[j + 1];
+            rhs[j] = vv / dd[j];
+        }
+        double err = 0.0;
+        for (int j = 0; j < m; ++j) err += fabs(rhs[j] - tl[j + 1]);
+        if (err > old_err) break;                           // surface.rs:842-848
+        if (err != err) { w.status |= ST_NAN_ERR; break; }  // reference panics, :850
+        for (int j = 0; j < m; ++j) tl[j + 1] = (tl[j + 1] + rhs[j]) * 0.5;  // :878-883
+        const double tol = count < 100 ? 0.01 : 0.5;       // :885
+        if (err / (double)m < tol) break;
+        old_err = err;
+        ++count;
+        if (count > 100000) { w.status |= ST_ITER_CAP; break; }
+    }
+    for (int j = 0; j < m; ++j) X.setT(ini + j, tl[j + 1]);
+}
+
+// Main-step inputs → per-main-step derived quantities (surface.rs:916-931, 647, 692).
+HB_HD void begin_main_step(const WallC& c, WallS& w) {
+    double solar_front = w.sol_f;
+    if (solar_front != solar_front || solar_front < 0.0) solar_front = 0.0;  // surface.rs:916-919
+    double solar_back = w.sol_b;
+    if (solar_back != solar_back || w.sol_f < 0.0) solar_back = 0.0;          // surface.rs:920-923 (tests solar_front)
+    w.solar_front = solar_front;
+    w.solar_back = solar_back;
+    w.trad_out_f = sqrt(sqrt(w.ir_f / kSigma)) - 273.15;
+    w.trad_out_b = sqrt(sqrt(w.ir_b / kSigma)) - 273.15;
+    (void)c;
+}
+
+// Before the nodes march: weather → boundary temperatures → border conditions with the OLD surface temperatures
+// (surface.rs:939-948) → no-mass chunks / cavity links (TILE_EXT) → boundary links for the massive march.
+template <bool EXT>
+HB_HD void scalar_pre(const WallC& c, WallS& w, const SubWeather& sw, double zone_t_front, double zone_t_back,
+                      double dt, const ExtWall& X, const CavityDev* cavs, const int32_t* nm_pairs, BoundaryLinks& out) {
+    const bool any_outdoor = c.kind_f == HB_BOUNDARY_OUTDOOR || c.kind_b == HB_BOUNDARY_OUTDOOR;
+    double forced = 0.;
+    if (any_outdoor) {
+        bool windward = true;  // surface.rs:37-46
+        if (fabs(c.cos_tilt) < 0.98) windward = c.nx * sw.sin_wd + c.ny * sw.cos_wd > 0.0;
+        forced = c.forced_c * (windward ? 1.0 : 0.5) * sw.sqrt_ws;
+    }
+    w.forced = forced;
+    // boundary temperatures (model.rs:79-96)
+    w.t_front = c.kind_f == HB_BOUNDARY_SPACE ? zone_t_front : c.kind_f == HB_BOUNDARY_AMBIENT ? c.amb_f : sw.t_out;
+    w.t_back = c.kind_b == HB_BOUNDARY_SPACE ? zone_t_back : c.kind_b == HB_BOUNDARY_AMBIENT ? c.amb_b : sw.t_out;
+
+    Face F, Bk;
+    border(c, w, w.ts_f, w.ts_b, F, Bk, w.status);
+    const double hf = F.h, hb = Bk.h;
+    const double xr_f = 273.15 + (F.trad + F.ts_env) / 2.;
+    const double xr_b = 273.15 + (Bk.trad + Bk.ts_env) / 2.;
+    const double rad_f = 4. * c.eps_f * kSigma * ((xr_f * xr_f) * xr_f);
+    const double rad_b = 4. * c.eps_b * kSigma * ((xr_b * xr_b) * xr_b);
+
+    if (EXT) {
+        // no-mass chunks first (surface.rs:950-965)
+        for (int k = c.nm_begin; k < c.nm_end; ++k)
+            solve_nomass(c, w, X, cavs, nm_pairs[2 * k], nm_pairs[2 * k + 1], F, Bk, hf, hb, rad_f, rad_b, dt);
+        if (c.nm_end > c.nm_begin) {
+            w.ts_f = X.T(0);
+            w.ts_b = X.T(c.n - 1);
+        }
+        // cavity links: conductance at the assembly temperatures, scaled by dt/C of the two nodes
+        for (int q = c.cav_begin; q < c.cav_end; ++q) {
+            const CavityDev cv = cavs[q];
+            const int i = cv.node;
+            const double uu = cavity_u(cv, X.T(i), X.T(i + 1), w.status);
+            const double mi = X.m(i), mj = X.m(i + 1);
+            X.a[X.at(i)] = uu * (mi >= kMassiveThreshold ? dt / mi : 0.);
+            X.b[X.at(i + 1)] = uu * (mj >= kMassiveThreshold ? dt / mj : 0.);
+        }
+    }
+    // film coefficients as links to ghost nodes at the equivalent air temperature:
+    //   h·(T_air − T_s) + rad·(T_rad − T_s⁰) + q_solar  =  h·(T_ghost − T_s)        (discretization.rs:658-697)
+    // T_s⁰ is the surface temperature at assembly time: the radiative term is explicit in the reference.
+    const double hf_s = hf > 1e-12 ? hf : 1e-12, hb_s = hb > 1e-12 ? hb : 1e-12;
+    out.ghost_f = F.air + (rad_f * (F.trad - w.ts_f) + c.af0 * w.solar_front) / hf_s;
+    out.ghost_b = Bk.air + (rad_b * (Bk.trad - w.ts_b) + c.abL * w.solar_back) / hb_s;
+    out.bf = hf_s * c.v0;
+    out.ab = hb_s * c.vL;
+}
+
+// After the nodes marched: film coefficients with the NEW surface temperatures, convective flows
+// (model.rs:145-169) and this wall's contributions to calculate_zones_abc (model.rs:556-590).
+HB_HD void scalar_post(const WallC& c, WallS& w, double ts_f, double ts_b, double dt, double (&pub)[4]) {
+    w.ts_f = ts_f;
+    w.ts_b = ts_b;
+    Face F, Bk;
+    border(c, w, ts_f, ts_b, F, Bk, w.status);
+    w.h_f = F.h;
+    w.h_b = Bk.h;
+    w.flow_f = (ts_f - w.t_front) * w.h_f;
+    w.flow_b = (ts_b - w.t_back) * w.h_b;
+    w.e_f += w.flow_f * c.area * dt;
+    w.e_b += w.flow_b * c.area * dt;
+    pub[0] = w.h_f * c.area;
+    pub[1] = w.h_f * c.area * ts_f;
+    pub[2] = w.h_b * c.area;
+    pub[3] = w.h_b * c.area * ts_b;
+}
+
+struct ZoneC {
+    double vol, q, inf_v, inf_t, vent_v, vent_t;
+    int32_t sb, se;
+};
+
+// model.rs:489-597 + 650-674.  pub_* are the per-wall contributions of the tile, zf/zb the walls' zone indices.
+HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const double* pub_hA_f, const double* pub_hAT_f,
+                         const double* pub_hA_b, const double* pub_hAT_b, const int32_t* zf, const int32_t* zb) {
+    double a = 0.0, b = 0.0;
+    a += z.q;
+    if (z.inf_t == z.inf_t) {
+        const double tk = z.inf_t + 273.15;
+        const double cp = 1002.7370 + 1.2324e-2 * tk;
+        const double rho = 101325. * 28.97 / (8314.46261815324 * tk);
+        a += rho * z.inf_v * cp * z.inf_t;
+        b += rho * z.inf_v * cp;
+    }
+    if (z.vent_t == z.vent_t) {
+        const double tk = z.vent_t + 273.15;
+        const double cp = 1002.7370 + 1.2324e-2 * tk;
+        const double rho = 101325. * 28.97 / (8314.46261815324 * tk);
+        a += rho * z.vent_v * cp * z.vent_t;
+        b += rho * z.vent_v * cp;
+    }
+    const double tk = tz + 273.15;
+    const double cc = z.vol * (101325. * 28.97 / (8314.46261815324 * tk)) * (1002.7370 + 1.2324e-2 * tk) / 1.;
+    for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
+        if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
+        if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
+    }
+    double tn = tz;
+    if (fabs(b) > 1e-9) tn = a / b + (tz - a / b) * exp(-b * dt / cc);
+    return tn;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Massive nodes: classic RK4 on  Ṫ = C⁻¹(K·T + q)  (surface.rs:228-308) for one lane's kNL slots.
+// K and q are frozen during a sub-step, so the four stages collapse to
+//     T⁺ = T + p + M p/2 + M² p/6 + M³ p/24,   p = M·T (ghost nodes carry q),   M = diag(dt/C)·K,
+// evaluated as four tridiagonal sweeps in flux form  (M x)_i = A_i (x_{i+1} − x_i) − B_i (x_i − x_{i−1}).
+// `left`/`right` are the neighbouring lanes' edge values of x (halo); ghost and padding slots have A = B = 0.
+// ------------------------------------------------------------------------------------------------------------
+template <int NL>
+HB_HD void sweep_first(double (&T)[NL], double (&V)[NL], const double (&A)[NL], const double (&B)[NL], double left,
+                       double right) {
+    double dprev = T[0] - left;
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+        const double dnext = (i + 1 < NL ? T[i + 1 < NL ? i + 1 : i] : right) - T[i];
+        V[i] = A[i] * dnext - B[i] * dprev;
+        dprev = dnext;
+    }
+}
+template <int NL>
+HB_HD void sweep_next(double (&T)[NL], double (&V)[NL], const double (&A)[NL], const double (&B)[NL], double left,
+                      double right, double c) {
+    double dprev = V[0] - left;
+#pragma unroll
+    for (int i = 0; i < NL; ++i) {
+        const double dnext = (i + 1 < NL ? V[i + 1 < NL ? i + 1 : i] : right) - V[i];
+        V[i] = A[i] * dnext - B[i] * dprev;
+        dprev = dnext;
+        T[i] = fma(c, V[i], T[i]);
+    }
+}
+
+}  // namespace hb

@@ -1,0 +1,376 @@
+// emu.cc — TEST INFRASTRUCTURE: a sequential host re-enactment of hb_march_kernel's data flow.
+//
+// It calls the very same HB_HD functions the CUDA kernel calls (heat_b200/csrc/hb_math.cuh) on the very same packed
+// buffers (hb::pack_arrays), with the block barriers replaced by phase loops and the warp shuffles by array reads.
+// Purpose: debug the device arithmetic and the packing against the oracle on a machine without a GPU.  It is built
+// and used by tests/ only; the product (heat_b200/) never links or calls it and has no CPU path.
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "hb_math.cuh"
+
+using namespace hb;
+
+namespace {
+std::string g_err;
+
+void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* zone_rec_base) {
+    const int G = tile.G, W = tile.W, TPB = G * W, NL = kNL, ROW = G * NL + 1;
+    const bool EXT = tile.flags & TILE_EXT, DIST = tile.flags & TILE_DIST, has_cav = tile.flags & TILE_CAV;
+    const int S = tile.S;
+    const double dt = tile.dt;
+    const int64_t NS = V.n_dev_surfaces;
+    std::vector<double> T(TPB * NL), A(TPB * NL), B(TPB * NL), Vv(TPB * NL), Q(TPB * NL, 0.);
+    std::vector<double> sT(W * ROW, 0.), sA(W * ROW, 0.), sB(W * ROW, 0.);
+    std::vector<WallC> wc(W);
+    std::vector<ZoneC> zc(W);
+    std::vector<WallS> ws(W);
+    std::vector<ExtWall> xs(W);
+    std::vector<double> zT(W, 0.), pub0(W, 0.), pub1(W, 0.), pub2(W, 0.), pub3(W, 0.), ts0(W, 0.), ts1(W, 0.);
+    std::vector<int32_t> zf(W), zb(W);
+    std::vector<BoundaryLinks> bc(W, BoundaryLinks{0., 0., 0., 0.});
+    std::vector<SubWeather> swt(kMaxSubsteps);
+    std::vector<double> ir_state(W, 0.);
+
+    auto rowof = [&](int tid) { return (tid / G) * ROW + tid % G; };
+    for (int tid = 0; tid < TPB; ++tid)
+        for (int i = 0; i < NL; ++i) {
+            const int64_t o = tile.node_offset + (int64_t)i * TPB + tid;
+            T[tid * NL + i] = V.nodeT[o];
+            A[tid * NL + i] = V.coefA[o];
+            B[tid * NL + i] = V.coefB[o];
+            sT[rowof(tid) + i * G] = V.nodeT[o];
+            sA[rowof(tid) + i * G] = V.coefA[o];
+            sB[rowof(tid) + i * G] = V.coefB[o];
+        }
+    for (int t = 0; t < W; ++t) {
+        const int64_t sg = (int64_t)tile.surface_begin + t;
+        WallC c{};
+        c.area = V.area[sg]; c.cos_tilt = V.cos_tilt[sg];
+        const double act = fabs(c.cos_tilt);
+        c.c_same = 9.482 / (7.238 - act); c.c_opp = 1.81 / (1.382 + act);
+        c.forced_c = V.forced_c[sg]; c.eps_f = V.eps_f[sg]; c.eps_b = V.eps_b[sg];
+        c.amb_f = V.amb_f[sg]; c.amb_b = V.amb_b[sg]; c.ov_f = V.hs_ov_f[sg]; c.ov_b = V.hs_ov_b[sg];
+        c.nx = V.nx[sg]; c.ny = V.ny[sg]; c.af0 = V.af0[sg]; c.abL = V.abL[sg]; c.v0 = V.v0[sg]; c.vL = V.vL[sg];
+        c.n = V.n_nodes[sg]; c.flags = V.flags[sg];
+        c.kind_f = c.flags & 15; c.kind_b = (c.flags >> 4) & 15;
+        c.zf = V.zone_f[sg]; c.zb = V.zone_b[sg]; c.site = P.single_site ? 0 : V.site[sg];
+        c.nm_begin = V.nm_off[sg]; c.nm_end = V.nm_off[sg + 1];
+        c.cav_begin = V.cav_off[sg]; c.cav_end = V.cav_off[sg + 1];
+        c.desc_index = V.desc_index[sg];
+        wc[t] = c;
+        zf[t] = c.zf;
+        zb[t] = c.zb;
+        const int64_t gz = (int64_t)tile.zone_begin + t;
+        ZoneC z{};
+        if (t < tile.n_zones) {
+            z.vol = V.zvol[gz]; z.q = V.zq[gz]; z.inf_v = V.zinf_v[gz]; z.inf_t = V.zinf_t[gz];
+            z.vent_v = V.zvent_v[gz]; z.vent_t = V.zvent_t[gz]; z.sb = V.z_surf_begin[gz]; z.se = V.z_surf_end[gz];
+            zT[t] = V.zoneT[gz];
+        }
+        zc[t] = z;
+    }
+    auto publish_ends = [&]() {
+        for (int tid = 0; tid < TPB; ++tid) {
+            const int wl = tid / G, part = tid % G;
+            const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
+            if (part == 0) ts0[wl] = T[tid * NL + 1];
+            for (int i = 0; i < NL; ++i)
+                if (i == n - part * NL) ts1[wl] = T[tid * NL + i];
+        }
+    };
+    publish_ends();
+    for (int t = 0; t < W; ++t) {
+        const int64_t sg = (int64_t)tile.surface_begin + t;
+        WallS w{};
+        if (wc[t].n > 0) {
+            w.h_f = V.sc[0 * NS + sg]; w.h_b = V.sc[1 * NS + sg]; w.flow_f = V.sc[2 * NS + sg]; w.flow_b = V.sc[3 * NS + sg];
+            w.sol_f = V.sc[4 * NS + sg]; w.sol_b = V.sc[5 * NS + sg]; w.ir_f = V.sc[6 * NS + sg]; w.ir_b = V.sc[7 * NS + sg];
+            w.ts_f = ts0[t];
+            w.ts_b = ts1[t];
+        }
+        ir_state[t] = w.ir_f;
+        ws[t] = w;
+        ExtWall X{};
+        if (EXT) {
+            X.t = sT.data() + t * ROW; X.a = sA.data() + t * ROW; X.b = sB.data() + t * ROW;
+            X.u = V.ext_u + tile.ext_offset + t; X.mass = V.ext_mass + tile.ext_offset + t;
+            X.af = V.ext_af + tile.ext_offset + t; X.ab = V.ext_ab + tile.ext_offset + t;
+            X.G = G; X.W = W;
+        }
+        xs[t] = X;
+    }
+
+    auto weather_at = [&](int site, int step, int s, SubWeather& out) {
+        const double* wtab = P.weather + (int64_t)site * P.weather_rows * 3;
+        const double* w0 = wtab + (int64_t)step * 3;
+        double t_out, wdir, wspeed;
+        if (P.weather_mode == HB_WEATHER_LINEAR) {
+            const double f = (double)(s + 1) / (double)S;
+            t_out = w0[0] + (w0[3] - w0[0]) * f;
+            wdir = w0[1] + (w0[4] - w0[1]) * f;
+            wspeed = w0[2] + (w0[5] - w0[2]) * f;
+        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+            w0 = wtab + ((int64_t)step * S + s) * 3;
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        } else {
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        }
+        sub_weather(t_out, wdir, wspeed, out);
+    };
+
+    int rec = 0;
+    std::vector<double> left(TPB), right(TPB);
+    for (int step = 0; step < P.n_steps; ++step) {
+        if (P.single_site)
+            for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
+        for (int t = 0; t < W; ++t) {
+            const WallC& c = wc[t];
+            if (c.n == 0) continue;
+            WallS& w = ws[t];
+            if (P.input_mode == HB_INPUT_SITE) {
+                const double* in = P.inputs + ((int64_t)c.site * P.n_steps + step) * 4;
+                w.sol_f = in[0]; w.sol_b = in[1]; w.ir_f = in[2]; w.ir_b = in[3];
+            } else if (P.input_mode == HB_INPUT_PER_SURFACE) {
+                const double* in = P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
+                w.sol_f = in[0]; w.sol_b = in[1]; w.ir_f = in[2]; w.ir_b = in[3];
+            }
+            if (P.input_mode != HB_INPUT_STATE && P.ir_mode == HB_IR_NET_GAIN) {
+                if (c.eps_f > 1e-3) {
+                    const double tk = w.ts_f + 273.15;
+                    const double tk2 = tk * tk;
+                    w.ir_f = w.ir_f / c.area / c.eps_f + kSigma * (tk2 * tk2);
+                } else {
+                    w.ir_f = ir_state[t];
+                }
+            }
+            begin_main_step(c, w);
+        }
+        if (DIST)
+            for (int tid = 0; tid < TPB; ++tid) {
+                const int wl = tid / G, part = tid % G;
+                const int64_t g = (int64_t)tile.surface_begin + wl;
+                const int n = V.n_nodes[g];
+                const bool wall_dist = (V.flags[g] >> 8) & 1;
+                for (int i = 0; i < NL; ++i) {
+                    Q[tid * NL + i] = 0.;
+                    const int node = part * NL + i - 1;
+                    if (wall_dist && node >= 0 && node < n) {
+                        const int64_t e = tile.ext_offset + (int64_t)node * W + wl;
+                        const double m = V.ext_mass[e];
+                        const double vi = m >= kMassiveThreshold ? dt / m : 0.;
+                        Q[tid * NL + i] = vi * (V.ext_af[e] * ws[wl].solar_front + V.ext_ab[e] * ws[wl].solar_back);
+                    }
+                }
+            }
+        for (int s = 0; s < S; ++s) {
+            for (int t = 0; t < W; ++t) {
+                const WallC& c = wc[t];
+                if (c.n == 0) continue;
+                SubWeather sw;
+                if (P.single_site) sw = swt[s];
+                else weather_at(c.site, step, s, sw);
+                const double ztf = c.zf >= 0 ? zT[c.zf] : 0.;
+                const double ztb = c.zb >= 0 ? zT[c.zb] : 0.;
+                if (EXT) scalar_pre<true>(c, ws[t], sw, ztf, ztb, dt, xs[t], V.cav, V.nm_pairs, bc[t]);
+                else scalar_pre<false>(c, ws[t], sw, ztf, ztb, dt, xs[t], V.cav, V.nm_pairs, bc[t]);
+            }
+            // ---- node role ----
+            for (int tid = 0; tid < TPB; ++tid) {
+                const int wl = tid / G, part = tid % G;
+                const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
+                double* t = &T[tid * NL];
+                if (EXT) {
+                    for (int i = 0; i < NL; ++i) t[i] = sT[rowof(tid) + i * G];
+                    if (has_cav)
+                        for (int i = 0; i < NL; ++i) {
+                            A[tid * NL + i] = sA[rowof(tid) + i * G];
+                            B[tid * NL + i] = sB[rowof(tid) + i * G];
+                        }
+                }
+                const BoundaryLinks bl = bc[wl];
+                if (part == 0) {
+                    t[0] = bl.ghost_f;
+                    B[tid * NL + 1] = bl.bf;
+                }
+                for (int i = 0; i < NL; ++i) {
+                    if (i == n - part * NL) A[tid * NL + i] = bl.ab;
+                    if (i == n + 1 - part * NL) t[i] = bl.ghost_b;
+                }
+            }
+            auto halos = [&](const std::vector<double>& x) {
+                for (int tid = 0; tid < TPB; ++tid) {
+                    const int part = tid % G;
+                    left[tid] = part > 0 ? x[(tid - 1) * NL + NL - 1] : x[tid * NL + NL - 1];
+                    right[tid] = part < G - 1 ? x[(tid + 1) * NL] : x[tid * NL];
+                }
+            };
+            using Arr = double(&)[kNL];
+            halos(T);
+            for (int tid = 0; tid < TPB; ++tid) {
+                sweep_first<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid], right[tid]);
+                for (int i = 0; i < NL; ++i) {
+                    if (DIST) Vv[tid * NL + i] += Q[tid * NL + i];
+                    T[tid * NL + i] += Vv[tid * NL + i];
+                }
+            }
+            const double cs[3] = {1. / 2., 1. / 6., 1. / 24.};
+            for (int k = 0; k < 3; ++k) {
+                halos(Vv);
+                for (int tid = 0; tid < TPB; ++tid)
+                    sweep_next<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid],
+                                    right[tid], cs[k]);
+            }
+            if (EXT) {
+                for (int tid = 0; tid < TPB; ++tid)
+                    for (int i = 0; i < NL; ++i) sT[rowof(tid) + i * G] = T[tid * NL + i];
+            } else {
+                publish_ends();
+            }
+            // ---- scalar role, after ----
+            for (int t = 0; t < W; ++t) {
+                const WallC& c = wc[t];
+                if (c.n == 0) continue;
+                double ts_f, ts_b;
+                if (EXT) {
+                    ts_f = xs[t].T(0);
+                    ts_b = xs[t].T(c.n - 1);
+                } else {
+                    ts_f = ts0[t];
+                    ts_b = ts1[t];
+                }
+                double pub[4];
+                scalar_post(c, ws[t], ts_f, ts_b, dt, pub);
+                pub0[t] = pub[0]; pub1[t] = pub[1]; pub2[t] = pub[2]; pub3[t] = pub[3];
+            }
+            std::vector<double> znew(zT);
+            for (int t = 0; t < tile.n_zones; ++t) {
+                const double tn = zone_update(zc[t], t, zT[t], dt, pub0.data(), pub1.data(), pub2.data(), pub3.data(),
+                                              zf.data(), zb.data());
+                if (tn != tn) V.status[(int64_t)tile.surface_begin + zc[t].sb] |= ST_NAN_ZONE;
+                znew[t] = tn;
+            }
+            zT = znew;
+        }
+        if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
+            if (zone_rec_base)
+                for (int t = 0; t < tile.n_zones; ++t)
+                    zone_rec_base[(int64_t)rec * V.n_dev_zones + tile.zone_begin + t] = zT[t];
+            if (P.node_rec) {
+                for (int tid = 0; tid < TPB; ++tid)
+                    for (int i = 0; i < NL; ++i)
+                        P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * TPB + tid] = T[tid * NL + i];
+                for (int t = 0; t < W; ++t) {
+                    if (wc[t].n == 0) continue;
+                    const int64_t sg = (int64_t)tile.surface_begin + t;
+                    const WallS& w = ws[t];
+                    double* r = P.sc_rec + (int64_t)rec * 8 * NS;
+                    r[0 * NS + sg] = w.h_f; r[1 * NS + sg] = w.h_b; r[2 * NS + sg] = w.flow_f; r[3 * NS + sg] = w.flow_b;
+                    r[4 * NS + sg] = w.sol_f; r[5 * NS + sg] = w.sol_b; r[6 * NS + sg] = w.ir_f; r[7 * NS + sg] = w.ir_b;
+                }
+            }
+            ++rec;
+        }
+    }
+    for (int tid = 0; tid < TPB; ++tid)
+        for (int i = 0; i < NL; ++i) V.nodeT[tile.node_offset + (int64_t)i * TPB + tid] = T[tid * NL + i];
+    for (int t = 0; t < W; ++t) {
+        if (wc[t].n == 0) continue;
+        const int64_t sg = (int64_t)tile.surface_begin + t;
+        const WallS& w = ws[t];
+        V.sc[0 * NS + sg] = w.h_f; V.sc[1 * NS + sg] = w.h_b; V.sc[2 * NS + sg] = w.flow_f; V.sc[3 * NS + sg] = w.flow_b;
+        V.sc[4 * NS + sg] = w.sol_f; V.sc[5 * NS + sg] = w.sol_b; V.sc[6 * NS + sg] = w.ir_f; V.sc[7 * NS + sg] = w.ir_b;
+        V.energy_f[sg] += w.e_f;
+        V.energy_b[sg] += w.e_b;
+        V.nm_iters[sg] += w.nm_iters;
+        V.status[sg] |= w.status;
+    }
+    for (int t = 0; t < tile.n_zones; ++t) V.zoneT[(int64_t)tile.zone_begin + t] = zT[t];
+}
+}  // namespace
+
+extern "C" {
+
+const char* emu_last_error() { return g_err.c_str(); }
+
+// state: in/out, reference layout (NULL-initialised state = the initial values).  zone inputs may be NULL.
+// zone_record [n_rec][zones], state_record [n_rec][state_len] may be NULL.  Returns 0 on success.
+int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, const double* q_internal,
+            const double* inf_v, const double* inf_t, const double* vent_v, const double* vent_t,
+            const hb_series* s, long long* nomass_iterations, long long* status_or) {
+    try {
+        BatchPlan B;
+        plan_batch(desc, B);
+        HostArrays H;
+        pack_arrays(B, H);
+        if (!use_initial_state) scatter_state(B, state, H.nodeT.data(), H.sc.data(), H.zoneT.data());
+        auto scatter = [&](const double* src, std::vector<double>& dst) {
+            if (src)
+                for (size_t z = 0; z < B.dev_zone_of.size(); ++z) dst[B.dev_zone_of[z]] = src[z];
+        };
+        scatter(q_internal, H.zq); scatter(inf_v, H.zinf_v); scatter(inf_t, H.zinf_t);
+        scatter(vent_v, H.zvent_v); scatter(vent_t, H.zvent_t);
+        bool single = true;
+        if (s->model_site)
+            for (size_t gd = 0; gd < B.dev_surface_of.size(); ++gd) {
+                H.site[B.dev_surface_of[gd]] = s->model_site[B.surface_model[gd]];
+                if (s->model_site[B.surface_model[gd]] != 0) single = false;
+            }
+        DevView V = H.view(B);
+        SeriesDev P{};
+        P.n_steps = s->n_steps; P.weather_mode = s->weather_mode; P.input_mode = s->input_mode; P.ir_mode = s->ir_mode;
+        P.weather = s->weather; P.weather_rows = s->weather_rows; P.inputs = s->inputs;
+        P.n_desc_surfaces = (int64_t)B.surfaces.size();
+        P.single_site = single ? 1 : 0;
+        P.slab_len = B.node_slab_len;
+        const int n_rec = s->record_every > 0 ? s->n_steps / s->record_every : 0;
+        std::vector<double> zr, nr, sr;
+        P.record_every = n_rec > 0 && (s->zone_t_record || s->state_record) ? s->record_every : 0;
+        if (P.record_every) {
+            zr.resize((size_t)n_rec * B.n_dev_zones);
+            if (s->state_record) {
+                nr.resize((size_t)n_rec * B.node_slab_len);
+                sr.resize((size_t)n_rec * 8 * B.n_dev_surfaces);
+                P.node_rec = nr.data();
+                P.sc_rec = sr.data();
+            }
+        }
+        for (const Tile& t : B.tiles) march_tile(V, P, t, zr.empty() ? nullptr : zr.data());
+        if (P.record_every) {
+            const int64_t nz_total = (int64_t)B.zone_volume.size();
+            for (int r = 0; r < n_rec; ++r) {
+                const double* z = zr.data() + (size_t)r * B.n_dev_zones;
+                if (s->zone_t_record)
+                    for (int64_t k = 0; k < nz_total; ++k) s->zone_t_record[(int64_t)r * nz_total + k] = z[B.dev_zone_of[k]];
+                if (s->state_record)
+                    gather_state(B, nr.data() + (size_t)r * B.node_slab_len, sr.data() + (size_t)r * 8 * B.n_dev_surfaces, z,
+                                 s->state_record + (int64_t)r * B.state_len_total);
+            }
+        }
+        gather_state(B, H.nodeT.data(), H.sc.data(), H.zoneT.data(), state);
+        long long it = 0, st = 0;
+        for (auto v : H.nm_iters) it += (long long)v;
+        for (auto v : H.status) st |= v;
+        if (nomass_iterations) *nomass_iterations = it;
+        if (status_or) *status_or = st;
+        return 0;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+long long emu_state_len(const hb_batch_desc* desc) {
+    try {
+        BatchPlan B;
+        plan_batch(desc, B);
+        return B.state_len_total;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+}
