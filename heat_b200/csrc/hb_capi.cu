@@ -300,7 +300,7 @@ hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) 
     *out = nullptr;
     std::unique_ptr<hb_handle> h(new hb_handle());
     hb_status rc = guarded([&] {
-        hb::plan_batch(desc, h->plan);
+        hb::plan_batch(desc, h->plan, device != HB_DEVICE_NONE);
         if (device == HB_DEVICE_NONE) {  // host-only planning handle: layout queries work, marching does not
             h->device = HB_DEVICE_NONE;
             return;

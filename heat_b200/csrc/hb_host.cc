@@ -264,7 +264,7 @@ void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int
     P.wind_speed_modifier = wind_modifier(s.centroid_z, terrain);
 }
 
-void plan_batch(const hb_batch_desc* d, BatchPlan& B) {
+void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
     if (d->steps_per_hour <= 0) fail("steps_per_hour must be positive");
     if (d->n_models <= 0) fail("batch has no models");
@@ -335,6 +335,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B) {
         B.updates_per_step += M.nodes * (int64_t)M.dt_subdivisions;
     }
     B.state_len_total = state;
+    if (!build_tiles) return;   // host-only planning handle: discretization and state layout only
 
     // ---- device ordering --------------------------------------------------------------------------------
     // Every model goes, whole, into one tile (its surfaces couple through its zones every sub-step).  Tiles are

@@ -135,6 +135,6 @@ struct BatchPlan {
 // Host discretization + planning (hb_host.cc). Throws std::runtime_error with the reference-style message.
 void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int terrain, double main_dt,
                   SurfacePlan& out);
-void plan_batch(const hb_batch_desc* desc, BatchPlan& out);
+void plan_batch(const hb_batch_desc* desc, BatchPlan& out, bool build_tiles = true);
 
 }  // namespace hb

@@ -63,6 +63,26 @@ struct SubWeather {
     double t_out, sqrt_ws, sin_wd, cos_wd;
 };
 
+// Products and sums that feed a DISCONTINUOUS decision (the windward test) are rounded separately, as the reference
+// does (Rust never contracts a*b+c): with an FMA, 300° + (0° − 300°)·0.7 is 90.00000000000001° instead of 90°, which
+// flips cos(wind direction) from +6e-17 to −1e-14 and with it the forced-convection factor of a south wall.
+HB_HD double mul_rn(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dmul_rn(a, b);
+#else
+    return a * b;
+#endif
+}
+HB_HD double add_rn(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dadd_rn(a, b);
+#else
+    return a + b;
+#endif
+}
+// row0 + (row1 − row0)·f with every operation rounded (model.rs:371-382 samples the weather at the sub-step's end)
+HB_HD double lerp_rn(double a, double b, double f) { return add_rn(a, mul_rn(add_rn(b, -a), f)); }
+
 HB_HD void sub_weather(double t_out, double wdir_deg, double wspeed, SubWeather& w) {
     w.t_out = t_out;
     w.sqrt_ws = sqrt(wspeed);
@@ -344,7 +364,7 @@ HB_HD void scalar_pre(const WallC& c, WallS& w, const SubWeather& sw, double zon
     double forced = 0.;
     if (any_outdoor) {
         bool windward = true;  // surface.rs:37-46
-        if (fabs(c.cos_tilt) < 0.98) windward = c.nx * sw.sin_wd + c.ny * sw.cos_wd > 0.0;
+        if (fabs(c.cos_tilt) < 0.98) windward = add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0;
         forced = c.forced_c * (windward ? 1.0 : 0.5) * sw.sqrt_ws;
     }
     w.forced = forced;

@@ -110,9 +110,9 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
         double t_out, wdir, wspeed;
         if (P.weather_mode == HB_WEATHER_LINEAR) {
             const double f = (double)(s + 1) / (double)S;
-            t_out = w0[0] + (w0[3] - w0[0]) * f;
-            wdir = w0[1] + (w0[4] - w0[1]) * f;
-            wspeed = w0[2] + (w0[5] - w0[2]) * f;
+            t_out = lerp_rn(w0[0], w0[3], f);
+            wdir = lerp_rn(w0[1], w0[4], f);
+            wspeed = lerp_rn(w0[2], w0[5], f);
         } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
             w0 = wtab + ((int64_t)step * S + s) * 3;
             t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
