@@ -28,7 +28,7 @@ namespace hb {
 constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2;
 
 template <int G, int W, int VAR>
-__global__ void __launch_bounds__(G* W) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+__global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     constexpr int TPB = G * W;
     constexpr int NL = kNL;
     constexpr bool EXT = VAR >= kVarExt, DIST = VAR == kVarDist;
@@ -88,18 +88,7 @@ __global__ void __launch_bounds__(G* W) hb_march_kernel(DevView V, SeriesDev P, 
     if (tid < W) {
         const int64_t sg = (int64_t)tile.surface_begin + tid;
         WallC c;
-        c.area = V.area[sg]; c.cos_tilt = V.cos_tilt[sg];
-        const double act = fabs(c.cos_tilt);
-        c.c_same = 9.482 / (7.238 - act); c.c_opp = 1.81 / (1.382 + act);
-        c.forced_c = V.forced_c[sg]; c.eps_f = V.eps_f[sg]; c.eps_b = V.eps_b[sg];
-        c.amb_f = V.amb_f[sg]; c.amb_b = V.amb_b[sg]; c.ov_f = V.hs_ov_f[sg]; c.ov_b = V.hs_ov_b[sg];
-        c.nx = V.nx[sg]; c.ny = V.ny[sg]; c.af0 = V.af0[sg]; c.abL = V.abL[sg]; c.v0 = V.v0[sg]; c.vL = V.vL[sg];
-        c.n = V.n_nodes[sg]; c.flags = V.flags[sg];
-        c.kind_f = c.flags & 15; c.kind_b = (c.flags >> 4) & 15;
-        c.zf = V.zone_f[sg]; c.zb = V.zone_b[sg]; c.site = P.single_site ? 0 : V.site[sg];
-        c.nm_begin = V.nm_off[sg]; c.nm_end = V.nm_off[sg + 1];
-        c.cav_begin = V.cav_off[sg]; c.cav_end = V.cav_off[sg + 1];
-        c.desc_index = V.desc_index[sg];
+        load_wallc(V, sg, P.single_site != 0, c);
         s_wc[tid] = c;
         s_zf[tid] = c.zf;
         s_zb[tid] = c.zb;

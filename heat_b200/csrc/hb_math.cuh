@@ -34,12 +34,60 @@ HB_HD double hb_nan() {
 #endif
 }
 
-// Per-wall constants (shared memory in the kernel).
-struct WallC {
-    double area, cos_tilt, c_same, c_opp, forced_c, eps_f, eps_b, amb_f, amb_b, ov_f, ov_b, nx, ny, af0, abL, v0, vL;
-    int32_t n, kind_f, kind_b, zf, zb, site, nm_begin, nm_end, cav_begin, cav_end, flags, desc_index;
-    int32_t pad_[2];   // sizeof == 17*8 + 14*4 = 192 … keep 8-byte multiples
+// Per-wall constants (shared memory in the kernel), derived once per launch by load_wallc().
+enum : int32_t {
+    WF_F_OUT = 1, WF_F_SPACE = 2, WF_B_OUT = 4, WF_B_SPACE = 8, WF_B_AMB = 16, WF_TILTED = 32, WF_ANY_OUT = 64,
+    WF_DIST = 128, WF_OV_F = 256, WF_OV_B = 512,
 };
+struct WallC {
+    double area, cos_tilt, forced_c, eps_f, eps4s_f, eps4s_b, amb_f, amb_b, ov_f, ov_b, nx, ny, af0, abL, v0, vL;
+    // TARP natural-convection factor by sign of (T_air − T_surface), per face (convection.rs:91-100 with the
+    // face's signed cos(tilt) folded in; 1.31 for a vertical face)
+    double kpos_f, kneg_f, kpos_b, kneg_b;
+    int32_t n, fl, zf, zb, site, nm_begin, nm_end, cav_begin, cav_end, desc_index;
+};
+static_assert(sizeof(WallC) % 8 == 0, "WallC is copied as doubles");
+
+HB_HD void load_wallc(const DevView& V, int64_t sg, bool single_site, WallC& c) {
+    c.area = V.area[sg];
+    c.cos_tilt = V.cos_tilt[sg];
+    c.forced_c = V.forced_c[sg];
+    c.eps_f = V.eps_f[sg];
+    c.eps4s_f = 4. * V.eps_f[sg] * kSigma;   // surface.rs:941-948: 4·ε·σ·T³ evaluated left to right
+    c.eps4s_b = 4. * V.eps_b[sg] * kSigma;
+    c.amb_f = V.amb_f[sg]; c.amb_b = V.amb_b[sg];
+    c.ov_f = V.hs_ov_f[sg]; c.ov_b = V.hs_ov_b[sg];
+    c.nx = V.nx[sg]; c.ny = V.ny[sg];
+    c.af0 = V.af0[sg]; c.abL = V.abL[sg]; c.v0 = V.v0[sg]; c.vL = V.vL[sg];
+    c.n = V.n_nodes[sg];
+    const int flags = V.flags[sg];
+    const int kind_f = flags & 15, kind_b = (flags >> 4) & 15;
+    int fl = 0;
+    if (kind_f == HB_BOUNDARY_OUTDOOR) fl |= WF_F_OUT | WF_ANY_OUT;
+    if (kind_f == HB_BOUNDARY_SPACE) fl |= WF_F_SPACE;
+    if (kind_b == HB_BOUNDARY_OUTDOOR) fl |= WF_B_OUT | WF_ANY_OUT;
+    if (kind_b == HB_BOUNDARY_SPACE) fl |= WF_B_SPACE;
+    if (kind_b == HB_BOUNDARY_AMBIENT) fl |= WF_B_AMB;
+    const double act = fabs(c.cos_tilt);
+    if (act < 0.98) fl |= WF_TILTED;       // surface.rs:38
+    if ((flags >> 8) & 1) fl |= WF_DIST;
+    if (c.ov_f == c.ov_f) fl |= WF_OV_F;
+    if (c.ov_b == c.ov_b) fl |= WF_OV_B;
+    c.fl = fl;
+    const double c_same = 9.482 / (7.238 - act), c_opp = 1.81 / (1.382 + act);
+    const double tilt_f = (fl & WF_F_OUT) ? -c.cos_tilt : c.cos_tilt;   // front Outdoor flips the tilt, surface.rs:652
+    const double tilt_b = c.cos_tilt;
+    const bool flat = act < 1e-3;
+    c.kpos_f = flat ? 1.31 : tilt_f > 0. ? c_same : c_opp;
+    c.kneg_f = flat ? 1.31 : tilt_f < 0. ? c_same : c_opp;
+    c.kpos_b = flat ? 1.31 : tilt_b > 0. ? c_same : c_opp;
+    c.kneg_b = flat ? 1.31 : tilt_b < 0. ? c_same : c_opp;
+    c.zf = V.zone_f[sg]; c.zb = V.zone_b[sg];
+    c.site = single_site ? 0 : V.site[sg];
+    c.nm_begin = V.nm_off[sg]; c.nm_end = V.nm_off[sg + 1];
+    c.cav_begin = V.cav_off[sg]; c.cav_end = V.cav_off[sg + 1];
+    c.desc_index = V.desc_index[sg];
+}
 
 // Per-wall dynamic scalar state (registers of the scalar lane).
 struct WallS {
@@ -83,6 +131,37 @@ HB_HD double add_rn(double a, double b) {
 // row0 + (row1 − row0)·f with every operation rounded (model.rs:371-382 samples the weather at the sub-step's end)
 HB_HD double lerp_rn(double a, double b, double f) { return add_rn(a, mul_rn(add_rn(b, -a), f)); }
 
+// ---- short-latency device arithmetic for the scalar lane (it is the block's critical path) -------------------
+// 1/x: MUFU.RCP64H seed (2^-23) + two Newton steps, no special-case branch (x is a positive, normal number here).
+HB_HD double fast_rcp(double x) {
+#if defined(__CUDA_ARCH__)
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
+#else
+    return 1.0 / x;
+#endif
+}
+// x^(1/3) for x >= 0: single-precision seed 2^(log2(x)/3) + two Newton steps with a frozen derivative (error
+// contracts by ~4e-6 per step -> < 1 ulp).  Below 1e-24 the result only ever feeds MIN_H-clamped coefficients.
+HB_HD double fast_cbrt(double x) {
+#if defined(__CUDA_ARCH__)
+    if (!(x >= 1e-24)) return x != x ? x : 0.0;
+    const float xf = (float)x;
+    const float yf = exp2f(__log2f(xf) * 0.33333334f);
+    const double y0 = (double)yf;
+    double w;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(w) : "d"(3.0 * y0 * y0));
+    double y = fma(-fma(y0 * y0, y0, -x), w, y0);
+    y = fma(-fma(y * y, y, -x), w, y);
+    return y;
+#else
+    return cbrt(x);
+#endif
+}
+
 HB_HD void sub_weather(double t_out, double wdir_deg, double wspeed, SubWeather& w) {
     w.t_out = t_out;
     w.sqrt_ws = sqrt(wspeed);
@@ -95,19 +174,14 @@ HB_HD void sub_weather(double t_out, double wdir_deg, double wspeed, SubWeather&
 #endif
 }
 
-// convection.rs:87-110 with the per-surface constants 9.482/(7.238-|cosΣ|) and 1.81/(1.382+|cosΣ|) hoisted.
-HB_HD double tarp_natural(double t_air, double t_surf, double tilt, double c_same, double c_opp) {
+// convection.rs:87-110: h = k·|ΔT|^(1/3), k = 1.31 | 9.482/(7.238−|cosΣ|) | 1.81/(1.382+|cosΣ|) by the signs of ΔT and
+// of the face's cos(tilt) (kpos/kneg, load_wallc), clamped at MIN_H = 0.1 (convection.rs:22).  NaN propagates.
+HB_HD double tarp_natural(double t_air, double t_surf, double kpos, double kneg) {
     const double d = t_air - t_surf;
     const double ad = fabs(d);
-    const double r = cbrt(ad);
-    double h;
-    if (ad < 1e-3 || fabs(tilt) < 1e-3)
-        h = 1.31 * r;
-    else if ((d < 0. && tilt < 0.) || (d > 0. && tilt > 0.))
-        h = c_same * r;
-    else
-        h = c_opp * r;
-    return h < 0.1 ? 0.1 : h;  // MIN_H, convection.rs:22; NaN propagates and is flagged by the caller
+    const double k = ad < 1e-3 ? 1.31 : d > 0. ? kpos : kneg;
+    const double h = k * fast_cbrt(ad);
+    return h < 0.1 ? 0.1 : h;
 }
 
 // gas.rs:45-74 — ascending-power polynomials in T[K]
@@ -202,29 +276,24 @@ struct Face {
 };
 
 // surface.rs:596-717: environment and film coefficient of both faces for given end-node temperatures.
+//   front: air = t_front; Outdoor → T_rad from the IR irradiance, forced + natural; Space/Ambient → T_rad = t_front.
+//   back : same with t_back, except the AmbientTemperature arm, which the reference builds from FRONT values
+//          (surface.rs:672-685): T_rad = t_front, surface temperature = front node.
 HB_HD void border(const WallC& c, const WallS& w, double ts_f, double ts_b, Face& F, Face& Bk, int& status) {
-    const double t_front = w.t_front, t_back = w.t_back;
-    if (c.kind_f == HB_BOUNDARY_OUTDOOR) {
-        F.air = t_front; F.trad = w.trad_out_f; F.ts_env = ts_f;
-        F.h = w.forced + tarp_natural(t_front, ts_f, -c.cos_tilt, c.c_same, c.c_opp);  // tilt flipped, surface.rs:652
-    } else {
-        F.air = c.kind_f == HB_BOUNDARY_SPACE ? t_front : c.amb_f; F.trad = t_front; F.ts_env = ts_f;
-        F.h = tarp_natural(F.air, ts_f, c.cos_tilt, c.c_same, c.c_opp);
-    }
-    if (c.kind_b == HB_BOUNDARY_OUTDOOR) {
-        Bk.air = t_back; Bk.trad = w.trad_out_b; Bk.ts_env = ts_b;
-        Bk.h = w.forced + tarp_natural(t_back, ts_b, c.cos_tilt, c.c_same, c.c_opp);
-    } else if (c.kind_b == HB_BOUNDARY_SPACE) {
-        Bk.air = t_back; Bk.trad = t_back; Bk.ts_env = ts_b;
-        Bk.h = tarp_natural(t_back, ts_b, c.cos_tilt, c.c_same, c.c_opp);
-    } else {
-        // surface.rs:672-685: the back AmbientTemperature arm is built from FRONT values
-        Bk.air = c.amb_b; Bk.trad = t_front; Bk.ts_env = ts_f;
-        Bk.h = tarp_natural(c.amb_b, ts_f, c.cos_tilt, c.c_same, c.c_opp);
-    }
-    if (F.h != F.h || Bk.h != Bk.h) status |= ST_NAN_H;  // surface.rs:704-707 (panic in the reference)
-    if (c.ov_f == c.ov_f) F.h = c.ov_f;                  // surface.rs:708-714 (debug-only overrides)
-    if (c.ov_b == c.ov_b) Bk.h = c.ov_b;
+    const int fl = c.fl;
+    F.air = w.t_front;
+    F.trad = (fl & WF_F_OUT) ? w.trad_out_f : w.t_front;
+    F.ts_env = ts_f;
+    double hf = tarp_natural(w.t_front, ts_f, c.kpos_f, c.kneg_f);
+    if (fl & WF_F_OUT) hf += w.forced;
+    Bk.air = w.t_back;
+    Bk.trad = (fl & WF_B_OUT) ? w.trad_out_b : (fl & WF_B_AMB) ? w.t_front : w.t_back;
+    Bk.ts_env = (fl & WF_B_AMB) ? ts_f : ts_b;
+    double hb = tarp_natural(w.t_back, Bk.ts_env, c.kpos_b, c.kneg_b);
+    if (fl & WF_B_OUT) hb += w.forced;
+    if (hf != hf || hb != hb) status |= ST_NAN_H;   // surface.rs:704-707 (panic in the reference)
+    F.h = (fl & WF_OV_F) ? c.ov_f : hf;             // surface.rs:708-714 (debug-only overrides)
+    Bk.h = (fl & WF_OV_B) ? c.ov_b : hb;
 }
 
 // Access to one wall's node temperatures and wall-major constant arrays from the scalar lane (TILE_EXT tiles).
@@ -269,7 +338,7 @@ HB_HD_NOINLINE void solve_nomass(const WallC& c, WallS& w, const ExtWall& X, con
             for (int q = c.cav_begin; q < c.cav_end; ++q)
                 if (cavs[q].node == link) cavl[j] = q;
     }
-    const bool dist = (c.flags >> 8) & 1;
+    const bool dist = (c.fl & WF_DIST) != 0;
     for (int j = 0; j < m; ++j) {
         const int node = ini + j;
         if (dist)
@@ -360,25 +429,22 @@ HB_HD void begin_main_step(const WallC& c, WallS& w) {
 template <bool EXT>
 HB_HD void scalar_pre(const WallC& c, WallS& w, const SubWeather& sw, double zone_t_front, double zone_t_back,
                       double dt, const ExtWall& X, const CavityDev* cavs, const int32_t* nm_pairs, BoundaryLinks& out) {
-    const bool any_outdoor = c.kind_f == HB_BOUNDARY_OUTDOOR || c.kind_b == HB_BOUNDARY_OUTDOOR;
-    double forced = 0.;
-    if (any_outdoor) {
-        bool windward = true;  // surface.rs:37-46
-        if (fabs(c.cos_tilt) < 0.98) windward = add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0;
-        forced = c.forced_c * (windward ? 1.0 : 0.5) * sw.sqrt_ws;
-    }
-    w.forced = forced;
+    const int fl = c.fl;
+    // surface.rs:37-46 (windward unless the tilted surface's normal points away from the wind) and the forced term
+    // 2.537·Wf·Rf·sqrt(P·v/A) (convection.rs:157-163); only Outdoor faces use it
+    const bool leeward = (fl & WF_TILTED) && !(add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0);
+    w.forced = c.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
     // boundary temperatures (model.rs:79-96)
-    w.t_front = c.kind_f == HB_BOUNDARY_SPACE ? zone_t_front : c.kind_f == HB_BOUNDARY_AMBIENT ? c.amb_f : sw.t_out;
-    w.t_back = c.kind_b == HB_BOUNDARY_SPACE ? zone_t_back : c.kind_b == HB_BOUNDARY_AMBIENT ? c.amb_b : sw.t_out;
+    w.t_front = (fl & WF_F_OUT) ? sw.t_out : (fl & WF_F_SPACE) ? zone_t_front : c.amb_f;
+    w.t_back = (fl & WF_B_OUT) ? sw.t_out : (fl & WF_B_SPACE) ? zone_t_back : c.amb_b;
 
     Face F, Bk;
     border(c, w, w.ts_f, w.ts_b, F, Bk, w.status);
     const double hf = F.h, hb = Bk.h;
     const double xr_f = 273.15 + (F.trad + F.ts_env) / 2.;
     const double xr_b = 273.15 + (Bk.trad + Bk.ts_env) / 2.;
-    const double rad_f = 4. * c.eps_f * kSigma * ((xr_f * xr_f) * xr_f);
-    const double rad_b = 4. * c.eps_b * kSigma * ((xr_b * xr_b) * xr_b);
+    const double rad_f = c.eps4s_f * ((xr_f * xr_f) * xr_f);
+    const double rad_b = c.eps4s_b * ((xr_b * xr_b) * xr_b);
 
     if (EXT) {
         // no-mass chunks first (surface.rs:950-965)
@@ -402,8 +468,8 @@ HB_HD void scalar_pre(const WallC& c, WallS& w, const SubWeather& sw, double zon
     //   h·(T_air − T_s) + rad·(T_rad − T_s⁰) + q_solar  =  h·(T_ghost − T_s)        (discretization.rs:658-697)
     // T_s⁰ is the surface temperature at assembly time: the radiative term is explicit in the reference.
     const double hf_s = hf > 1e-12 ? hf : 1e-12, hb_s = hb > 1e-12 ? hb : 1e-12;
-    out.ghost_f = F.air + (rad_f * (F.trad - w.ts_f) + c.af0 * w.solar_front) / hf_s;
-    out.ghost_b = Bk.air + (rad_b * (Bk.trad - w.ts_b) + c.abL * w.solar_back) / hb_s;
+    out.ghost_f = F.air + (rad_f * (F.trad - w.ts_f) + c.af0 * w.solar_front) * fast_rcp(hf_s);
+    out.ghost_b = Bk.air + (rad_b * (Bk.trad - w.ts_b) + c.abL * w.solar_back) * fast_rcp(hb_s);
     out.bf = hf_s * c.v0;
     out.ab = hb_s * c.vL;
 }
@@ -452,13 +518,18 @@ HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const dou
         b += rho * z.vent_v * cp;
     }
     const double tk = tz + 273.15;
-    const double cc = z.vol * (101325. * 28.97 / (8314.46261815324 * tk)) * (1002.7370 + 1.2324e-2 * tk) / 1.;
+    // 1/c with c = V·ρ(T)·cp(T) (zone.rs:59-65), ρ = 101325·28.97/(8314.46261815324·T_K)
+    const double inv_cc = (8314.46261815324 * tk) * fast_rcp(z.vol * (101325. * 28.97) * (1002.7370 + 1.2324e-2 * tk));
+#pragma unroll 1
     for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
         if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
         if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
     }
     double tn = tz;
-    if (fabs(b) > 1e-9) tn = a / b + (tz - a / b) * exp(-b * dt / cc);
+    if (fabs(b) > 1e-9) {
+        const double ab = a * fast_rcp(b);   // b > 0: sums of h·A and ρ·V̇·cp
+        tn = ab + (tz - ab) * exp(-b * dt * inv_cc);
+    }
     return tn;
 }
 

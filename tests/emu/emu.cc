@@ -48,19 +48,8 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
         }
     for (int t = 0; t < W; ++t) {
         const int64_t sg = (int64_t)tile.surface_begin + t;
-        WallC c{};
-        c.area = V.area[sg]; c.cos_tilt = V.cos_tilt[sg];
-        const double act = fabs(c.cos_tilt);
-        c.c_same = 9.482 / (7.238 - act); c.c_opp = 1.81 / (1.382 + act);
-        c.forced_c = V.forced_c[sg]; c.eps_f = V.eps_f[sg]; c.eps_b = V.eps_b[sg];
-        c.amb_f = V.amb_f[sg]; c.amb_b = V.amb_b[sg]; c.ov_f = V.hs_ov_f[sg]; c.ov_b = V.hs_ov_b[sg];
-        c.nx = V.nx[sg]; c.ny = V.ny[sg]; c.af0 = V.af0[sg]; c.abL = V.abL[sg]; c.v0 = V.v0[sg]; c.vL = V.vL[sg];
-        c.n = V.n_nodes[sg]; c.flags = V.flags[sg];
-        c.kind_f = c.flags & 15; c.kind_b = (c.flags >> 4) & 15;
-        c.zf = V.zone_f[sg]; c.zb = V.zone_b[sg]; c.site = P.single_site ? 0 : V.site[sg];
-        c.nm_begin = V.nm_off[sg]; c.nm_end = V.nm_off[sg + 1];
-        c.cav_begin = V.cav_off[sg]; c.cav_end = V.cav_off[sg + 1];
-        c.desc_index = V.desc_index[sg];
+        WallC c;
+        load_wallc(V, sg, P.single_site != 0, c);
         wc[t] = c;
         zf[t] = c.zf;
         zb[t] = c.zb;
