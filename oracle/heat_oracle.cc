@@ -1193,16 +1193,20 @@ const char* ho_last_error(void) { return g_error.c_str(); }
 
 // ThermalModel::new — src/model.rs:215-354
 ho_model* ho_model_new(const ho_model_desc* d) {
+    return ho_model_new_ex(d, 0., 0.04 /* model.rs:236 */, 60. /* model.rs:237 */);
+}
+
+// Same, with the discretization parameters the reference's unit tests pass to Discretization::new directly
+// (src/surface.rs:1124-1127,1264-1267,1377-1380,1485-1488).  main_dt_override <= 0: main_dt = 3600/n (model.rs:240).
+ho_model* ho_model_new_ex(const ho_model_desc* d, double main_dt_override, double max_dx, double min_dt) {
     return guarded(
         [&]() -> ho_model* {
             auto m = std::make_unique<ho_model>();
             m->zone_volume.assign(d->zone_volume, d->zone_volume + d->n_zones);
             size_t state_len = (size_t)d->n_zones;  // one SpaceDryBulbTemperature per space, zone.rs:43-50
-            const Float max_dx = 0.04;              // :236
-            const Float min_dt = 60.;               // :237
             size_t dt_subdivisions = 1;
             const size_t n = (size_t)d->steps_per_hour;
-            const Float main_dt = 60. * 60. / (Float)n;  // :240
+            const Float main_dt = main_dt_override > 0. ? main_dt_override : 60. * 60. / (Float)n;  // :240
             // surfaces first, then fenestrations (:244-323); the descriptor must already be in that order
             bool seen_fen = false;
             for (int i = 0; i < d->n_surfaces; ++i) {
@@ -1398,6 +1402,91 @@ int32_t ho_discretize(const ho_layer* layers, int32_t n_layers, double model_dt,
             return (int32_t)d.segments.size();
         },
         -1);
+}
+
+
+/* Discretization::build on given element counts (src/discretization.rs:163-298) */
+int32_t ho_build(const ho_layer* layers, int32_t n_layers, int32_t tstep_subdivision, const int32_t* n_elements,
+                 double height, double angle, double* mass, double* u, int32_t cap_nodes) {
+    return guarded(
+        [&]() -> int32_t {
+            std::vector<size_t> el(n_elements, n_elements + n_layers);
+            Discretization d = Discretization::build(layers, (size_t)n_layers, (size_t)tstep_subdivision, el, height, angle);
+            if ((int32_t)d.segments.size() > cap_nodes) throw Panic("cap_nodes too small");
+            for (size_t i = 0; i < d.segments.size(); ++i) {
+                mass[i] = d.segments[i].first;
+                const auto& uv = d.segments[i].second;
+                u[i] = uv.kind == UValue::Solid ? uv.u : (uv.kind == UValue::CavityK ? -1. : 0.);
+            }
+            return (int32_t)d.segments.size();
+        },
+        -1);
+}
+
+/* Discretization::get_chunks on bare node masses (src/discretization.rs:117-160); returns the chunk count */
+int32_t ho_chunks(const double* mass, int32_t n, int32_t massive, int32_t* out, int32_t cap) {
+    return guarded(
+        [&]() -> int32_t {
+            Discretization d;
+            d.segments.resize((size_t)n);
+            for (int i = 0; i < n; ++i) d.segments[i].first = mass[i];
+            std::vector<std::pair<size_t, size_t>> ma, nm;
+            d.get_chunks(ma, nm);
+            const auto& v = massive ? ma : nm;
+            if ((int32_t)(2 * v.size()) > cap) throw Panic("cap too small");
+            for (size_t i = 0; i < v.size(); ++i) {
+                out[2 * i] = (int32_t)v[i].first;
+                out[2 * i + 1] = (int32_t)v[i].second;
+            }
+            return (int32_t)v.size();
+        },
+        -1);
+}
+
+/* Discretization::get_k_q on solid segments (src/discretization.rs:596-700): segments = (mass[i], Solid(u[i])),
+ * last one Back.  k_out: dense (fin-ini)x(fin-ini) row-major, q_out: fin-ini. */
+int32_t ho_get_k_q(int32_t n, const double* mass, const double* u, int32_t ini, int32_t fin, const double* temps,
+                   double front_air, double front_rad_t, double front_hs, double front_rad_hs, double back_air,
+                   double back_rad_t, double back_hs, double back_rad_hs, double* k_out, double* q_out) {
+    return guarded(
+        [&]() -> int32_t {
+            Discretization d;
+            d.segments.resize((size_t)n);
+            for (int i = 0; i < n; ++i) {
+                d.segments[i].first = mass[i];
+                d.segments[i].second.kind = i + 1 < n ? UValue::Solid : UValue::Back;
+                d.segments[i].second.u = u[i];
+            }
+            Matrix t = Matrix::from_data((size_t)n, 1, std::vector<Float>(temps, temps + n));
+            ConvectionParams fe{}, be{};
+            fe.air_temperature = front_air; fe.rad_temperature = front_rad_t; fe.surface_temperature = 22.;
+            fe.roughness_index = 1;
+            be.air_temperature = back_air; be.rad_temperature = back_rad_t; be.surface_temperature = 22.;
+            be.roughness_index = 1;
+            ChunkMemory mem((size_t)ini, (size_t)fin);
+            d.get_k_q((size_t)ini, (size_t)fin, t, fe, front_hs, front_rad_hs, be, back_hs, back_rad_hs, mem);
+            const size_t m = (size_t)(fin - ini);
+            for (size_t r = 0; r < m; ++r) {
+                q_out[r] = mem.q.get(r, 0);
+                for (size_t c = 0; c < m; ++c) k_out[r * m + c] = mem.k.get(r, c);
+            }
+            return 0;
+        },
+        1);
+}
+
+/* ISO 9050 pair combination (src/glazing.rs:180-218): out = tau, rho_front, rho_back, alpha_front, alpha_back of
+ * the n panes combined front to back */
+int32_t ho_glazing_combine(const double* tau, const double* rho_front, const double* rho_back, int32_t n, double* out) {
+    return guarded(
+        [&]() -> int32_t {
+            std::vector<Glazing> g;
+            for (int i = 0; i < n; ++i) g.push_back(Glazing::make(tau[i], rho_front[i], rho_back[i]));
+            Glazing c = Glazing::combine_layers(g.data(), g.size());
+            out[0] = c.tau; out[1] = c.rho_front; out[2] = c.rho_back; out[3] = c.alpha_front; out[4] = c.alpha_back;
+            return 0;
+        },
+        1);
 }
 
 int32_t ho_glazing_alphas(const double* tau, const double* rho_front, const double* rho_back, int32_t n,

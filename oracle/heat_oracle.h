@@ -86,6 +86,9 @@ typedef struct ho_model ho_model;
 
 /* ThermalModel::new (src/model.rs:215-354).  Returns NULL on error (see ho_last_error). */
 ho_model* ho_model_new(const ho_model_desc* desc);
+/* Same with the arguments the reference's unit tests hand to Discretization::new (src/surface.rs:1124-1127 etc.):
+ * main_dt_override <= 0 keeps main_dt = 3600/steps_per_hour. */
+ho_model* ho_model_new_ex(const ho_model_desc* desc, double main_dt_override, double max_dx, double min_dt);
 void ho_model_free(ho_model* m);
 const char* ho_last_error(void);
 
@@ -151,6 +154,18 @@ void ho_rk4_steps(int32_t n, double* k, const double* c, double* q, double* temp
 int32_t ho_discretize(const ho_layer* layers, int32_t n_layers, double model_dt, double max_dx, double min_dt,
                       double height, double angle, int32_t* tstep_subdivision, int32_t* n_elements,
                       double* mass, double* u, int32_t cap_nodes);
+/* Discretization::build on GIVEN element counts (src/discretization.rs:163-298); returns the node count */
+int32_t ho_build(const ho_layer* layers, int32_t n_layers, int32_t tstep_subdivision, const int32_t* n_elements,
+                 double height, double angle, double* mass, double* u, int32_t cap_nodes);
+/* Discretization::get_chunks on bare node masses (src/discretization.rs:117-160); returns the chunk count */
+int32_t ho_chunks(const double* mass, int32_t n, int32_t massive, int32_t* out, int32_t cap);
+/* Discretization::get_k_q on solid segments (mass[i], Solid(u[i])), last Back (src/discretization.rs:596-700);
+ * k_out dense (fin-ini)^2 row-major, q_out fin-ini */
+int32_t ho_get_k_q(int32_t n, const double* mass, const double* u, int32_t ini, int32_t fin, const double* temps,
+                   double front_air, double front_rad_t, double front_hs, double front_rad_hs, double back_air,
+                   double back_rad_t, double back_hs, double back_rad_hs, double* k_out, double* q_out);
+/* ISO 9050 combination of n panes (src/glazing.rs:180-230): out = tau, rho_f, rho_b, alpha_f, alpha_b */
+int32_t ho_glazing_combine(const double* tau, const double* rho_front, const double* rho_back, int32_t n, double* out);
 /* glazing alphas (src/glazing.rs:259-286) for tau/rho_front/rho_back triples */
 int32_t ho_glazing_alphas(const double* tau, const double* rho_front, const double* rho_back, int32_t n, double* out);
 

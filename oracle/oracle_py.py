@@ -47,6 +47,8 @@ def load() -> C.CDLL:
         lib = C.CDLL(LIB_PATH)
         lib.ho_model_new.restype = _P
         lib.ho_model_new.argtypes = [C.POINTER(ModelDescC)]
+        lib.ho_model_new_ex.restype = _P
+        lib.ho_model_new_ex.argtypes = [C.POINTER(ModelDescC), C.c_double, C.c_double, C.c_double]
         lib.ho_model_free.argtypes = [_P]
         lib.ho_last_error.restype = C.c_char_p
         lib.ho_dt.restype = C.c_double
@@ -96,6 +98,14 @@ def load() -> C.CDLL:
         lib.ho_discretize.restype = C.c_int32
         lib.ho_discretize.argtypes = [_P, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _P, _P,
                                       _P, _P, C.c_int32]
+        lib.ho_build.restype = C.c_int32
+        lib.ho_build.argtypes = [_P, C.c_int32, C.c_int32, _P, C.c_double, C.c_double, _P, _P, C.c_int32]
+        lib.ho_chunks.restype = C.c_int32
+        lib.ho_chunks.argtypes = [_P, C.c_int32, C.c_int32, _P, C.c_int32]
+        lib.ho_get_k_q.restype = C.c_int32
+        lib.ho_get_k_q.argtypes = [C.c_int32, _P, _P, C.c_int32, C.c_int32, _P] + [C.c_double] * 8 + [_P, _P]
+        lib.ho_glazing_combine.restype = C.c_int32
+        lib.ho_glazing_combine.argtypes = [_P, _P, _P, C.c_int32, _P]
         lib.ho_glazing_alphas.restype = C.c_int32
         lib.ho_glazing_alphas.argtypes = [_P, _P, _P, C.c_int32, _P]
         lib.ho_run_ensemble.restype = C.c_int64
@@ -115,8 +125,9 @@ def _f8(a):
 class OracleModel:
     """One `ThermalModel` of the reference, restated on the CPU."""
 
-    def __init__(self, desc, m: int = 0):
-        """`desc`: heat_b200.desc.BatchDesc; `m`: which model of the batch."""
+    def __init__(self, desc, m: int = 0, discretization=None):
+        """`desc`: heat_b200.desc.BatchDesc; `m`: which model of the batch; `discretization` = (main_dt, max_dx,
+        min_dt) as the reference's unit tests pass to Discretization::new (default: model.rs:236-240)."""
         lib = load()
         self._lib = lib
         z0, z1 = int(desc.model_zone_offset[m]), int(desc.model_zone_offset[m + 1])
@@ -134,7 +145,10 @@ class OracleModel:
         d.surfaces = self._keep[3].ctypes.data
         d.terrain = -1 if desc.model_terrain is None else int(desc.model_terrain[m])
         d.steps_per_hour = int(desc.steps_per_hour)
-        self._m = lib.ho_model_new(C.byref(d))
+        if discretization is None:
+            self._m = lib.ho_model_new(C.byref(d))
+        else:
+            self._m = lib.ho_model_new_ex(C.byref(d), *[float(v) for v in discretization])
         if not self._m:
             raise OracleError(lib.ho_last_error().decode())
         self.n_zones = d.n_zones
@@ -312,6 +326,48 @@ def discretize(layers, model_dt, max_dx, min_dt, height=1.0, angle=0.0, cap=512)
     if n < 0:
         raise OracleError(load().ho_last_error().decode())
     return tsub.value, el, mass[:n].copy(), u[:n].copy()
+
+
+def build_segments(layers, tstep_subdivision, n_elements, height=1.0, angle=0.0, cap=512):
+    """Discretization::build on given element counts → (mass[n_nodes], u[n_nodes]) (u: solid k/dx, cavity -1, back 0)."""
+    layers = np.ascontiguousarray(layers)
+    el = np.ascontiguousarray(n_elements, np.int32)
+    mass, u = np.zeros(cap), np.zeros(cap)
+    n = load().ho_build(layers.ctypes.data, len(layers), tstep_subdivision, el.ctypes.data, height, angle,
+                        mass.ctypes.data, u.ctypes.data, cap)
+    if n < 0:
+        raise OracleError(load().ho_last_error().decode())
+    return mass[:n].copy(), u[:n].copy()
+
+
+def chunks(mass, massive: bool):
+    mass = _f8(mass)
+    out = np.zeros(2 * mass.size + 2, np.int32)
+    n = load().ho_chunks(mass.ctypes.data, mass.size, int(massive), out.ctypes.data, out.size)
+    if n < 0:
+        raise OracleError(load().ho_last_error().decode())
+    return [(int(out[2 * i]), int(out[2 * i + 1])) for i in range(n)]
+
+
+def get_k_q(mass, u, ini, fin, temps, front, back):
+    """front/back = (air_temperature, rad_temperature, hs, rad_hs). Returns dense K[(fin-ini)²], q[fin-ini]."""
+    mass, u, temps = _f8(mass), _f8(u), _f8(temps)
+    m = fin - ini
+    k, q = np.zeros((m, m)), np.zeros(m)
+    rc = load().ho_get_k_q(mass.size, mass.ctypes.data, u.ctypes.data, ini, fin, temps.ctypes.data, *map(float, front),
+                           *map(float, back), k.ctypes.data, q.ctypes.data)
+    if rc:
+        raise OracleError(load().ho_last_error().decode())
+    return k, q
+
+
+def glazing_combine(tau, rho_front, rho_back):
+    """ISO 9050 combination → (tau, rho_front, rho_back, alpha_front, alpha_back)."""
+    tau, rf, rb = _f8(tau), _f8(rho_front), _f8(rho_back)
+    out = np.zeros(5)
+    if load().ho_glazing_combine(tau.ctypes.data, rf.ctypes.data, rb.ctypes.data, tau.size, out.ctypes.data):
+        raise OracleError(load().ho_last_error().decode())
+    return out
 
 
 def glazing_alphas(tau, rho_front, rho_back):
