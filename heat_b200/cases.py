@@ -137,7 +137,7 @@ def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, 
     Massive walls: 1..max_layers random solid layers. Mixed walls (fraction `mixed_fraction`): polyurethane /
     random solid / polyurethane, whose outer layers the reference's rule classifies as no-mass.
     Walls that the reference's discretization rule cuts into more than `max_nodes` nodes (thick layers of very low
-    diffusivity) are re-drawn, up to 8 times, then replaced by a 20 cm concrete wall.
+    diffusivity) or leaves without any massive node are re-drawn, up to 8 times, then replaced by a 20 cm concrete wall.
     """
     d = _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers)
     if not max_nodes:
@@ -145,10 +145,10 @@ def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, 
     from .model import ThermalBatch
     for attempt in range(1, 10):
         plan = ThermalBatch(d, device=-1)  # host-only planning handle (discretization runs on the host anyway)
-        n_nodes = np.array([plan.surface_info(s).n_nodes for s in range(n_walls)]) if n_walls <= 2000 else \
-            _bulk_n_nodes(plan, n_walls)
+        n_nodes, n_massive = _bulk_n_nodes(plan, n_walls)
         plan.close()
-        bad = np.nonzero(n_nodes > max_nodes)[0]
+        # re-draw too, walls whose every layer the rule classifies no-mass (nothing left to march)
+        bad = np.nonzero((n_nodes > max_nodes) | (n_massive == 0))[0]
         if bad.size == 0:
             return d
         # the layers to re-draw: every layer of a bad wall except the fixed polyurethane skins of mixed walls
@@ -169,12 +169,14 @@ def _bulk_n_nodes(plan, n: int) -> np.ndarray:
     import ctypes as C
     from . import _lib
     out = np.empty(n, np.int64)
+    massive = np.empty(n, np.int64)
     info = _lib.SurfaceInfoC()
     fn, h = plan._lib.hb_get_surface_info, plan._h
     for s in range(n):
         fn(h, s, C.byref(info))
         out[s] = info.n_nodes
-    return out
+        massive[s] = info.n_massive_chunks
+    return out, massive
 
 
 def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers) -> D.BatchDesc:

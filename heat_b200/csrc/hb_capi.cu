@@ -2,11 +2,13 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -60,7 +62,7 @@ struct hb_handle {
     // device buffers (uploaded verbatim from hb::HostArrays)
     DevBuf<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     DevBuf<hb::CavityDev> cav;
-    DevBuf<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL;
+    DevBuf<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL, u_f, u_b;
     DevBuf<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     DevBuf<unsigned long long> nm_iters;
     DevBuf<int32_t> status;
@@ -73,7 +75,7 @@ struct hb_handle {
 
     // one launch per (lanes-per-wall, kernel variant); each on its own stream so that small groups overlap
     struct Group {
-        int G, var;
+        int G, W, var;
         int n_tiles;
         DevBuf<int32_t> ids;   // tile ids, heaviest first
         cudaStream_t stream = nullptr;
@@ -90,7 +92,7 @@ struct hb_handle {
         V.n_nodes = n_nodes.p; V.flags = flags.p; V.zone_f = zone_f.p; V.zone_b = zone_b.p; V.site = site.p;
         V.desc_index = desc_index.p; V.area = area.p; V.nx = nx.p; V.ny = ny.p; V.cos_tilt = cos_tilt.p;
         V.forced_c = forced_c.p; V.eps_f = eps_f.p; V.eps_b = eps_b.p; V.amb_f = amb_f.p; V.amb_b = amb_b.p;
-        V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p; V.af0 = af0.p; V.abL = abL.p; V.v0 = v0.p; V.vL = vL.p;
+        V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p; V.af0 = af0.p; V.abL = abL.p; V.v0 = v0.p; V.vL = vL.p; V.u_f = u_f.p; V.u_b = u_b.p;
         V.nm_off = nm_off.p; V.nm_pairs = nm_pairs.p; V.cav_off = cav_off.p; V.cav = cav.p;
         V.nodeT = nodeT.p; V.coefA = coefA.p; V.coefB = coefB.p;
         V.ext_u = ext_u.p; V.ext_mass = ext_mass.p; V.ext_af = ext_af.p; V.ext_ab = ext_ab.p;
@@ -141,7 +143,7 @@ void build_device(hb_handle* h) {
     h->forced_c.upload(H.forced_c, st); h->eps_f.upload(H.eps_f, st); h->eps_b.upload(H.eps_b, st);
     h->amb_f.upload(H.amb_f, st); h->amb_b.upload(H.amb_b, st); h->hs_ov_f.upload(H.hs_ov_f, st);
     h->hs_ov_b.upload(H.hs_ov_b, st); h->af0.upload(H.af0, st); h->abL.upload(H.abL, st); h->v0.upload(H.v0, st);
-    h->vL.upload(H.vL, st);
+    h->vL.upload(H.vL, st); h->u_f.upload(H.u_f, st); h->u_b.upload(H.u_b, st);
     h->nodeT.upload(H.nodeT, st); h->coefA.upload(H.coefA, st); h->coefB.upload(H.coefB, st);
     h->ext_u.upload(H.ext_u, st); h->ext_mass.upload(H.ext_mass, st); h->ext_af.upload(H.ext_af, st);
     h->ext_ab.upload(H.ext_ab, st); h->sc.upload(H.sc, st);
@@ -156,17 +158,18 @@ void build_device(hb_handle* h) {
     h->host_site.assign(B.n_dev_surfaces, 0);
 
     // launch groups: (lanes per wall, kernel variant); inside a group the heaviest tiles are scheduled first
-    std::map<std::pair<int, int>, std::vector<int32_t>> by;
+    std::map<std::tuple<int, int, int>, std::vector<int32_t>> by;
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
-        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : 0;
-        by[{-t.G, var}].push_back((int32_t)ti);   // largest walls first
+        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_END) ? 3 : 0;
+        by[{-t.G, var, t.W}].push_back((int32_t)ti);   // largest walls first
     }
     HB_CUDA(cudaEventCreateWithFlags(&h->fork, cudaEventDisableTiming));
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
-        grp->G = -kv.first.first;
-        grp->var = kv.first.second;
+        grp->G = -std::get<0>(kv.first);
+        grp->var = std::get<1>(kv.first);
+        grp->W = std::get<2>(kv.first);
         std::stable_sort(kv.second.begin(), kv.second.end(),
                          [&](int32_t a, int32_t b) { return B.tiles[a].S > B.tiles[b].S; });
         grp->n_tiles = (int)kv.second.size();
@@ -183,7 +186,7 @@ void build_device(hb_handle* h) {
 namespace hb {
 // one translation unit per lanes-per-wall tier (hb_march_tier.cu compiled with -DHB_TIER=G) so they build in parallel
 #define HB_DECL_TIER(N) \
-    cudaError_t launch_march_##N(int var, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+    cudaError_t launch_march_##N(int var, int W, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
 HB_DECL_TIER(1) HB_DECL_TIER(2) HB_DECL_TIER(4) HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(32)
 #undef HB_DECL_TIER
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
@@ -199,20 +202,37 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
     const hb::DevView V = h->view();
     P.single_site = h->single_site ? 1 : 0;
     HB_CUDA(cudaEventRecord(h->fork, h->stream));
+    // HB_GROUP_TIMES=1 (diagnostic): run the launch groups one after the other and print each one's duration
+    static const bool group_times = std::getenv("HB_GROUP_TIMES") != nullptr;
     for (auto& gp : h->groups) {
         hb_handle::Group& g = *gp;
         HB_CUDA(cudaStreamWaitEvent(g.stream, h->fork, 0));
+        cudaEvent_t t0 = nullptr, t1 = nullptr;
+        if (group_times) {
+            HB_CUDA(cudaEventCreate(&t0));
+            HB_CUDA(cudaEventCreate(&t1));
+            HB_CUDA(cudaEventRecord(t0, g.stream));
+        }
         cudaError_t e;
         switch (g.G) {
-            case 1: e = hb::launch_march_1(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 2: e = hb::launch_march_2(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 4: e = hb::launch_march_4(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 8: e = hb::launch_march_8(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 16: e = hb::launch_march_16(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            default: e = hb::launch_march_32(g.var, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 1: e = hb::launch_march_1(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 2: e = hb::launch_march_2(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 4: e = hb::launch_march_4(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 8: e = hb::launch_march_8(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 16: e = hb::launch_march_16(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            default: e = hb::launch_march_32(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
         }
         HB_CUDA(e);
         h->launches += 1;
+        if (group_times) {
+            HB_CUDA(cudaEventRecord(t1, g.stream));
+            HB_CUDA(cudaEventSynchronize(t1));
+            float ms = 0.f;
+            HB_CUDA(cudaEventElapsedTime(&ms, t0, t1));
+            std::fprintf(stderr, "[hb] group G=%d W=%d var=%d tiles=%d: %.3f ms\n", g.G, g.W, g.var, g.n_tiles, ms);
+            cudaEventDestroy(t0);
+            cudaEventDestroy(t1);
+        }
         HB_CUDA(cudaEventRecord(g.done, g.stream));
         HB_CUDA(cudaStreamWaitEvent(h->stream, g.done, 0));
     }

@@ -16,7 +16,8 @@ struct CavityDev {
 struct DevView {
     // ---- per device surface slot (tile.surface_begin + wall) ----
     const int32_t* n_nodes;   // 0 on padding slots
-    const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity
+    const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity,
+                              // 10 / 11: node 0 / node n-1 is a single-node no-mass chunk (TILE_END tiles)
     const int32_t* zone_f;    // tile-local zone index or -1
     const int32_t* zone_b;
     const int32_t* site;
@@ -36,6 +37,8 @@ struct DevView {
     const double* abL;        // back solar absorptance of node n-1
     const double* v0;         // dt/C of node 0 (0 when it has no mass)
     const double* vL;         // dt/C of node n-1
+    const double* u_f;        // conductance of the link node 0 → 1 (TILE_END)
+    const double* u_b;        // conductance of the link node n-2 → n-1
     const int32_t* nm_off;    // CSR over no-mass chunks: pairs (ini, fin)
     const int32_t* nm_pairs;
     const int32_t* cav_off;   // CSR over cavity links
@@ -74,7 +77,8 @@ struct DevView {
 struct HostArrays {
     std::vector<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     std::vector<CavityDev> cav;
-    std::vector<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL;
+    std::vector<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL,
+        u_f, u_b;
     std::vector<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     std::vector<unsigned long long> nm_iters;
     std::vector<int32_t> status;

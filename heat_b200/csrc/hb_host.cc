@@ -264,6 +264,8 @@ void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int
     P.wind_speed_modifier = wind_modifier(s.centroid_z, terrain);
 }
 
+constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END;   // tiles are uniform in these
+
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
     if (d->steps_per_hour <= 0) fail("steps_per_hour must be positive");
@@ -345,21 +347,30 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         ModelPlan& M = B.models[m];
         if (M.nmax > kMaxNodes) fail("surface has more nodes than the supported maximum (254)");
         M.variant = 0;
+        bool ends_only = true;   // every no-mass chunk is one node at an end of a wall of >= 3 nodes
         for (int k = 0; k < M.n_surfaces; ++k) {
             const SurfacePlan& P = B.plans[M.surface_begin + k];
             if (!P.nomass_chunks.empty() || !P.cavities.empty()) M.variant |= TILE_EXT;
             if (!P.cavities.empty()) M.variant |= TILE_CAV;
             if (P.distributed_solar) M.variant |= TILE_EXT | TILE_DIST;
+            for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2) {
+                const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
+                if (fin - ini != 1 || P.n_nodes < 3 || (ini != 0 && fin != P.n_nodes)) ends_only = false;
+            }
         }
-        const int W = walls_of_group(group_of_nodes(M.nmax));
-        if (M.n_surfaces > W || M.n_zones > W)
-            fail("model larger than one tile (" + std::to_string(W) + " surfaces / zones at this wall size)");
+        if (M.variant == TILE_EXT && ends_only) M.variant = TILE_END;
+        const int Wmax = walls_of_group(group_of_nodes(M.nmax));
+        if (M.n_surfaces > Wmax || M.n_zones > Wmax)
+            fail("model larger than one tile (" + std::to_string(Wmax) + " surfaces / zones at this wall size)");
+        // tiles of the face kernel (all-massive / no-mass ends) are as small as the model allows
+        const bool face = (M.variant & (TILE_EXT | TILE_DIST)) == 0;
+        M.walls = face ? walls_for_model(group_of_nodes(M.nmax), M.n_surfaces, M.n_zones) : Wmax;
     }
     B.model_order.resize(d->n_models);
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
     auto key = [&](int m) {
         const ModelPlan& M = B.models[m];
-        return std::make_tuple(group_of_nodes(M.nmax), M.variant & (TILE_EXT | TILE_DIST), M.dt_subdivisions);
+        return std::make_tuple(group_of_nodes(M.nmax), M.variant & kTileKey, M.walls, M.dt_subdivisions);
     };
     if (d->n_models > 1)
         std::stable_sort(B.model_order.begin(), B.model_order.end(), [&](int a, int b) { return key(a) < key(b); });
@@ -391,9 +402,9 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         const int m = B.model_order[pos];
         const ModelPlan& M = B.models[m];
         const int G = group_of_nodes(M.nmax);
-        const int W = walls_of_group(G);
-        const int variant = M.variant & (TILE_EXT | TILE_DIST);
-        if (open && (cur.G != G || (cur.flags & (TILE_EXT | TILE_DIST)) != variant || cur.S != M.dt_subdivisions ||
+        const int W = M.walls;
+        const int variant = M.variant & kTileKey;
+        if (open && (cur.G != G || cur.W != W || (cur.flags & kTileKey) != variant || cur.S != M.dt_subdivisions ||
                      cur.n_surfaces + M.n_surfaces > W || cur.n_zones + M.n_zones > W))
             close_tile();
         if (!open) {
@@ -437,7 +448,7 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
     H.site.assign(NS, 0); H.desc_index.assign(NS, 0); H.nm_off.assign(NS + 1, 0); H.cav_off.assign(NS + 1, 0);
     H.nm_pairs.clear(); H.cav.clear();
     for (auto* v : {&H.area, &H.nx, &H.ny, &H.cos_tilt, &H.forced_c, &H.eps_f, &H.eps_b, &H.amb_f, &H.amb_b, &H.af0,
-                    &H.abL, &H.v0, &H.vL, &H.energy_f, &H.energy_b})
+                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.energy_f, &H.energy_b})
         v->assign(NS, 0.);
     H.hs_ov_f.assign(NS, NAN); H.hs_ov_b.assign(NS, NAN);
     H.nodeT.assign(B.node_slab_len, 0.); H.coefA.assign(B.node_slab_len, 0.); H.coefB.assign(B.node_slab_len, 0.);
@@ -462,6 +473,11 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
         H.n_nodes[g] = n;
         H.flags[g] = (s.front_kind & 15) | ((s.back_kind & 15) << 4) | ((P.distributed_solar ? 1 : 0) << 8) |
                      ((P.cavities.empty() ? 0 : 1) << 9);
+        if (tile.flags & TILE_END)
+            for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2)
+                H.flags[g] |= P.nomass_chunks[c] == 0 ? (1 << 10) : (1 << 11);
+        H.u_f[g] = n > 1 ? P.u[0] : 0.;
+        H.u_b[g] = n > 1 ? P.u[n - 2] : 0.;
         const int zone_local0 = M.n_zones ? B.dev_zone_of[M.zone_begin] - tile.zone_begin : 0;
         H.zone_f[g] = s.front_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.front_zone : -1;
         H.zone_b[g] = s.back_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.back_zone : -1;
@@ -541,7 +557,7 @@ DevView HostArrays::view(const BatchPlan& B) {
     V.site = site.data(); V.desc_index = desc_index.data(); V.area = area.data(); V.nx = nx.data(); V.ny = ny.data();
     V.cos_tilt = cos_tilt.data(); V.forced_c = forced_c.data(); V.eps_f = eps_f.data(); V.eps_b = eps_b.data();
     V.amb_f = amb_f.data(); V.amb_b = amb_b.data(); V.hs_ov_f = hs_ov_f.data(); V.hs_ov_b = hs_ov_b.data();
-    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data();
+    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data();
     V.nm_off = nm_off.data(); V.nm_pairs = nm_pairs.data(); V.cav_off = cav_off.data(); V.cav = cav.data();
     V.nodeT = nodeT.data(); V.coefA = coefA.data(); V.coefB = coefB.data();
     V.ext_u = ext_u.data(); V.ext_mass = ext_mass.data(); V.ext_af = ext_af.data(); V.ext_ab = ext_ab.data();

@@ -21,7 +21,16 @@ constexpr int kMaxWalls = 32;        // walls (and zones) per tile; == warp size
 constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
 constexpr int kMaxSubsteps = 128;    // shared weather table rows (S <= 120 for n >= 1 step/hour)
 
+// Largest tile of a tier (256 threads) and smallest one (64 threads: the two face warps of hb_face_kernel).  Small
+// tiles shorten the node phase of a sub-step and put more independent scalar chains on an SM; a model needs all its
+// surfaces and zones in one tile, so tiles grow in powers of two up to walls_of_group(G) when a model asks for it.
 inline constexpr int walls_of_group(int G) { return G <= 8 ? 32 : G == 16 ? 16 : 8; }
+inline constexpr int min_walls_of_group(int G) { return G >= 64 ? 1 : (64 / G > 32 ? 32 : 64 / G); }
+inline int walls_for_model(int G, int n_surfaces, int n_zones) {
+    int W = min_walls_of_group(G);
+    while (W < walls_of_group(G) && (W < n_surfaces || W < n_zones)) W *= 2;
+    return W;
+}
 inline int group_of_nodes(int n) {
     int G = 1;
     while (G * kNL < n + 2) G *= 2;
@@ -71,12 +80,14 @@ struct ModelPlan {
     int64_t nodes = 0;
     int32_t nmax = 0;
     int32_t variant = 0;             // TILE_* flags needed by its surfaces
+    int32_t walls = 0;               // wall slots of the tiles this model goes into
 };
 
 enum : int32_t {
     TILE_EXT = 1,    // some wall has no-mass chunks or cavities: node temperatures are mirrored in shared memory
     TILE_DIST = 2,   // some wall absorbs solar radiation on inner nodes (transparent layers)
     TILE_CAV = 4,    // some wall has a gas cavity (temperature-dependent link)
+    TILE_END = 8,    // the only no-mass chunks are single nodes at the ends of walls (solved by the face lanes)
 };
 
 // A tile = the models one CUDA block marches.

@@ -25,7 +25,7 @@
 
 namespace hb {
 
-constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2;
+constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3;
 
 template <int G, int W, int VAR>
 __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
@@ -336,6 +336,350 @@ __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V
         if (w.status) atomicOr(&V.status[sg], w.status);
     }
     if (szone) V.zoneT[sgz] = s_zT[stid];
+}
+
+// ----------------------------------------------------------------------------------------------------------------
+// K1/K2 (fast path)  hb_face_kernel<G, W, END>: same tile / lane-group layout and the same node march as
+// hb_march_kernel, for tiles whose walls are all-massive (END = false) or whose only no-mass chunks are single nodes
+// at the ends of walls (END = true; e.g. insulation | concrete | insulation).
+//
+// The time of a series is set by the dependent chain  scalar physics → march → scalar physics → zone  of the tiles
+// with the most sub-steps, so this kernel shortens that chain:
+//   * the FRONT and BACK faces of wall j are evaluated by lane j of two different warps (two SM sub-partitions);
+//   * the zone update is done by the back-face warp; the front-face warp only signals (bar.arrive) and goes on to
+//     the next sub-step's border conditions unless a front face of the tile looks at a zone;
+//   * single-node no-mass ends are solved in the face lane's registers (solve_end_node) from the two temperatures
+//     the node lanes publish per end — no shared-memory mirror of the wall.
+// ----------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pair_sync() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
+__device__ __forceinline__ void pair_arrive() { asm volatile("bar.arrive 1, 64;" ::: "memory"); }
+
+__host__ __device__ constexpr int face_threads(int G, int W) { return G * W >= 64 ? G * W : 64; }
+
+template <int G, int W, bool END>
+__global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
+    hb_face_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+    constexpr int NT = G * W;                   // node lanes (the tile's slab stride)
+    constexpr int TPB = face_threads(G, W);     // a tile of 32 node lanes gets a second warp for the back faces
+    constexpr int NL = kNL;
+    constexpr int NWARP = TPB / 32;
+    constexpr bool SPLIT = true;
+    constexpr int NF = 1;
+    static_assert(NT >= 32 && NT % 32 == 0 && W <= 32, "tile shape");
+    const Tile tile = V.tiles[tile_ids[blockIdx.x]];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t NS = V.n_dev_surfaces;
+
+    __shared__ ZoneC s_zc[W];
+    __shared__ double s_zT[W];
+    __shared__ double s_pub[4][W];      // h·A and h·A·T_s of the front face, then of the back face
+    __shared__ int32_t s_zf[W], s_zb[W];
+    __shared__ double s_end[4][W];      // node 0, node 1, node n-2, node n-1
+    __shared__ double s_link[6][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
+    __shared__ SubWeather s_w[kMaxSubsteps];
+
+    const int S = tile.S;
+    const double dt = tile.dt;
+
+    // ---- node role (identical to hb_march_kernel) ----
+    const bool node_lane = NT == TPB || tid < NT;   // warp-uniform
+    const int wl = node_lane ? tid / G : 0, part = tid % G;
+    const int64_t g = (int64_t)tile.surface_begin + wl;
+    const int n = V.n_nodes[g];
+    const int iN = n - part * NL;        // lane-local index of the last node's slot (slot n)
+    const int iG = n + 1 - part * NL;    // … of the back ghost (slot n+1)
+    const int nmf = END ? (V.flags[g] >> 10) & 1 : 0, nmb = END ? (V.flags[g] >> 11) & 1 : 0;
+    double T[NL], A[NL], B[NL], Vv[NL];
+    if (node_lane) {
+        const int64_t o = tile.node_offset + tid;
+#pragma unroll
+        for (int i = 0; i < NL; ++i) {
+            T[i] = V.nodeT[o + (int64_t)i * NT];
+            A[i] = V.coefA[o + (int64_t)i * NT];
+            B[i] = V.coefB[o + (int64_t)i * NT];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] = A[i] = B[i] = 0.;
+    }
+    auto publish_ends = [&]() {
+        if (part == 0) {
+            s_end[0][wl] = T[1];
+            if constexpr (END) s_end[1][wl] = T[2];
+        }
+#pragma unroll
+        for (int i = 0; i < NL; ++i) {
+            if (i == iN) s_end[3][wl] = T[i];
+            if constexpr (END)
+                if (i == iN - 1) s_end[2][wl] = T[i];
+        }
+    };
+    if (node_lane) publish_ends();
+
+    // ---- face role ----
+    const int wf = SPLIT ? (int)(blockIdx.x % NWARP) : 0;          // warp of the front faces
+    const int wb = SPLIT ? (wf + 1) % NWARP : 0;                   // warp of the back faces and of the zones
+    const bool face_warp = warp == wf || warp == wb;
+    const int64_t sg = (int64_t)tile.surface_begin + lane;          // lane j ↔ wall j
+    const bool fwall = face_warp && lane < W && V.n_nodes[lane < W ? sg : (int64_t)tile.surface_begin] > 0;
+    const bool szone = warp == wb && lane < tile.n_zones;
+    const int64_t sgz = (int64_t)tile.zone_begin + lane;
+    FaceC fc[NF];
+    FaceS fs[NF];
+    bool any_front_zone = false;
+    if (fwall) {
+        WallC c;
+        load_wallc(V, sg, P.single_site != 0, c);
+        const int flg = V.flags[sg];
+#pragma unroll
+        for (int r = 0; r < NF; ++r) {
+            const bool back = SPLIT ? warp == wb : r == 1;
+            const bool nm = END && ((flg >> (back ? 11 : 10)) & 1);
+            load_facec(c, back, back ? V.u_b[sg] : V.u_f[sg], nm, fc[r]);
+            FaceS w{};
+            const int k = back ? 1 : 0;
+            w.h = V.sc[(0 + k) * NS + sg]; w.flow = V.sc[(2 + k) * NS + sg];
+            w.sol = V.sc[(4 + k) * NS + sg]; w.ir = V.sc[(6 + k) * NS + sg];
+            fs[r] = w;
+        }
+        if (warp == wb) {
+            s_zf[lane] = c.zf;
+            s_zb[lane] = c.zb;
+        }
+        any_front_zone = c.zf >= 0;
+    } else if (warp == wb && lane < W) {
+        s_zf[lane] = -1;
+        s_zb[lane] = -1;
+    }
+    if (warp == wb && lane < W) {
+        ZoneC z{};
+        if (lane < tile.n_zones) {
+            z.vol = V.zvol[sgz]; z.q = V.zq[sgz]; z.inf_v = V.zinf_v[sgz]; z.inf_t = V.zinf_t[sgz];
+            z.vent_v = V.zvent_v[sgz]; z.vent_t = V.zvent_t[sgz]; z.sb = V.z_surf_begin[sgz]; z.se = V.z_surf_end[sgz];
+            s_zT[lane] = V.zoneT[sgz];
+        }
+        s_zc[lane] = z;
+    }
+    // the front warp has to wait for the zone update only if one of its faces looks at a zone
+    const bool front_waits = __syncthreads_or(any_front_zone ? 1 : 0) != 0;
+    if (fwall) {
+#pragma unroll
+        for (int r = 0; r < NF; ++r) fs[r].ts = s_end[(fc[r].fl & FC_BACK) ? 3 : 0][lane];
+    }
+    double ir_state = fs[0].ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
+
+    int rec = 0;
+    for (int step = 0; step < P.n_steps; ++step) {
+        // ---- main-step prologue: sub-step weather table, per-step inputs ----
+        if (P.single_site) {
+            const double* w0 = P.weather + (int64_t)step * 3;
+            if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) w0 = P.weather + (int64_t)step * S * 3;
+            for (int s = tid; s < S; s += TPB) {  // all threads of the block
+                double t_out, wdir, wspeed;
+                if (P.weather_mode == HB_WEATHER_LINEAR) {
+                    const double f = (double)(s + 1) / (double)S;
+                    t_out = lerp_rn(w0[0], w0[3], f);
+                    wdir = lerp_rn(w0[1], w0[4], f);
+                    wspeed = lerp_rn(w0[2], w0[5], f);
+                } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+                    t_out = w0[3 * s + 0]; wdir = w0[3 * s + 1]; wspeed = w0[3 * s + 2];
+                } else {
+                    t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+                }
+                sub_weather(t_out, wdir, wspeed, s_w[s]);
+            }
+        }
+        if (fwall) {
+#pragma unroll
+            for (int r = 0; r < NF; ++r) {
+                const FaceC& c = fc[r];
+                FaceS& w = fs[r];
+                const int k = (c.fl & FC_BACK) ? 1 : 0;
+                double sol_front = k ? V.sc[4 * NS + sg] : w.sol;
+                if (!SPLIT && k) sol_front = fs[0].sol;
+                if (P.input_mode != HB_INPUT_STATE) {
+                    const double* in = P.input_mode == HB_INPUT_SITE
+                                           ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
+                                           : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
+                    w.sol = in[k];
+                    w.ir = in[2 + k];
+                    sol_front = in[0];
+                    if (k == 0 && P.ir_mode == HB_IR_NET_GAIN) {
+                        // validate_wall_heat_transfer.rs:689-699 (front face only, as in the reference driver)
+                        if (c.eps > 1e-3) {
+                            const double tk = w.ts + 273.15;
+                            const double tk2 = tk * tk;
+                            w.ir = w.ir / c.area / c.eps + kSigma * (tk2 * tk2);
+                        } else {
+                            w.ir = ir_state;
+                        }
+                    }
+                }
+                face_begin_main_step(c, w, sol_front);
+            }
+        }
+        __syncthreads();
+
+        for (int s = 0; s < S; ++s) {
+            // ================= face role, before the march =================
+            if (fwall) {
+#pragma unroll
+                for (int r = 0; r < NF; ++r) {
+                    const FaceC& c = fc[r];
+                    FaceS& w = fs[r];
+                    SubWeather sw;
+                    if (P.single_site) {
+                        sw = s_w[s];
+                    } else {
+                        const double* wtab = P.weather + (int64_t)c.site * P.weather_rows * 3;
+                        const double* w0 = wtab + (int64_t)step * 3;
+                        double t_out, wdir, wspeed;
+                        if (P.weather_mode == HB_WEATHER_LINEAR) {
+                            const double f = (double)(s + 1) / (double)S;
+                            t_out = lerp_rn(w0[0], w0[3], f);
+                            wdir = lerp_rn(w0[1], w0[4], f);
+                            wspeed = lerp_rn(w0[2], w0[5], f);
+                        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+                            w0 = wtab + ((int64_t)step * S + s) * 3;
+                            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+                        } else {
+                            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+                        }
+                        sub_weather(t_out, wdir, wspeed, sw);
+                    }
+                    const bool back = (c.fl & FC_BACK) != 0;
+                    const double zone_t = c.zone >= 0 ? s_zT[c.zone] : 0.;
+                    double t_front = 0., ts_front = 0., t_nb = 0.;
+                    if (c.fl & FC_BACK_AMB) {
+                        t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out
+                                  : (c.fl & FC_FRONT_SPACE) ? s_zT[c.zone_front] : c.amb_front;
+                        ts_front = SPLIT ? s_end[0][lane] : fs[0].ts;
+                    }
+                    if constexpr (END)
+                        if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][lane];
+                    double ghost, link;
+                    face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, link);
+                    s_link[back ? 2 : 0][lane] = ghost;
+                    s_link[back ? 3 : 1][lane] = link;
+                    if constexpr (END) s_link[back ? 5 : 4][lane] = w.ts;
+                }
+            }
+            __syncthreads();
+            // ================= node role: RK4 of the massive nodes =================
+            if (node_lane) {
+                const double ghost_f = s_link[0][wl], bf = s_link[1][wl], ghost_b = s_link[2][wl], ab = s_link[3][wl];
+                if (part == 0) {
+                    T[0] = ghost_f;
+                    B[1] = bf;
+                    if constexpr (END)
+                        if (nmf) T[1] = s_link[4][wl];
+                }
+#pragma unroll
+                for (int i = 0; i < NL; ++i) {
+                    if (i == iN) {
+                        A[i] = ab;
+                        if constexpr (END)
+                            if (nmb) T[i] = s_link[5][wl];
+                    }
+                    if (i == iG) T[i] = ghost_b;
+                }
+                double left = 0., right = 0.;
+                if constexpr (G > 1) {
+                    left = __shfl_up_sync(0xffffffffu, T[NL - 1], 1, G);
+                    right = __shfl_down_sync(0xffffffffu, T[0], 1, G);
+                }
+                sweep_first<NL>(T, Vv, A, B, left, right);
+#pragma unroll
+                for (int i = 0; i < NL; ++i) T[i] += Vv[i];
+                if constexpr (G > 1) {
+                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
+                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
+                }
+                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 2.);
+                if constexpr (G > 1) {
+                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
+                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
+                }
+                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 6.);
+                if constexpr (G > 1) {
+                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
+                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
+                }
+                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 24.);
+                publish_ends();
+            }
+            __syncthreads();
+            // ================= face role, after the march; zones =================
+            if (face_warp) {   // warp-uniform
+                if (fwall) {
+#pragma unroll
+                    for (int r = 0; r < NF; ++r) {
+                        const FaceC& c = fc[r];
+                        FaceS& w = fs[r];
+                        const bool back = (c.fl & FC_BACK) != 0;
+                        const double ts = s_end[back ? 3 : 0][lane];
+                        const double ts_front = (c.fl & FC_BACK_AMB) ? s_end[0][lane] : 0.;
+                        double hA, hAT;
+                        face_post(c, w, ts, ts_front, dt, hA, hAT);
+                        s_pub[back ? 2 : 0][lane] = hA;
+                        s_pub[back ? 3 : 1][lane] = hAT;
+                    }
+                }
+                if constexpr (SPLIT) {
+                    if (warp == wb || front_waits) pair_sync(); else pair_arrive();
+                } else {
+                    __syncwarp();
+                }
+                if (szone) {
+                    const double tn = zone_update(s_zc[lane], lane, s_zT[lane], dt, s_pub[0], s_pub[1], s_pub[2], s_pub[3],
+                                                  s_zf, s_zb);
+                    if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[lane].sb], ST_NAN_ZONE);
+                    s_zT[lane] = tn;
+                }
+                if constexpr (SPLIT) {
+                    if (front_waits) pair_sync();
+                } else {
+                    __syncwarp();
+                }
+            }
+        }
+
+        if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
+            if (P.zone_rec && szone) P.zone_rec[(int64_t)rec * V.n_dev_zones + sgz] = s_zT[lane];
+            if (P.node_rec) {
+#pragma unroll
+                for (int i = 0; i < NL; ++i)
+                    if (node_lane) P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * NT + tid] = T[i];
+                if (fwall) {
+                    double* rr = P.sc_rec + (int64_t)rec * 8 * NS;
+#pragma unroll
+                    for (int r = 0; r < NF; ++r) {
+                        const int k = (fc[r].fl & FC_BACK) ? 1 : 0;
+                        rr[(0 + k) * NS + sg] = fs[r].h; rr[(2 + k) * NS + sg] = fs[r].flow;
+                        rr[(4 + k) * NS + sg] = fs[r].sol; rr[(6 + k) * NS + sg] = fs[r].ir;
+                    }
+                }
+            }
+            ++rec;
+        }
+    }
+
+    // ---- write the state back ----
+#pragma unroll
+    for (int i = 0; i < NL; ++i)
+        if (node_lane) V.nodeT[tile.node_offset + (int64_t)i * NT + tid] = T[i];
+    if (fwall) {
+#pragma unroll
+        for (int r = 0; r < NF; ++r) {
+            const int k = (fc[r].fl & FC_BACK) ? 1 : 0;
+            V.sc[(0 + k) * NS + sg] = fs[r].h; V.sc[(2 + k) * NS + sg] = fs[r].flow;
+            V.sc[(4 + k) * NS + sg] = fs[r].sol; V.sc[(6 + k) * NS + sg] = fs[r].ir;
+            if (k) V.energy_b[sg] += fs[r].e; else V.energy_f[sg] += fs[r].e;
+            if (fs[r].nm_iters) atomicAdd(&V.nm_iters[sg], fs[r].nm_iters);
+            if (fs[r].status) atomicOr(&V.status[sg], fs[r].status);
+        }
+    }
+    if (szone) V.zoneT[sgz] = s_zT[lane];
 }
 
 #ifdef HB_AUX_KERNELS

@@ -22,15 +22,31 @@ cudaError_t launch_variant(int n_tiles, cudaStream_t st, const DevView& V, const
     hb_march_kernel<G, W, VAR><<<n_tiles, G * W, dyn, st>>>(V, P, ids);
     return cudaGetLastError();
 }
+template <int G, int W, bool END>
+cudaError_t launch_face(int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
+    hb_face_kernel<G, W, END><<<n_tiles, face_threads(G, W), 0, st>>>(V, P, ids);
+    return cudaGetLastError();
+}
+
+template <int G, bool END>
+cudaError_t launch_face_w(int W, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
+    constexpr int W0 = min_walls_of_group(G), W2 = walls_of_group(G);
+    constexpr int W1 = W0 * 2 <= W2 ? W0 * 2 : W2;
+    if (W == W0) return launch_face<G, W0, END>(n_tiles, st, V, P, ids);
+    if (W == W1) return launch_face<G, W1, END>(n_tiles, st, V, P, ids);
+    if (W == W2) return launch_face<G, W2, END>(n_tiles, st, V, P, ids);
+    return cudaErrorInvalidValue;
+}
 }  // namespace
 
-cudaError_t HB_CAT(launch_march_, HB_TIER)(int var, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P,
-                                           const int32_t* ids) {
-    constexpr int G = HB_TIER, W = walls_of_group(HB_TIER);
+cudaError_t HB_CAT(launch_march_, HB_TIER)(int var, int W, int n_tiles, cudaStream_t st, const DevView& V,
+                                           const SeriesDev& P, const int32_t* ids) {
+    constexpr int G = HB_TIER, WL = walls_of_group(HB_TIER);
     switch (var) {
-        case kVarPlain: return launch_variant<G, W, kVarPlain>(n_tiles, st, V, P, ids);
-        case kVarExt: return launch_variant<G, W, kVarExt>(n_tiles, st, V, P, ids);
-        default: return launch_variant<G, W, kVarDist>(n_tiles, st, V, P, ids);
+        case kVarPlain: return launch_face_w<G, false>(W, n_tiles, st, V, P, ids);
+        case kVarEnd: return launch_face_w<G, true>(W, n_tiles, st, V, P, ids);
+        case kVarExt: return W == WL ? launch_variant<G, WL, kVarExt>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
+        default: return W == WL ? launch_variant<G, WL, kVarDist>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
     }
 }
 }  // namespace hb

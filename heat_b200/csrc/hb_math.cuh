@@ -534,6 +534,147 @@ HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const dou
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Per-FACE formulation of the same scalar physics (hb_face_kernel): the front and the back face of a wall are
+// evaluated by two different lanes (two warps of the block), which halves the dependent chain that separates two
+// node marches.  Arithmetic and operation order are those of border()/scalar_pre()/scalar_post() above.
+// ------------------------------------------------------------------------------------------------------------
+enum : int32_t {
+    FC_OUT = 1, FC_SPACE = 2, FC_BACK = 4, FC_TILTED = 8, FC_OV = 16, FC_NM = 32,
+    FC_BACK_AMB = 64,        // back face, Boundary::AmbientTemperature: built from FRONT values (surface.rs:672-685)
+    FC_FRONT_OUT = 128, FC_FRONT_SPACE = 256,   // kind of the wall's front boundary (needed by FC_BACK_AMB)
+};
+// Constants of one face of one wall.
+struct FaceC {
+    double kpos, kneg;     // TARP natural-convection factors of this face (load_wallc)
+    double eps4s;          // 4·ε·σ of this face
+    double area;
+    double v_end;          // dt/C of the face's end node (0: no mass)
+    double alpha_end;      // solar absorptance landing on the end node from this side
+    double amb;            // AmbientTemperature of this boundary
+    double ov;             // film-coefficient override (debug-only field of the reference) when FC_OV
+    double forced_c, nx, ny;
+    double eps;            // emissivity of this face (front: IR net-gain conversion)
+    double u_nb;           // conductance of the link between the end node and its neighbour (FC_NM)
+    double amb_front;      // FC_BACK_AMB: the front boundary's ambient temperature
+    int32_t fl, zone, zone_front, site, desc_index, n;
+};
+HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f) {
+    const int wf = c.fl;
+    int fl = back ? FC_BACK : 0;
+    if (wf & (back ? WF_B_OUT : WF_F_OUT)) fl |= FC_OUT;
+    if (wf & (back ? WF_B_SPACE : WF_F_SPACE)) fl |= FC_SPACE;
+    if (wf & WF_TILTED) fl |= FC_TILTED;
+    if (wf & (back ? WF_OV_B : WF_OV_F)) fl |= FC_OV;
+    if (back && (wf & WF_B_AMB)) fl |= FC_BACK_AMB;
+    if (wf & WF_F_OUT) fl |= FC_FRONT_OUT;
+    if (wf & WF_F_SPACE) fl |= FC_FRONT_SPACE;
+    if (nm) fl |= FC_NM;
+    f.fl = fl;
+    f.kpos = back ? c.kpos_b : c.kpos_f;
+    f.kneg = back ? c.kneg_b : c.kneg_f;
+    f.eps4s = back ? c.eps4s_b : c.eps4s_f;
+    f.area = c.area;
+    f.v_end = back ? c.vL : c.v0;
+    f.alpha_end = back ? c.abL : c.af0;
+    f.amb = back ? c.amb_b : c.amb_f;
+    f.ov = back ? c.ov_b : c.ov_f;
+    f.forced_c = c.forced_c; f.nx = c.nx; f.ny = c.ny;
+    f.eps = c.eps_f;
+    f.u_nb = u_nb;
+    f.amb_front = c.amb_f;
+    f.zone = back ? c.zb : c.zf;
+    f.zone_front = c.zf;
+    f.site = c.site; f.desc_index = c.desc_index; f.n = c.n;
+}
+// Dynamic state of one face (registers of the face lane).
+struct FaceS {
+    double h, flow, sol, ir;   // this face's 4 SimulationState slots (surface.rs:428-442)
+    double e;                  // ∫ flow·A dt
+    double ts;                 // temperature of the face's end node
+    double solar;              // clamped irradiance of this main step (surface.rs:916-923)
+    double trad_out;           // outdoor radiant temperature of this main step (surface.rs:647,692)
+    double air, forced;        // carried from the pre- to the post-march phase of a sub-step
+    unsigned long long nm_iters;
+    int32_t status;
+};
+// surface.rs:916-931,647,692 for one face. `sol_front` is the FRONT irradiance slot: the reference's back clamp
+// tests it (surface.rs:921).
+HB_HD void face_begin_main_step(const FaceC& c, FaceS& w, double sol_front) {
+    double s = w.sol;
+    if (c.fl & FC_BACK) {
+        if (s != s || sol_front < 0.0) s = 0.0;
+    } else {
+        if (s != s || s < 0.0) s = 0.0;
+    }
+    w.solar = s;
+    w.trad_out = sqrt(sqrt(w.ir / kSigma)) - 273.15;
+}
+// Film coefficient of a face for end-node temperature ts_env (border() for one face).
+HB_HD double face_h(const FaceC& c, const FaceS& w, double ts_env, int& status) {
+    double h = tarp_natural(w.air, ts_env, c.kpos, c.kneg);
+    if (c.fl & FC_OUT) h += w.forced;
+    if (h != h) status |= ST_NAN_H;
+    return (c.fl & FC_OV) ? c.ov : h;
+}
+// One no-mass end node (chunk (0,1) or (n-1,n)): damped fixed point of surface.rs:790-898 on a 1x1 system.
+//   K = -(h + u),  q = air·h + rad·(trad - T) + u·T_neighbour (+ absorbed solar)
+HB_HD double solve_end_node(double air, double h, double rad, double trad, double u, double t_nb, double sol, double t,
+                            unsigned long long& iters, int& status) {
+    const double dd = -h - u;
+    const double r = 1.0 / dd;
+    const double qn = u * t_nb;
+    double old_err = 99999.;
+    int count = 0;
+    while (true) {
+        ++iters;
+        const double rhs = -(((air * h + rad * (trad - t)) + qn) + sol);
+        const double x = rhs * r;
+        const double err = fabs(x - t);
+        if (err > old_err) break;
+        if (err != err) { status |= ST_NAN_ERR; break; }
+        t = (t + x) * 0.5;
+        const double tol = count < 100 ? 0.01 : 0.5;
+        if (err < tol) break;
+        old_err = err;
+        ++count;
+        if (count > 100000) { status |= ST_ITER_CAP; break; }
+    }
+    return t;
+}
+// Before the nodes march (scalar_pre for one face).  zone_t: temperature of the zone this face looks at (FC_SPACE);
+// t_front/ts_front: air temperature and end-node temperature of the wall's FRONT face (FC_BACK_AMB only);
+// t_nb: neighbour node of a no-mass end node (FC_NM).  Returns ghost temperature and link coefficient for the
+// march, and (FC_NM) the end node's new temperature in w.ts.
+HB_HD void face_pre(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
+                    double t_nb, double& ghost, double& link) {
+    const int fl = c.fl;
+    const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0);
+    w.forced = c.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
+    w.air = (fl & FC_OUT) ? sw.t_out : (fl & FC_SPACE) ? zone_t : c.amb;
+    const double trad = (fl & FC_OUT) ? w.trad_out : (fl & FC_BACK_AMB) ? t_front : w.air;
+    const double ts_env = (fl & FC_BACK_AMB) ? ts_front : w.ts;
+    const double h = face_h(c, w, ts_env, w.status);
+    const double xr = 273.15 + (trad + ts_env) / 2.;
+    const double rad = c.eps4s * ((xr * xr) * xr);
+    if (fl & FC_NM)
+        w.ts = solve_end_node(w.air, h, rad, trad, c.u_nb, t_nb, c.alpha_end * w.solar, w.ts, w.nm_iters, w.status);
+    const double hs = h > 1e-12 ? h : 1e-12;
+    ghost = w.air + (rad * (trad - w.ts) + c.alpha_end * w.solar) * fast_rcp(hs);
+    link = hs * c.v_end;
+}
+// After the nodes marched (scalar_post for one face): new film coefficient, convective flow, energy integral and
+// this face's contribution (h·A, h·A·T_s) to calculate_zones_abc.
+HB_HD void face_post(const FaceC& c, FaceS& w, double ts, double ts_front, double dt, double& hA, double& hAT) {
+    w.ts = ts;
+    const double ts_env = (c.fl & FC_BACK_AMB) ? ts_front : ts;
+    w.h = face_h(c, w, ts_env, w.status);
+    w.flow = (ts - w.air) * w.h;
+    w.e += w.flow * c.area * dt;
+    hA = w.h * c.area;
+    hAT = w.h * c.area * ts;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Massive nodes: classic RK4 on  Ṫ = C⁻¹(K·T + q)  (surface.rs:228-308) for one lane's kNL slots.
 // K and q are frozen during a sub-step, so the four stages collapse to
 //     T⁺ = T + p + M p/2 + M² p/6 + M³ p/24,   p = M·T (ghost nodes carry q),   M = diag(dt/C)·K,

@@ -279,6 +279,235 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
     }
     for (int t = 0; t < tile.n_zones; ++t) V.zoneT[(int64_t)tile.zone_begin + t] = zT[t];
 }
+
+// hb_face_kernel's data flow (all-massive tiles and tiles whose no-mass chunks are single end nodes): per-face lanes.
+void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, double* zone_rec_base) {
+    const int G = tile.G, W = tile.W, NT = G * W, NL = kNL;
+    const bool END = tile.flags & TILE_END;
+    const int S = tile.S;
+    const double dt = tile.dt;
+    const int64_t NS = V.n_dev_surfaces;
+    std::vector<double> T(NT * NL), A(NT * NL), B(NT * NL), Vv(NT * NL);
+    std::vector<FaceC> fc(2 * W);
+    std::vector<FaceS> fs(2 * W);
+    std::vector<char> have(W, 0);
+    std::vector<ZoneC> zc(W);
+    std::vector<double> zT(W, 0.), pub0(W, 0.), pub1(W, 0.), pub2(W, 0.), pub3(W, 0.);
+    std::vector<double> e0(W, 0.), e1(W, 0.), e2(W, 0.), e3(W, 0.), link(6 * W, 0.), ir_state(W, 0.);
+    std::vector<int32_t> zf(W, -1), zb(W, -1);
+    std::vector<SubWeather> swt(kMaxSubsteps);
+    for (int tid = 0; tid < NT; ++tid)
+        for (int i = 0; i < NL; ++i) {
+            const int64_t o = tile.node_offset + (int64_t)i * NT + tid;
+            T[tid * NL + i] = V.nodeT[o];
+            A[tid * NL + i] = V.coefA[o];
+            B[tid * NL + i] = V.coefB[o];
+        }
+    auto publish_ends = [&]() {
+        for (int tid = 0; tid < NT; ++tid) {
+            const int wl = tid / G, part = tid % G;
+            const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
+            const int iN = n - part * NL;
+            if (part == 0) { e0[wl] = T[tid * NL + 1]; e1[wl] = T[tid * NL + 2]; }
+            for (int i = 0; i < NL; ++i) {
+                if (i == iN) e3[wl] = T[tid * NL + i];
+                if (i == iN - 1) e2[wl] = T[tid * NL + i];
+            }
+        }
+    };
+    publish_ends();
+    for (int t = 0; t < W; ++t) {
+        const int64_t sg = (int64_t)tile.surface_begin + t;
+        if (V.n_nodes[sg] > 0) {
+            have[t] = 1;
+            WallC c;
+            load_wallc(V, sg, P.single_site != 0, c);
+            const int flg = V.flags[sg];
+            for (int k = 0; k < 2; ++k) {
+                const bool nm = END && ((flg >> (k ? 11 : 10)) & 1);
+                load_facec(c, k == 1, k ? V.u_b[sg] : V.u_f[sg], nm, fc[2 * t + k]);
+                FaceS w{};
+                w.h = V.sc[(0 + k) * NS + sg]; w.flow = V.sc[(2 + k) * NS + sg];
+                w.sol = V.sc[(4 + k) * NS + sg]; w.ir = V.sc[(6 + k) * NS + sg];
+                w.ts = k ? e3[t] : e0[t];
+                fs[2 * t + k] = w;
+            }
+            zf[t] = c.zf; zb[t] = c.zb;
+            ir_state[t] = fs[2 * t].ir;
+        }
+        const int64_t gz = (int64_t)tile.zone_begin + t;
+        ZoneC z{};
+        if (t < tile.n_zones) {
+            z.vol = V.zvol[gz]; z.q = V.zq[gz]; z.inf_v = V.zinf_v[gz]; z.inf_t = V.zinf_t[gz];
+            z.vent_v = V.zvent_v[gz]; z.vent_t = V.zvent_t[gz]; z.sb = V.z_surf_begin[gz]; z.se = V.z_surf_end[gz];
+            zT[t] = V.zoneT[gz];
+        }
+        zc[t] = z;
+    }
+    auto weather_at = [&](int site, int step, int s, SubWeather& out) {
+        const double* wtab = P.weather + (int64_t)site * P.weather_rows * 3;
+        const double* w0 = wtab + (int64_t)step * 3;
+        double t_out, wdir, wspeed;
+        if (P.weather_mode == HB_WEATHER_LINEAR) {
+            const double f = (double)(s + 1) / (double)S;
+            t_out = lerp_rn(w0[0], w0[3], f); wdir = lerp_rn(w0[1], w0[4], f); wspeed = lerp_rn(w0[2], w0[5], f);
+        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+            w0 = wtab + ((int64_t)step * S + s) * 3;
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        } else {
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        }
+        sub_weather(t_out, wdir, wspeed, out);
+    };
+    int rec = 0;
+    std::vector<double> left(NT), right(NT);
+    for (int step = 0; step < P.n_steps; ++step) {
+        if (P.single_site)
+            for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
+        for (int t = 0; t < W; ++t) {
+            if (!have[t]) continue;
+            double sol_front = fs[2 * t].sol;
+            for (int k = 0; k < 2; ++k) {
+                const FaceC& c = fc[2 * t + k];
+                FaceS& w = fs[2 * t + k];
+                if (P.input_mode != HB_INPUT_STATE) {
+                    const double* in = P.input_mode == HB_INPUT_SITE
+                                           ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
+                                           : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
+                    w.sol = in[k]; w.ir = in[2 + k];
+                    sol_front = in[0];
+                    if (k == 0 && P.ir_mode == HB_IR_NET_GAIN) {
+                        if (c.eps > 1e-3) {
+                            const double tk = w.ts + 273.15;
+                            const double tk2 = tk * tk;
+                            w.ir = w.ir / c.area / c.eps + kSigma * (tk2 * tk2);
+                        } else {
+                            w.ir = ir_state[t];
+                        }
+                    }
+                }
+                face_begin_main_step(c, w, sol_front);
+            }
+        }
+        for (int s = 0; s < S; ++s) {
+            for (int t = 0; t < W; ++t) {
+                if (!have[t]) continue;
+                for (int k = 0; k < 2; ++k) {
+                    const FaceC& c = fc[2 * t + k];
+                    FaceS& w = fs[2 * t + k];
+                    SubWeather sw;
+                    if (P.single_site) sw = swt[s];
+                    else weather_at(c.site, step, s, sw);
+                    const double zone_t = c.zone >= 0 ? zT[c.zone] : 0.;
+                    double t_front = 0., ts_front = 0., t_nb = 0.;
+                    if (c.fl & FC_BACK_AMB) {
+                        t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out : (c.fl & FC_FRONT_SPACE) ? zT[c.zone_front] : c.amb_front;
+                        ts_front = e0[t];
+                    }
+                    if (c.fl & FC_NM) t_nb = k ? e2[t] : e1[t];
+                    double ghost, lk;
+                    face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, lk);
+                    link[(k ? 2 : 0) * W + t] = ghost;
+                    link[(k ? 3 : 1) * W + t] = lk;
+                    link[(k ? 5 : 4) * W + t] = w.ts;
+                }
+            }
+            for (int tid = 0; tid < NT; ++tid) {
+                const int wl = tid / G, part = tid % G;
+                const int64_t g = (int64_t)tile.surface_begin + wl;
+                const int n = V.n_nodes[g];
+                const int nmf = END ? (V.flags[g] >> 10) & 1 : 0, nmb = END ? (V.flags[g] >> 11) & 1 : 0;
+                double* t = &T[tid * NL];
+                if (part == 0) {
+                    t[0] = link[0 * W + wl];
+                    B[tid * NL + 1] = link[1 * W + wl];
+                    if (nmf) t[1] = link[4 * W + wl];
+                }
+                for (int i = 0; i < NL; ++i) {
+                    if (i == n - part * NL) {
+                        A[tid * NL + i] = link[3 * W + wl];
+                        if (nmb) t[i] = link[5 * W + wl];
+                    }
+                    if (i == n + 1 - part * NL) t[i] = link[2 * W + wl];
+                }
+            }
+            auto halos = [&](const std::vector<double>& x) {
+                for (int tid = 0; tid < NT; ++tid) {
+                    const int part = tid % G;
+                    left[tid] = part > 0 ? x[(tid - 1) * NL + NL - 1] : x[tid * NL + NL - 1];
+                    right[tid] = part < G - 1 ? x[(tid + 1) * NL] : x[tid * NL];
+                }
+            };
+            using Arr = double(&)[kNL];
+            halos(T);
+            for (int tid = 0; tid < NT; ++tid) {
+                sweep_first<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid], right[tid]);
+                for (int i = 0; i < NL; ++i) T[tid * NL + i] += Vv[tid * NL + i];
+            }
+            const double cs[3] = {1. / 2., 1. / 6., 1. / 24.};
+            for (int k = 0; k < 3; ++k) {
+                halos(Vv);
+                for (int tid = 0; tid < NT; ++tid)
+                    sweep_next<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid],
+                                    right[tid], cs[k]);
+            }
+            publish_ends();
+            for (int t = 0; t < W; ++t) {
+                if (!have[t]) continue;
+                for (int k = 0; k < 2; ++k) {
+                    double hA, hAT;
+                    face_post(fc[2 * t + k], fs[2 * t + k], k ? e3[t] : e0[t], e0[t], dt, hA, hAT);
+                    (k ? pub2 : pub0)[t] = hA;
+                    (k ? pub3 : pub1)[t] = hAT;
+                }
+            }
+            std::vector<double> znew(zT);
+            for (int t = 0; t < tile.n_zones; ++t) {
+                const double tn = zone_update(zc[t], t, zT[t], dt, pub0.data(), pub1.data(), pub2.data(), pub3.data(),
+                                              zf.data(), zb.data());
+                if (tn != tn) V.status[(int64_t)tile.surface_begin + zc[t].sb] |= ST_NAN_ZONE;
+                znew[t] = tn;
+            }
+            zT = znew;
+        }
+        if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
+            if (zone_rec_base)
+                for (int t = 0; t < tile.n_zones; ++t)
+                    zone_rec_base[(int64_t)rec * V.n_dev_zones + tile.zone_begin + t] = zT[t];
+            if (P.node_rec) {
+                for (int tid = 0; tid < NT; ++tid)
+                    for (int i = 0; i < NL; ++i)
+                        P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * NT + tid] = T[tid * NL + i];
+                for (int t = 0; t < W; ++t) {
+                    if (!have[t]) continue;
+                    const int64_t sg = (int64_t)tile.surface_begin + t;
+                    double* r = P.sc_rec + (int64_t)rec * 8 * NS;
+                    for (int k = 0; k < 2; ++k) {
+                        const FaceS& w = fs[2 * t + k];
+                        r[(0 + k) * NS + sg] = w.h; r[(2 + k) * NS + sg] = w.flow;
+                        r[(4 + k) * NS + sg] = w.sol; r[(6 + k) * NS + sg] = w.ir;
+                    }
+                }
+            }
+            ++rec;
+        }
+    }
+    for (int tid = 0; tid < NT; ++tid)
+        for (int i = 0; i < NL; ++i) V.nodeT[tile.node_offset + (int64_t)i * NT + tid] = T[tid * NL + i];
+    for (int t = 0; t < W; ++t) {
+        if (!have[t]) continue;
+        const int64_t sg = (int64_t)tile.surface_begin + t;
+        for (int k = 0; k < 2; ++k) {
+            const FaceS& w = fs[2 * t + k];
+            V.sc[(0 + k) * NS + sg] = w.h; V.sc[(2 + k) * NS + sg] = w.flow;
+            V.sc[(4 + k) * NS + sg] = w.sol; V.sc[(6 + k) * NS + sg] = w.ir;
+            (k ? V.energy_b : V.energy_f)[sg] += w.e;
+            V.nm_iters[sg] += w.nm_iters;
+            V.status[sg] |= w.status;
+        }
+    }
+    for (int t = 0; t < tile.n_zones; ++t) V.zoneT[(int64_t)tile.zone_begin + t] = zT[t];
+}
 }  // namespace
 
 extern "C" {
@@ -327,7 +556,10 @@ int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, con
                 P.sc_rec = sr.data();
             }
         }
-        for (const Tile& t : B.tiles) march_tile(V, P, t, zr.empty() ? nullptr : zr.data());
+        for (const Tile& t : B.tiles) {
+            if (t.flags & (TILE_EXT | TILE_DIST)) march_tile(V, P, t, zr.empty() ? nullptr : zr.data());
+            else march_tile_face(V, P, t, zr.empty() ? nullptr : zr.data());
+        }
         if (P.record_every) {
             const int64_t nz_total = (int64_t)B.zone_volume.size();
             for (int r = 0; r < n_rec; ++r) {
