@@ -7,7 +7,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libheat_b200.so")
+LIB_PATH = os.environ.get("HEAT_B200_LIB") or os.path.join(_HERE, "libheat_b200.so")
 
 HB_OK, HB_ERR_INVALID, HB_ERR_CUDA, HB_ERR_PHYSICS, HB_ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 WEATHER_STEP_CONSTANT, WEATHER_LINEAR, WEATHER_PER_SUBSTEP = 0, 1, 2

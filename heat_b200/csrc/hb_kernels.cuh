@@ -345,16 +345,88 @@ __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V
 //
 // The time of a series is set by the dependent chain  scalar physics → march → scalar physics → zone  of the tiles
 // with the most sub-steps, so this kernel shortens that chain:
+//   * tiles are as small as the models allow (64 threads: more independent chains per SM, shorter node phase);
 //   * the FRONT and BACK faces of wall j are evaluated by lane j of two different warps (two SM sub-partitions);
-//   * the zone update is done by the back-face warp; the front-face warp only signals (bar.arrive) and goes on to
-//     the next sub-step's border conditions unless a front face of the tile looks at a zone;
+//   * between two node marches a face lane runs  post(s) → zone → pre(s+1)  as one straight-line region; the
+//     sub-step weather table of the NEXT main step is prepared one step ahead (double buffer);
+//   * "simple" tiles (every zone has exactly one wall, whose back face looks at it — a wall with its own zone):
+//     the back-face lane advances its zone in registers, no shared-memory exchange and no pair barrier;
+//     otherwise the zone sums go through shared memory and the front warp only signals (bar.arrive) unless one of
+//     its faces looks at a zone;
 //   * single-node no-mass ends are solved in the face lane's registers (solve_end_node) from the two temperatures
-//     the node lanes publish per end — no shared-memory mirror of the wall.
+//     the node lanes publish per end — no shared-memory mirror of the wall;
+//   * in the node phase the two edge slots of a lane are evaluated first and their values shuffled to the
+//     neighbouring lanes while the six inner slots are computed.
 // ----------------------------------------------------------------------------------------------------------------
+#ifdef HB_PHASE_CLOCKS
+__device__ unsigned long long hb_phase_clk[8];   // wait B1, node, wait B2, post, zone, pre, -, sub-steps
+#define HB_CLK(k) { const long long _t = clock64(); clk[k] += _t - tlast; tlast = _t; }
+#else
+#define HB_CLK(k)
+#endif
 __device__ __forceinline__ void pair_sync() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
 __device__ __forceinline__ void pair_arrive() { asm volatile("bar.arrive 1, 64;" ::: "memory"); }
 
 __host__ __device__ constexpr int face_threads(int G, int W) { return G * W >= 64 ? G * W : 64; }
+
+// One sub-step of RK4 for a lane's kNL slots (see sweep_first/sweep_next in hb_math.cuh for the algebra), with the
+// edge slots first: their results are what the neighbouring lanes need for the next sweep.
+template <int G, int NL>
+__device__ __forceinline__ void node_rk4(double (&T)[NL], const double (&A)[NL], const double (&B)[NL]) {
+    constexpr unsigned FULL = 0xffffffffu;
+    double X[NL];
+    double left = 0., right = 0.;
+    if constexpr (G > 1) {
+        left = __shfl_up_sync(FULL, T[NL - 1], 1, G);
+        right = __shfl_down_sync(FULL, T[0], 1, G);
+    }
+    // sweep 1: X = M·T
+    {
+        const double d0 = T[1] - T[0], dl = T[0] - left;
+        const double dr = right - T[NL - 1], dm = T[NL - 1] - T[NL - 2];
+        X[0] = A[0] * d0 - B[0] * dl;
+        X[NL - 1] = A[NL - 1] * dr - B[NL - 1] * dm;
+        if constexpr (G > 1) {
+            left = __shfl_up_sync(FULL, X[NL - 1], 1, G);
+            right = __shfl_down_sync(FULL, X[0], 1, G);
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double dnext = T[i + 1] - T[i];
+            X[i] = A[i] * dnext - B[i] * dprev;
+            dprev = dnext;
+        }
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] += X[i];
+    }
+    // sweeps 2-4: X ← M·X, T += c·X
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double c = k == 0 ? 1. / 2. : k == 1 ? 1. / 6. : 1. / 24.;
+        const double d0 = X[1] - X[0], dl = X[0] - left;
+        const double dr = right - X[NL - 1], dm = X[NL - 1] - X[NL - 2];
+        const double x0 = A[0] * d0 - B[0] * dl;
+        const double xl = A[NL - 1] * dr - B[NL - 1] * dm;
+        if constexpr (G > 1) {
+            if (k < 2) {
+                left = __shfl_up_sync(FULL, xl, 1, G);
+                right = __shfl_down_sync(FULL, x0, 1, G);
+            }
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double dnext = (i + 1 == NL - 1 ? X[NL - 1] : X[i + 1]) - X[i];
+            X[i] = A[i] * dnext - B[i] * dprev;
+            dprev = dnext;
+        }
+        X[0] = x0;
+        X[NL - 1] = xl;
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] = fma(c, X[i], T[i]);
+    }
+}
 
 template <int G, int W, bool END>
 __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
@@ -363,9 +435,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     constexpr int TPB = face_threads(G, W);     // a tile of 32 node lanes gets a second warp for the back faces
     constexpr int NL = kNL;
     constexpr int NWARP = TPB / 32;
-    constexpr bool SPLIT = true;
-    constexpr int NF = 1;
-    static_assert(NT >= 32 && NT % 32 == 0 && W <= 32, "tile shape");
+    static_assert(NT >= 32 && NT % 32 == 0 && W <= 32 && NWARP >= 2, "tile shape");
     const Tile tile = V.tiles[tile_ids[blockIdx.x]];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t NS = V.n_dev_surfaces;
@@ -376,12 +446,13 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     __shared__ int32_t s_zf[W], s_zb[W];
     __shared__ double s_end[4][W];      // node 0, node 1, node n-2, node n-1
     __shared__ double s_link[6][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
-    __shared__ SubWeather s_w[kMaxSubsteps];
+    __shared__ SubWeather s_w[2][kMaxSubsteps];
+    __shared__ FaceC s_fc[2][W];        // per-face constants: read from shared memory where they are used
 
     const int S = tile.S;
     const double dt = tile.dt;
 
-    // ---- node role (identical to hb_march_kernel) ----
+    // ---- node role ----
     const bool node_lane = NT == TPB || tid < NT;   // warp-uniform
     const int wl = node_lane ? tid / G : 0, part = tid % G;
     const int64_t g = (int64_t)tile.surface_begin + wl;
@@ -389,7 +460,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     const int iN = n - part * NL;        // lane-local index of the last node's slot (slot n)
     const int iG = n + 1 - part * NL;    // … of the back ghost (slot n+1)
     const int nmf = END ? (V.flags[g] >> 10) & 1 : 0, nmb = END ? (V.flags[g] >> 11) & 1 : 0;
-    double T[NL], A[NL], B[NL], Vv[NL];
+    double T[NL], A[NL], B[NL];
     if (node_lane) {
         const int64_t o = tile.node_offset + tid;
 #pragma unroll
@@ -402,169 +473,179 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
 #pragma unroll
         for (int i = 0; i < NL; ++i) T[i] = A[i] = B[i] = 0.;
     }
+    // value of the lane-local slot k (0 <= k < NL) as a 3-level mux: no divergent branches
+    auto slot = [&](int k) {
+        const double a0 = (k & 1) ? T[1] : T[0], a1 = (k & 1) ? T[3] : T[2], a2 = (k & 1) ? T[5] : T[4],
+                     a3 = (k & 1) ? T[7] : T[6];
+        const double b0 = (k & 2) ? a1 : a0, b1 = (k & 2) ? a3 : a2;
+        return (k & 4) ? b1 : b0;
+    };
+    static_assert(NL == 8, "slot() is an 8-way mux");
+    const bool has_last = iN >= 0 && iN < NL, has_prev = END && iN - 1 >= 0 && iN - 1 < NL;
+    double* const p_last = &s_end[3][wl];
+    double* const p_prev = &s_end[2][wl];
     auto publish_ends = [&]() {
         if (part == 0) {
             s_end[0][wl] = T[1];
             if constexpr (END) s_end[1][wl] = T[2];
         }
-#pragma unroll
-        for (int i = 0; i < NL; ++i) {
-            if (i == iN) s_end[3][wl] = T[i];
-            if constexpr (END)
-                if (i == iN - 1) s_end[2][wl] = T[i];
-        }
+        if (has_last) *p_last = slot(iN);
+        if constexpr (END)
+            if (has_prev) *p_prev = slot(iN - 1);
     };
     if (node_lane) publish_ends();
 
     // ---- face role ----
-    const int wf = SPLIT ? (int)(blockIdx.x % NWARP) : 0;          // warp of the front faces
-    const int wb = SPLIT ? (wf + 1) % NWARP : 0;                   // warp of the back faces and of the zones
+    const int wf = (int)(blockIdx.x % NWARP);     // warp of the front faces
+    const int wb = (wf + 1) % NWARP;              // warp of the back faces and of the zones
     const bool face_warp = warp == wf || warp == wb;
-    const int64_t sg = (int64_t)tile.surface_begin + lane;          // lane j ↔ wall j
-    const bool fwall = face_warp && lane < W && V.n_nodes[lane < W ? sg : (int64_t)tile.surface_begin] > 0;
-    const bool szone = warp == wb && lane < tile.n_zones;
+    const bool back = warp == wb;
+    const int kf = back ? 1 : 0;
+    const int64_t sg = (int64_t)tile.surface_begin + (lane < W ? lane : 0);   // lane j ↔ wall j
+    const bool fwall = face_warp && lane < W && V.n_nodes[sg] > 0;
+    const bool szone = back && lane < tile.n_zones;
     const int64_t sgz = (int64_t)tile.zone_begin + lane;
-    FaceC fc[NF];
-    FaceS fs[NF];
-    bool any_front_zone = false;
+    const FaceC& c = s_fc[kf][lane < W ? lane : 0];
+    FaceS w{};
+    double zT = 0.;        // this lane's zone temperature
+    double za0 = 0., zb0 = 0.;   // a, b of the zone's non-surface sources (constant over a series)
+    bool any_front_zone = false, simple_ok = true;
+    {
+        ZoneC zc{};
+        if (szone) {
+            zc.vol = V.zvol[sgz]; zc.q = V.zq[sgz]; zc.inf_v = V.zinf_v[sgz]; zc.inf_t = V.zinf_t[sgz];
+            zc.vent_v = V.zvent_v[sgz]; zc.vent_t = V.zvent_t[sgz]; zc.sb = V.z_surf_begin[sgz];
+            zc.se = V.z_surf_end[sgz];
+            zT = V.zoneT[sgz];
+            s_zT[lane] = zT;
+            simple_ok = zc.sb == lane && zc.se == lane + 1;
+            zone_sources(zc, za0, zb0);
+        }
+        if (back && lane < W) s_zc[lane] = zc;
+    }
     if (fwall) {
-        WallC c;
-        load_wallc(V, sg, P.single_site != 0, c);
+        WallC wc;
+        load_wallc(V, sg, P.single_site != 0, wc);
         const int flg = V.flags[sg];
-#pragma unroll
-        for (int r = 0; r < NF; ++r) {
-            const bool back = SPLIT ? warp == wb : r == 1;
-            const bool nm = END && ((flg >> (back ? 11 : 10)) & 1);
-            load_facec(c, back, back ? V.u_b[sg] : V.u_f[sg], nm, fc[r]);
-            FaceS w{};
-            const int k = back ? 1 : 0;
-            w.h = V.sc[(0 + k) * NS + sg]; w.flow = V.sc[(2 + k) * NS + sg];
-            w.sol = V.sc[(4 + k) * NS + sg]; w.ir = V.sc[(6 + k) * NS + sg];
-            fs[r] = w;
+        const bool nm = END && ((flg >> (back ? 11 : 10)) & 1);
+        load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][lane]);
+        w.h = V.sc[(0 + kf) * NS + sg]; w.flow = V.sc[(2 + kf) * NS + sg];
+        w.sol = V.sc[(4 + kf) * NS + sg]; w.ir = V.sc[(6 + kf) * NS + sg];
+        if (back) {
+            s_zf[lane] = wc.zf;
+            s_zb[lane] = wc.zb;
+            simple_ok = simple_ok && wc.zb == lane && szone;
         }
-        if (warp == wb) {
-            s_zf[lane] = c.zf;
-            s_zb[lane] = c.zb;
-        }
-        any_front_zone = c.zf >= 0;
-    } else if (warp == wb && lane < W) {
+        any_front_zone = wc.zf >= 0;
+    } else if (back && lane < W) {
         s_zf[lane] = -1;
         s_zb[lane] = -1;
-    }
-    if (warp == wb && lane < W) {
-        ZoneC z{};
-        if (lane < tile.n_zones) {
-            z.vol = V.zvol[sgz]; z.q = V.zq[sgz]; z.inf_v = V.zinf_v[sgz]; z.inf_t = V.zinf_t[sgz];
-            z.vent_v = V.zvent_v[sgz]; z.vent_t = V.zvent_t[sgz]; z.sb = V.z_surf_begin[sgz]; z.se = V.z_surf_end[sgz];
-            s_zT[lane] = V.zoneT[sgz];
-        }
-        s_zc[lane] = z;
+        simple_ok = simple_ok && !szone;
     }
     // the front warp has to wait for the zone update only if one of its faces looks at a zone
     const bool front_waits = __syncthreads_or(any_front_zone ? 1 : 0) != 0;
-    if (fwall) {
-#pragma unroll
-        for (int r = 0; r < NF; ++r) fs[r].ts = s_end[(fc[r].fl & FC_BACK) ? 3 : 0][lane];
-    }
-    double ir_state = fs[0].ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
+    const bool simple = __syncthreads_and(simple_ok ? 1 : 0) != 0 && !front_waits;
+    if (fwall) w.ts = s_end[back ? 3 : 0][lane];
+    const double ir_state = w.ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
 
+    // sub-step weather of main step `step` into buffer step & 1 (all threads of the block)
+    auto fill_weather = [&](int step) {
+        if (!P.single_site) return;
+        const double* w0 = P.weather + (int64_t)step * 3;
+        if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) w0 = P.weather + (int64_t)step * S * 3;
+        for (int s = tid; s < S; s += TPB) {
+            double t_out, wdir, wspeed;
+            if (P.weather_mode == HB_WEATHER_LINEAR) {
+                const double f = (double)(s + 1) / (double)S;
+                t_out = lerp_rn(w0[0], w0[3], f);
+                wdir = lerp_rn(w0[1], w0[4], f);
+                wspeed = lerp_rn(w0[2], w0[5], f);
+            } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+                t_out = w0[3 * s + 0]; wdir = w0[3 * s + 1]; wspeed = w0[3 * s + 2];
+            } else {
+                t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+            }
+            sub_weather(t_out, wdir, wspeed, s_w[step & 1][s]);
+        }
+    };
+    // what the caller writes into SimulationState before a main step + the per-step derived quantities
+    auto main_step_inputs = [&](int step) {
+        double sol_front = back ? V.sc[4 * NS + sg] : w.sol;
+        if (P.input_mode != HB_INPUT_STATE) {
+            const double* in = P.input_mode == HB_INPUT_SITE
+                                   ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
+                                   : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
+            w.sol = in[kf];
+            w.ir = in[2 + kf];
+            sol_front = in[0];
+            if (!back && P.ir_mode == HB_IR_NET_GAIN) {
+                // validate_wall_heat_transfer.rs:689-699 (front face only, as in the reference driver)
+                if (c.eps > 1e-3) {
+                    const double tk = w.ts + 273.15;
+                    const double tk2 = tk * tk;
+                    w.ir = w.ir / c.area / c.eps + kSigma * (tk2 * tk2);
+                } else {
+                    w.ir = ir_state;
+                }
+            }
+        }
+        face_begin_main_step(c, w, sol_front);
+    };
+    // border conditions of sub-step s of main step `step` → links for the node lanes
+    auto pre = [&](int step, int s) {
+        SubWeather sw;
+        if (P.single_site) {
+            sw = s_w[step & 1][s];
+        } else {
+            const double* wtab = P.weather + (int64_t)c.site * P.weather_rows * 3;
+            const double* w0 = wtab + (int64_t)step * 3;
+            double t_out, wdir, wspeed;
+            if (P.weather_mode == HB_WEATHER_LINEAR) {
+                const double f = (double)(s + 1) / (double)S;
+                t_out = lerp_rn(w0[0], w0[3], f);
+                wdir = lerp_rn(w0[1], w0[4], f);
+                wspeed = lerp_rn(w0[2], w0[5], f);
+            } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+                w0 = wtab + ((int64_t)step * S + s) * 3;
+                t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+            } else {
+                t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+            }
+            sub_weather(t_out, wdir, wspeed, sw);
+        }
+        const double zone_t = simple ? zT : (c.zone >= 0 ? s_zT[c.zone] : 0.);
+        double t_front = 0., ts_front = 0., t_nb = 0.;
+        if (c.fl & FC_BACK_AMB) {
+            t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out : (c.fl & FC_FRONT_SPACE) ? s_zT[c.zone_front] : c.amb_front;
+            ts_front = s_end[0][lane];
+        }
+        if constexpr (END)
+            if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][lane];
+        double ghost, link;
+        face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, link);
+        s_link[back ? 2 : 0][lane] = ghost;
+        s_link[back ? 3 : 1][lane] = link;
+        if constexpr (END) s_link[back ? 5 : 4][lane] = w.ts;
+    };
+
+    fill_weather(0);
+    if (fwall) main_step_inputs(0);
+    __syncthreads();
+    if (fwall) pre(0, 0);
+
+#ifdef HB_PHASE_CLOCKS
+    long long clk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+#endif
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
-        // ---- main-step prologue: sub-step weather table, per-step inputs ----
-        if (P.single_site) {
-            const double* w0 = P.weather + (int64_t)step * 3;
-            if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) w0 = P.weather + (int64_t)step * S * 3;
-            for (int s = tid; s < S; s += TPB) {  // all threads of the block
-                double t_out, wdir, wspeed;
-                if (P.weather_mode == HB_WEATHER_LINEAR) {
-                    const double f = (double)(s + 1) / (double)S;
-                    t_out = lerp_rn(w0[0], w0[3], f);
-                    wdir = lerp_rn(w0[1], w0[4], f);
-                    wspeed = lerp_rn(w0[2], w0[5], f);
-                } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
-                    t_out = w0[3 * s + 0]; wdir = w0[3 * s + 1]; wspeed = w0[3 * s + 2];
-                } else {
-                    t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
-                }
-                sub_weather(t_out, wdir, wspeed, s_w[s]);
-            }
-        }
-        if (fwall) {
-#pragma unroll
-            for (int r = 0; r < NF; ++r) {
-                const FaceC& c = fc[r];
-                FaceS& w = fs[r];
-                const int k = (c.fl & FC_BACK) ? 1 : 0;
-                double sol_front = k ? V.sc[4 * NS + sg] : w.sol;
-                if (!SPLIT && k) sol_front = fs[0].sol;
-                if (P.input_mode != HB_INPUT_STATE) {
-                    const double* in = P.input_mode == HB_INPUT_SITE
-                                           ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
-                                           : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
-                    w.sol = in[k];
-                    w.ir = in[2 + k];
-                    sol_front = in[0];
-                    if (k == 0 && P.ir_mode == HB_IR_NET_GAIN) {
-                        // validate_wall_heat_transfer.rs:689-699 (front face only, as in the reference driver)
-                        if (c.eps > 1e-3) {
-                            const double tk = w.ts + 273.15;
-                            const double tk2 = tk * tk;
-                            w.ir = w.ir / c.area / c.eps + kSigma * (tk2 * tk2);
-                        } else {
-                            w.ir = ir_state;
-                        }
-                    }
-                }
-                face_begin_main_step(c, w, sol_front);
-            }
-        }
-        __syncthreads();
-
+        if (step + 1 < P.n_steps) fill_weather(step + 1);   // read from the next main step's first pre() on
         for (int s = 0; s < S; ++s) {
-            // ================= face role, before the march =================
-            if (fwall) {
-#pragma unroll
-                for (int r = 0; r < NF; ++r) {
-                    const FaceC& c = fc[r];
-                    FaceS& w = fs[r];
-                    SubWeather sw;
-                    if (P.single_site) {
-                        sw = s_w[s];
-                    } else {
-                        const double* wtab = P.weather + (int64_t)c.site * P.weather_rows * 3;
-                        const double* w0 = wtab + (int64_t)step * 3;
-                        double t_out, wdir, wspeed;
-                        if (P.weather_mode == HB_WEATHER_LINEAR) {
-                            const double f = (double)(s + 1) / (double)S;
-                            t_out = lerp_rn(w0[0], w0[3], f);
-                            wdir = lerp_rn(w0[1], w0[4], f);
-                            wspeed = lerp_rn(w0[2], w0[5], f);
-                        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
-                            w0 = wtab + ((int64_t)step * S + s) * 3;
-                            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
-                        } else {
-                            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
-                        }
-                        sub_weather(t_out, wdir, wspeed, sw);
-                    }
-                    const bool back = (c.fl & FC_BACK) != 0;
-                    const double zone_t = c.zone >= 0 ? s_zT[c.zone] : 0.;
-                    double t_front = 0., ts_front = 0., t_nb = 0.;
-                    if (c.fl & FC_BACK_AMB) {
-                        t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out
-                                  : (c.fl & FC_FRONT_SPACE) ? s_zT[c.zone_front] : c.amb_front;
-                        ts_front = SPLIT ? s_end[0][lane] : fs[0].ts;
-                    }
-                    if constexpr (END)
-                        if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][lane];
-                    double ghost, link;
-                    face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, link);
-                    s_link[back ? 2 : 0][lane] = ghost;
-                    s_link[back ? 3 : 1][lane] = link;
-                    if constexpr (END) s_link[back ? 5 : 4][lane] = w.ts;
-                }
-            }
+#ifdef HB_PHASE_CLOCKS
+            tlast = clock64();
+            clk[7] += 1;
+#endif
             __syncthreads();
+            HB_CLK(0)
             // ================= node role: RK4 of the massive nodes =================
             if (node_lane) {
                 const double ghost_f = s_link[0][wl], bf = s_link[1][wl], ghost_b = s_link[2][wl], ab = s_link[3][wl];
@@ -583,103 +664,86 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
                     }
                     if (i == iG) T[i] = ghost_b;
                 }
-                double left = 0., right = 0.;
-                if constexpr (G > 1) {
-                    left = __shfl_up_sync(0xffffffffu, T[NL - 1], 1, G);
-                    right = __shfl_down_sync(0xffffffffu, T[0], 1, G);
-                }
-                sweep_first<NL>(T, Vv, A, B, left, right);
-#pragma unroll
-                for (int i = 0; i < NL; ++i) T[i] += Vv[i];
-                if constexpr (G > 1) {
-                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
-                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
-                }
-                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 2.);
-                if constexpr (G > 1) {
-                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
-                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
-                }
-                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 6.);
-                if constexpr (G > 1) {
-                    left = __shfl_up_sync(0xffffffffu, Vv[NL - 1], 1, G);
-                    right = __shfl_down_sync(0xffffffffu, Vv[0], 1, G);
-                }
-                sweep_next<NL>(T, Vv, A, B, left, right, 1. / 24.);
+                node_rk4<G, NL>(T, A, B);
                 publish_ends();
             }
+            HB_CLK(1)
             __syncthreads();
-            // ================= face role, after the march; zones =================
+            HB_CLK(2)
+            // ================= face role: post(s) → zones → pre(s+1) =================
             if (face_warp) {   // warp-uniform
+                double hA = 0., hAT = 0.;
                 if (fwall) {
-#pragma unroll
-                    for (int r = 0; r < NF; ++r) {
-                        const FaceC& c = fc[r];
-                        FaceS& w = fs[r];
-                        const bool back = (c.fl & FC_BACK) != 0;
-                        const double ts = s_end[back ? 3 : 0][lane];
-                        const double ts_front = (c.fl & FC_BACK_AMB) ? s_end[0][lane] : 0.;
-                        double hA, hAT;
-                        face_post(c, w, ts, ts_front, dt, hA, hAT);
+                    const double ts = s_end[back ? 3 : 0][lane];
+                    const double ts_front = (c.fl & FC_BACK_AMB) ? s_end[0][lane] : 0.;
+                    face_post(c, w, ts, ts_front, dt, hA, hAT);
+                }
+                HB_CLK(3)
+                if (simple) {
+                    if (szone) {   // the lane's own wall is the zone's only surface (back face)
+                        const double inv_cc = zone_inv_c(s_zc[lane], zT);
+                        const double a = za0 + hAT, b = zb0 + hA;
+                        const double tn = zone_advance(zT, dt, inv_cc, a, b);
+                        if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
+                        zT = tn;
+                    }
+                } else {
+                    if (fwall) {
                         s_pub[back ? 2 : 0][lane] = hA;
                         s_pub[back ? 3 : 1][lane] = hAT;
                     }
+                    if (back || front_waits) pair_sync(); else pair_arrive();
+                    if (szone) {
+                        const double tn = zone_update(s_zc[lane], lane, s_zT[lane], dt, s_pub[0], s_pub[1], s_pub[2],
+                                                      s_pub[3], s_zf, s_zb);
+                        if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[lane].sb], ST_NAN_ZONE);
+                        s_zT[lane] = tn;
+                        zT = tn;
+                    }
+                    if (front_waits) pair_sync(); else if (back) __syncwarp();
                 }
-                if constexpr (SPLIT) {
-                    if (warp == wb || front_waits) pair_sync(); else pair_arrive();
-                } else {
-                    __syncwarp();
-                }
-                if (szone) {
-                    const double tn = zone_update(s_zc[lane], lane, s_zT[lane], dt, s_pub[0], s_pub[1], s_pub[2], s_pub[3],
-                                                  s_zf, s_zb);
-                    if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[lane].sb], ST_NAN_ZONE);
-                    s_zT[lane] = tn;
-                }
-                if constexpr (SPLIT) {
-                    if (front_waits) pair_sync();
-                } else {
-                    __syncwarp();
-                }
+                HB_CLK(4)
+                if (fwall && s + 1 < S) pre(step, s + 1);
+                HB_CLK(5)
             }
         }
 
         if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
-            if (P.zone_rec && szone) P.zone_rec[(int64_t)rec * V.n_dev_zones + sgz] = s_zT[lane];
+            if (P.zone_rec && szone) P.zone_rec[(int64_t)rec * V.n_dev_zones + sgz] = zT;
             if (P.node_rec) {
 #pragma unroll
                 for (int i = 0; i < NL; ++i)
                     if (node_lane) P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * NT + tid] = T[i];
                 if (fwall) {
                     double* rr = P.sc_rec + (int64_t)rec * 8 * NS;
-#pragma unroll
-                    for (int r = 0; r < NF; ++r) {
-                        const int k = (fc[r].fl & FC_BACK) ? 1 : 0;
-                        rr[(0 + k) * NS + sg] = fs[r].h; rr[(2 + k) * NS + sg] = fs[r].flow;
-                        rr[(4 + k) * NS + sg] = fs[r].sol; rr[(6 + k) * NS + sg] = fs[r].ir;
-                    }
+                    rr[(0 + kf) * NS + sg] = w.h; rr[(2 + kf) * NS + sg] = w.flow;
+                    rr[(4 + kf) * NS + sg] = w.sol; rr[(6 + kf) * NS + sg] = w.ir;
                 }
             }
             ++rec;
         }
+        if (fwall && step + 1 < P.n_steps) {
+            main_step_inputs(step + 1);
+            pre(step + 1, 0);
+        }
     }
 
+#ifdef HB_PHASE_CLOCKS
+    if (back && lane == 0 && S >= 100)
+        for (int q = 0; q < 8; ++q) atomicAdd(&hb_phase_clk[q], (unsigned long long)clk[q]);
+#endif
     // ---- write the state back ----
 #pragma unroll
     for (int i = 0; i < NL; ++i)
         if (node_lane) V.nodeT[tile.node_offset + (int64_t)i * NT + tid] = T[i];
     if (fwall) {
-#pragma unroll
-        for (int r = 0; r < NF; ++r) {
-            const int k = (fc[r].fl & FC_BACK) ? 1 : 0;
-            V.sc[(0 + k) * NS + sg] = fs[r].h; V.sc[(2 + k) * NS + sg] = fs[r].flow;
-            V.sc[(4 + k) * NS + sg] = fs[r].sol; V.sc[(6 + k) * NS + sg] = fs[r].ir;
-            if (k) V.energy_b[sg] += fs[r].e; else V.energy_f[sg] += fs[r].e;
-            if (fs[r].nm_iters) atomicAdd(&V.nm_iters[sg], fs[r].nm_iters);
-            if (fs[r].status) atomicOr(&V.status[sg], fs[r].status);
-        }
+        V.sc[(0 + kf) * NS + sg] = w.h; V.sc[(2 + kf) * NS + sg] = w.flow;
+        V.sc[(4 + kf) * NS + sg] = w.sol; V.sc[(6 + kf) * NS + sg] = w.ir;
+        if (back) V.energy_b[sg] += w.e; else V.energy_f[sg] += w.e;
+        if (w.nm_iters) atomicAdd(&V.nm_iters[sg], w.nm_iters);
+        if (w.status) atomicOr(&V.status[sg], w.status);
     }
-    if (szone) V.zoneT[sgz] = s_zT[lane];
+    if (szone) V.zoneT[sgz] = zT;
 }
 
 #ifdef HB_AUX_KERNELS

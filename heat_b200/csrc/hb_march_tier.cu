@@ -1,4 +1,5 @@
 // hb_march_tier.cu — instantiates hb_march_kernel for one lanes-per-wall tier (compile with -DHB_TIER=G).
+#include <cstdio>
 #include "hb_kernels.cuh"
 
 #define HB_CAT_(a, b) a##b
@@ -24,7 +25,19 @@ cudaError_t launch_variant(int n_tiles, cudaStream_t st, const DevView& V, const
 }
 template <int G, int W, bool END>
 cudaError_t launch_face(int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
+#ifdef HB_PHASE_CLOCKS
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
+    cudaMemcpyToSymbol(hb_phase_clk, z, sizeof(z));
+#endif
     hb_face_kernel<G, W, END><<<n_tiles, face_threads(G, W), 0, st>>>(V, P, ids);
+#ifdef HB_PHASE_CLOCKS
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(o, hb_phase_clk, sizeof(o));
+    if (o[7])
+        fprintf(stderr, "[hb clk] G=%d W=%d END=%d per sub-step of S>=100 tiles: waitB1 %.0f node %.0f waitB2 %.0f post %.0f "
+                "zone %.0f pre %.0f\n", G, W, (int)END, (double)o[0] / o[7], (double)o[1] / o[7], (double)o[2] / o[7],
+                (double)o[3] / o[7], (double)o[4] / o[7], (double)o[5] / o[7]);
+#endif
     return cudaGetLastError();
 }
 

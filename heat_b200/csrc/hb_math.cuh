@@ -498,10 +498,11 @@ struct ZoneC {
     int32_t sb, se;
 };
 
-// model.rs:489-597 + 650-674.  pub_* are the per-wall contributions of the tile, zf/zb the walls' zone indices.
-HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const double* pub_hA_f, const double* pub_hAT_f,
-                         const double* pub_hA_b, const double* pub_hAT_b, const int32_t* zf, const int32_t* zb) {
-    double a = 0.0, b = 0.0;
+// model.rs:489-597 + 650-674, in three pieces so that a zone with a single wall can be advanced by that wall's lane.
+// zone_sources: a, b of everything that is not a surface (model.rs:502-544).
+HB_HD void zone_sources(const ZoneC& z, double& a, double& b) {
+    a = 0.0;
+    b = 0.0;
     a += z.q;
     if (z.inf_t == z.inf_t) {
         const double tk = z.inf_t + 273.15;
@@ -517,20 +518,33 @@ HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const dou
         a += rho * z.vent_v * cp * z.vent_t;
         b += rho * z.vent_v * cp;
     }
+}
+// 1/c with c = V·ρ(T)·cp(T) (zone.rs:59-65), ρ = 101325·28.97/(8314.46261815324·T_K)
+HB_HD double zone_inv_c(const ZoneC& z, double tz) {
     const double tk = tz + 273.15;
-    // 1/c with c = V·ρ(T)·cp(T) (zone.rs:59-65), ρ = 101325·28.97/(8314.46261815324·T_K)
-    const double inv_cc = (8314.46261815324 * tk) * fast_rcp(z.vol * (101325. * 28.97) * (1002.7370 + 1.2324e-2 * tk));
-#pragma unroll 1
-    for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
-        if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
-        if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
-    }
+    return (8314.46261815324 * tk) * fast_rcp(z.vol * (101325. * 28.97) * (1002.7370 + 1.2324e-2 * tk));
+}
+// model.rs:650-674: T' = a/b + (T − a/b)·exp(−b·dt/c) when |b| > 1e-9
+HB_HD double zone_advance(double tz, double dt, double inv_cc, double a, double b) {
     double tn = tz;
     if (fabs(b) > 1e-9) {
         const double ab = a * fast_rcp(b);   // b > 0: sums of h·A and ρ·V̇·cp
         tn = ab + (tz - ab) * exp(-b * dt * inv_cc);
     }
     return tn;
+}
+// pub_* are the per-wall contributions of the tile, zf/zb the walls' zone indices.
+HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const double* pub_hA_f, const double* pub_hAT_f,
+                         const double* pub_hA_b, const double* pub_hAT_b, const int32_t* zf, const int32_t* zb) {
+    double a, b;
+    zone_sources(z, a, b);
+    const double inv_cc = zone_inv_c(z, tz);
+#pragma unroll 1
+    for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
+        if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
+        if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
+    }
+    return zone_advance(tz, dt, inv_cc, a, b);
 }
 
 // ------------------------------------------------------------------------------------------------------------
