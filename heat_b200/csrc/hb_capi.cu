@@ -158,23 +158,31 @@ void build_device(hb_handle* h) {
     h->host_site.assign(B.n_dev_surfaces, 0);
 
     // launch groups: (lanes per wall, kernel variant); inside a group the heaviest tiles are scheduled first
-    std::map<std::tuple<int, int, int>, std::vector<int32_t>> by;
+    // A tile's run time is proportional to its sub-step count S (2 … 118), and a series is only as short as its
+    // longest tile: tiles are binned by S and the bins with the most sub-steps are launched first, on streams of
+    // higher priority, so that across ALL groups the long tiles start at once and the short ones fill in behind.
+    auto s_class = [](int S) { return S >= 96 ? 0 : S >= 56 ? 1 : S >= 32 ? 2 : S >= 16 ? 3 : 4; };
+    std::map<std::tuple<int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
         const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_END) ? 3 : 0;
-        by[{-t.G, var, t.W}].push_back((int32_t)ti);   // largest walls first
+        // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
+        by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.G, var, t.W}].push_back((int32_t)ti);
     }
+    int prio_lo = 0, prio_hi = 0;   // numerically lower = higher priority
+    HB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     HB_CUDA(cudaEventCreateWithFlags(&h->fork, cudaEventDisableTiming));
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
-        grp->G = -std::get<0>(kv.first);
-        grp->var = std::get<1>(kv.first);
-        grp->W = std::get<2>(kv.first);
+        const int cls = std::get<0>(kv.first);
+        grp->G = -std::get<2>(kv.first);
+        grp->var = std::get<3>(kv.first);
+        grp->W = std::get<4>(kv.first);
         std::stable_sort(kv.second.begin(), kv.second.end(),
                          [&](int32_t a, int32_t b) { return B.tiles[a].S > B.tiles[b].S; });
         grp->n_tiles = (int)kv.second.size();
         grp->ids.upload(kv.second, st);
-        HB_CUDA(cudaStreamCreateWithFlags(&grp->stream, cudaStreamNonBlocking));
+        HB_CUDA(cudaStreamCreateWithPriority(&grp->stream, cudaStreamNonBlocking, std::max(prio_hi, std::min(prio_lo, prio_hi + cls))));
         HB_CUDA(cudaEventCreateWithFlags(&grp->done, cudaEventDisableTiming));
         h->groups.push_back(std::move(grp));
     }
