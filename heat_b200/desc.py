@@ -110,6 +110,14 @@ class BatchDesc:
     def n_constructions(self) -> int:
         return len(self.construction_offset) - 1
 
+    def slice_models(self, m0: int, m1: int) -> "BatchDesc":
+        """Models [m0, m1) as their own batch (a rank's shard); the constructions pool is shared, not copied."""
+        z0, z1 = int(self.model_zone_offset[m0]), int(self.model_zone_offset[m1])
+        s0, s1 = int(self.model_surface_offset[m0]), int(self.model_surface_offset[m1])
+        return BatchDesc(self.layers, self.construction_offset, self.model_zone_offset[m0:m1 + 1] - z0,
+                         self.model_surface_offset[m0:m1 + 1] - s0, self.zone_volume[z0:z1], self.surfaces[s0:s1],
+                         self.steps_per_hour, None if self.model_terrain is None else self.model_terrain[m0:m1])
+
     def model(self, m: int) -> "BatchDesc":
         """The single-model batch holding model `m` (constructions pool shared)."""
         z0, z1 = self.model_zone_offset[m], self.model_zone_offset[m + 1]
