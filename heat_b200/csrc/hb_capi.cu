@@ -222,13 +222,15 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             HB_CUDA(cudaEventRecord(t0, g.stream));
         }
         cudaError_t e;
+        // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
+        const int var = g.var == 0 && !P.single_site ? 3 : g.var;
         switch (g.G) {
-            case 1: e = hb::launch_march_1(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 2: e = hb::launch_march_2(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 4: e = hb::launch_march_4(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 8: e = hb::launch_march_8(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 16: e = hb::launch_march_16(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            default: e = hb::launch_march_32(g.var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 1: e = hb::launch_march_1(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 2: e = hb::launch_march_2(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 4: e = hb::launch_march_4(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 8: e = hb::launch_march_8(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 16: e = hb::launch_march_16(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            default: e = hb::launch_march_32(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
         }
         HB_CUDA(e);
         h->launches += 1;

@@ -359,6 +359,15 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             }
         }
         if (M.variant == TILE_EXT && ends_only) M.variant = TILE_END;
+        // the lean face kernel leaves out film-coefficient overrides and AmbientTemperature back faces: such models
+        // take the general face kernel (the TILE_END one, which handles massive ends as well)
+        if (M.variant == 0)
+            for (int k = 0; k < M.n_surfaces; ++k) {
+                const hb_surface& s = B.surfaces[M.surface_begin + k];
+                if (s.back_kind == HB_BOUNDARY_AMBIENT || s.front_hs_override == s.front_hs_override ||
+                    s.back_hs_override == s.back_hs_override)
+                    M.variant = TILE_END;
+            }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)
             fail("model larger than one tile (" + std::to_string(Wmax) + " surfaces / zones at this wall size)");

@@ -21,13 +21,15 @@ constexpr int kMaxWalls = 32;        // walls (and zones) per tile; == warp size
 constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
 constexpr int kMaxSubsteps = 128;    // shared weather table rows (S <= 120 for n >= 1 step/hour)
 
-// Largest tile of a tier (256 threads) and smallest one (64 threads: the two face warps of hb_face_kernel).  Small
-// tiles shorten the node phase of a sub-step and put more independent scalar chains on an SM; a model needs all its
-// surfaces and zones in one tile, so tiles grow in powers of two up to walls_of_group(G) when a model asks for it.
+// Tile widths.  walls_of_group: the largest tile of a tier (256 node lanes) and the width of the shared-memory-mirror
+// kernel (hb_march_kernel).  pref_walls_of_group: what hb_face_kernel tiles use unless a model needs more slots —
+// at most 128 node lanes (one warp per SM sub-partition: the shortest node phase) and at most 16 walls, so that the
+// front and back faces of all walls fit in ONE warp (dense FP64 issue of the scalar chain).  A model needs all its
+// surfaces and zones in one tile: tiles grow in powers of two up to walls_of_group(G) when a model asks for it.
 inline constexpr int walls_of_group(int G) { return G <= 8 ? 32 : G == 16 ? 16 : 8; }
-inline constexpr int min_walls_of_group(int G) { return G >= 64 ? 1 : (64 / G > 32 ? 32 : 64 / G); }
+inline constexpr int pref_walls_of_group(int G) { return G == 1 ? 32 : G <= 8 ? 16 : 128 / G; }
 inline int walls_for_model(int G, int n_surfaces, int n_zones) {
-    int W = min_walls_of_group(G);
+    int W = pref_walls_of_group(G);
     while (W < walls_of_group(G) && (W < n_surfaces || W < n_zones)) W *= 2;
     return W;
 }

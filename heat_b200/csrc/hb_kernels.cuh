@@ -367,7 +367,11 @@ __device__ unsigned long long hb_phase_clk[8];   // wait B1, node, wait B2, post
 __device__ __forceinline__ void pair_sync() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
 __device__ __forceinline__ void pair_arrive() { asm volatile("bar.arrive 1, 64;" ::: "memory"); }
 
-__host__ __device__ constexpr int face_threads(int G, int W) { return G * W >= 64 ? G * W : 64; }
+// Threads of a face-kernel block: the node lanes, but at least the warps the face role needs (one warp when both
+// faces of every wall fit in it, 2·W <= 32; else one warp per side).
+__host__ __device__ constexpr int face_threads(int G, int W) {
+    return G * W >= (2 * W <= 32 ? 32 : 64) ? G * W : (2 * W <= 32 ? 32 : 64);
+}
 
 // One sub-step of RK4 for a lane's kNL slots (see sweep_first/sweep_next in hb_math.cuh for the algebra), with the
 // edge slots first: their results are what the neighbouring lanes need for the next sweep.
@@ -435,7 +439,8 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     constexpr int TPB = face_threads(G, W);     // a tile of 32 node lanes gets a second warp for the back faces
     constexpr int NL = kNL;
     constexpr int NWARP = TPB / 32;
-    static_assert(NT >= 32 && NT % 32 == 0 && W <= 32 && NWARP >= 2, "tile shape");
+    constexpr bool ONE = 2 * W <= 32;           // front faces on lanes [0, W), back faces on lanes [W, 2W) of ONE warp
+    static_assert(NT >= 32 && NT % 32 == 0 && W <= 32 && (ONE || NWARP >= 2), "tile shape");
     const Tile tile = V.tiles[tile_ids[blockIdx.x]];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t NS = V.n_dev_surfaces;
@@ -497,18 +502,21 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
 
     // ---- face role ----
     const int wf = (int)(blockIdx.x % NWARP);     // warp of the front faces
-    const int wb = (wf + 1) % NWARP;              // warp of the back faces and of the zones
+    const int wb = ONE ? wf : (wf + 1) % NWARP;   // warp of the back faces and of the zones
     const bool face_warp = warp == wf || warp == wb;
-    const bool back = warp == wb;
+    const bool back = ONE ? lane >= W : warp == wb;
     const int kf = back ? 1 : 0;
-    const int64_t sg = (int64_t)tile.surface_begin + (lane < W ? lane : 0);   // lane j ↔ wall j
-    const bool fwall = face_warp && lane < W && V.n_nodes[sg] > 0;
-    const bool szone = back && lane < tile.n_zones;
-    const int64_t sgz = (int64_t)tile.zone_begin + lane;
-    const FaceC& c = s_fc[kf][lane < W ? lane : 0];
+    const int j = ONE ? (lane & (W - 1)) : lane;  // the face lane's wall (and, for back lanes, zone) in the tile
+    const bool face_lane = face_warp && (ONE ? lane < 2 * W : lane < W);
+    const int64_t sg = (int64_t)tile.surface_begin + j;
+    const bool fwall = face_lane && V.n_nodes[sg] > 0;
+    const bool szone = face_lane && back && j < tile.n_zones;
+    const int64_t sgz = (int64_t)tile.zone_begin + j;
+    const FaceC& c = s_fc[kf][j];
     FaceS w{};
     double zT = 0.;        // this lane's zone temperature
     double za0 = 0., zb0 = 0.;   // a, b of the zone's non-surface sources (constant over a series)
+    double zvol = 1.;            // the zone's volume (simple tiles: register copy)
     bool any_front_zone = false, simple_ok = true;
     {
         ZoneC zc{};
@@ -517,35 +525,39 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
             zc.vent_v = V.zvent_v[sgz]; zc.vent_t = V.zvent_t[sgz]; zc.sb = V.z_surf_begin[sgz];
             zc.se = V.z_surf_end[sgz];
             zT = V.zoneT[sgz];
-            s_zT[lane] = zT;
-            simple_ok = zc.sb == lane && zc.se == lane + 1;
+            s_zT[j] = zT;
+            simple_ok = zc.sb == j && zc.se == j + 1;
             zone_sources(zc, za0, zb0);
+            zvol = zc.vol;
         }
-        if (back && lane < W) s_zc[lane] = zc;
+        if (face_lane && back) s_zc[j] = zc;
     }
     if (fwall) {
         WallC wc;
         load_wallc(V, sg, P.single_site != 0, wc);
         const int flg = V.flags[sg];
         const bool nm = END && ((flg >> (back ? 11 : 10)) & 1);
-        load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][lane]);
+        load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][j]);
         w.h = V.sc[(0 + kf) * NS + sg]; w.flow = V.sc[(2 + kf) * NS + sg];
         w.sol = V.sc[(4 + kf) * NS + sg]; w.ir = V.sc[(6 + kf) * NS + sg];
         if (back) {
-            s_zf[lane] = wc.zf;
-            s_zb[lane] = wc.zb;
-            simple_ok = simple_ok && wc.zb == lane && szone;
+            s_zf[j] = wc.zf;
+            s_zb[j] = wc.zb;
+            simple_ok = simple_ok && wc.zb == j && szone;
         }
         any_front_zone = wc.zf >= 0;
-    } else if (back && lane < W) {
-        s_zf[lane] = -1;
-        s_zb[lane] = -1;
-        simple_ok = simple_ok && !szone;
+    } else if (face_lane) {
+        s_fc[kf][j] = FaceC{};   // the lean face path runs unpredicated: lanes without a wall work on zeros
+        if (back) {
+            s_zf[j] = -1;
+            s_zb[j] = -1;
+            simple_ok = simple_ok && !szone;
+        }
     }
     // the front warp has to wait for the zone update only if one of its faces looks at a zone
     const bool front_waits = __syncthreads_or(any_front_zone ? 1 : 0) != 0;
     const bool simple = __syncthreads_and(simple_ok ? 1 : 0) != 0 && !front_waits;
-    if (fwall) w.ts = s_end[back ? 3 : 0][lane];
+    if (fwall) w.ts = s_end[back ? 3 : 0][j];
     const double ir_state = w.ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
 
     // sub-step weather of main step `step` into buffer step & 1 (all threads of the block)
@@ -593,6 +605,28 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     };
     // border conditions of sub-step s of main step `step` → links for the node lanes
     auto pre = [&](int step, int s) {
+        if constexpr (!END) {
+            // lean: single-site weather table, no film override, no AmbientTemperature back face, massive ends —
+            // straight-line and branch-free (face_pre's arithmetic in face_pre's order)
+            const SubWeather sw = s_w[step & 1][s];
+            const int fl = c.fl;
+            const bool is_out = fl & FC_OUT;
+            const bool leeward =
+                (fl & FC_TILTED) && !(add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0);
+            w.forced = c.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
+            const double zone_t = simple ? zT : (c.zone >= 0 ? s_zT[c.zone] : 0.);
+            w.air = is_out ? sw.t_out : (fl & FC_SPACE) ? zone_t : c.amb;
+            const double trad = is_out ? w.trad_out : w.air;
+            const double hn = tarp_lean(w.air - w.ts, c.kpos, c.kneg);
+            const double h = is_out ? hn + w.forced : hn;
+            if (h != h) w.status |= ST_NAN_H;
+            const double xr = 273.15 + (trad + w.ts) / 2.;
+            const double rad = c.eps4s * ((xr * xr) * xr);
+            const double hs = h > 1e-12 ? h : 1e-12;
+            s_link[back ? 2 : 0][j] = w.air + (rad * (trad - w.ts) + c.alpha_end * w.solar) * rcp_lean(hs);
+            s_link[back ? 3 : 1][j] = hs * c.v_end;
+            return;
+        }
         SubWeather sw;
         if (P.single_site) {
             sw = s_w[step & 1][s];
@@ -617,15 +651,15 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
         double t_front = 0., ts_front = 0., t_nb = 0.;
         if (c.fl & FC_BACK_AMB) {
             t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out : (c.fl & FC_FRONT_SPACE) ? s_zT[c.zone_front] : c.amb_front;
-            ts_front = s_end[0][lane];
+            ts_front = s_end[0][j];
         }
         if constexpr (END)
-            if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][lane];
+            if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][j];
         double ghost, link;
         face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, link);
-        s_link[back ? 2 : 0][lane] = ghost;
-        s_link[back ? 3 : 1][lane] = link;
-        if constexpr (END) s_link[back ? 5 : 4][lane] = w.ts;
+        s_link[back ? 2 : 0][j] = ghost;
+        s_link[back ? 3 : 1][j] = link;
+        if constexpr (END) s_link[back ? 5 : 4][j] = w.ts;
     };
 
     fill_weather(0);
@@ -673,15 +707,35 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
             // ================= face role: post(s) → zones → pre(s+1) =================
             if (face_warp) {   // warp-uniform
                 double hA = 0., hAT = 0.;
-                if (fwall) {
-                    const double ts = s_end[back ? 3 : 0][lane];
-                    const double ts_front = (c.fl & FC_BACK_AMB) ? s_end[0][lane] : 0.;
+                if constexpr (!END) {
+                    if (face_lane) {   // face_post's arithmetic, unpredicated
+                        const double ts = s_end[back ? 3 : 0][j];
+                        const double hn = tarp_lean(w.air - ts, c.kpos, c.kneg);
+                        const double h = (c.fl & FC_OUT) ? hn + w.forced : hn;
+                        if (h != h) w.status |= ST_NAN_H;
+                        w.ts = ts;
+                        w.h = h;
+                        w.flow = (ts - w.air) * h;
+                        w.e += w.flow * c.area * dt;
+                        hA = h * c.area;
+                        hAT = hA * ts;
+                    }
+                } else if (fwall) {
+                    const double ts = s_end[back ? 3 : 0][j];
+                    const double ts_front = (c.fl & FC_BACK_AMB) ? s_end[0][j] : 0.;
                     face_post(c, w, ts, ts_front, dt, hA, hAT);
                 }
                 HB_CLK(3)
                 if (simple) {
-                    if (szone) {   // the lane's own wall is the zone's only surface (back face)
-                        const double inv_cc = zone_inv_c(s_zc[lane], zT);
+                    if constexpr (!END) {   // the lane's own wall is the zone's only surface (back face)
+                        const double inv_cc = zone_inv_c_t<true>(zvol, zT);
+                        const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT, zb0 + hA);
+                        if (szone) {
+                            if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
+                            zT = tn;
+                        }
+                    } else if (szone) {
+                        const double inv_cc = zone_inv_c(s_zc[j], zT);
                         const double a = za0 + hAT, b = zb0 + hA;
                         const double tn = zone_advance(zT, dt, inv_cc, a, b);
                         if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
@@ -689,21 +743,29 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
                     }
                 } else {
                     if (fwall) {
-                        s_pub[back ? 2 : 0][lane] = hA;
-                        s_pub[back ? 3 : 1][lane] = hAT;
+                        s_pub[back ? 2 : 0][j] = hA;
+                        s_pub[back ? 3 : 1][j] = hAT;
                     }
-                    if (back || front_waits) pair_sync(); else pair_arrive();
+                    if constexpr (ONE) {
+                        __syncwarp();
+                    } else {
+                        if (back || front_waits) pair_sync(); else pair_arrive();
+                    }
                     if (szone) {
-                        const double tn = zone_update(s_zc[lane], lane, s_zT[lane], dt, s_pub[0], s_pub[1], s_pub[2],
-                                                      s_pub[3], s_zf, s_zb);
-                        if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[lane].sb], ST_NAN_ZONE);
-                        s_zT[lane] = tn;
+                        const double tn = zone_update_ab<!END>(s_zc[j], j, s_zT[j], dt, za0, zb0, s_pub[0], s_pub[1],
+                                                               s_pub[2], s_pub[3], s_zf, s_zb);
+                        if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[j].sb], ST_NAN_ZONE);
+                        s_zT[j] = tn;
                         zT = tn;
                     }
-                    if (front_waits) pair_sync(); else if (back) __syncwarp();
+                    if constexpr (ONE) {
+                        __syncwarp();
+                    } else {
+                        if (front_waits) pair_sync(); else if (back) __syncwarp();
+                    }
                 }
                 HB_CLK(4)
-                if (fwall && s + 1 < S) pre(step, s + 1);
+                if ((END ? fwall : face_lane) && s + 1 < S) pre(step, s + 1);
                 HB_CLK(5)
             }
         }
@@ -729,7 +791,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     }
 
 #ifdef HB_PHASE_CLOCKS
-    if (back && lane == 0 && S >= 100)
+    if (szone && j == 0 && S >= 100)
         for (int q = 0; q < 8; ++q) atomicAdd(&hb_phase_clk[q], (unsigned long long)clk[q]);
 #endif
     // ---- write the state back ----

@@ -43,11 +43,10 @@ cudaError_t launch_face(int n_tiles, cudaStream_t st, const DevView& V, const Se
 
 template <int G, bool END>
 cudaError_t launch_face_w(int W, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
-    constexpr int W0 = min_walls_of_group(G), W2 = walls_of_group(G);
-    constexpr int W1 = W0 * 2 <= W2 ? W0 * 2 : W2;
+    constexpr int W0 = pref_walls_of_group(G), W1 = walls_of_group(G);
+    static_assert(W1 == W0 || W1 == 2 * W0, "two tile widths per tier");
     if (W == W0) return launch_face<G, W0, END>(n_tiles, st, V, P, ids);
     if (W == W1) return launch_face<G, W1, END>(n_tiles, st, V, P, ids);
-    if (W == W2) return launch_face<G, W2, END>(n_tiles, st, V, P, ids);
     return cudaErrorInvalidValue;
 }
 }  // namespace

@@ -162,6 +162,72 @@ HB_HD double fast_cbrt(double x) {
 #endif
 }
 
+// ---- branch-free variants for the lean face path (hb_face_kernel<.., END = false>) ---------------------------------
+// They trade the last bits of the Newton polish (results stay within ~1e-12 relative, six orders below the parity
+// tolerance of 1e-6 degC on temperatures) for a shorter dependent chain and no slow-path branches.
+#if defined(__CUDACC__)
+// exp(r) on |r| <= ln2/2 as sum r^i / i!, i <= 12 (truncation 4e-16), + range-reduction constants
+static __constant__ double hb_expc[18] = {
+    1.0, 1.0, 1.0 / 2, 1.0 / 6, 1.0 / 24, 1.0 / 120, 1.0 / 720, 1.0 / 5040, 1.0 / 40320, 1.0 / 362880, 1.0 / 3628800,
+    1.0 / 39916800, 1.0 / 479001600, 0.0,
+    1.4426950408889634074,      // [14] log2(e)
+    6755399441055744.0,         // [15] 1.5 * 2^52: round-to-nearest-integer shifter
+    6.93147180369123816490e-01, // [16] ln2 high part (low 32 bits of the mantissa are zero: k*hi is exact)
+    1.90821492927058770002e-10, // [17] ln2 low part
+};
+#endif
+// 1/x, one Newton step on the MUFU seed: relative error ~1e-12.
+HB_HD double rcp_lean(double x) {
+#if defined(__CUDA_ARCH__)
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = fma(-x, r, 1.0);
+    return fma(fma(e, e, e), r, r);   // r(1 + e + e^2): third-order step for the price of one more FMA
+#else
+    return 1.0 / x;
+#endif
+}
+// x^(1/3), x >= 0 (NaN propagates, x < 1e-24 gives 0 as in fast_cbrt): no branch.
+HB_HD double cbrt_lean(double x) {
+#if defined(__CUDA_ARCH__)
+    const float xf = (float)x;
+    float l, yf;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(xf));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(yf) : "f"(l * 0.33333334f));
+    const double y0 = (double)yf;
+    const double y2 = y0 * y0;
+    double w;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(w) : "d"(3.0 * y2));
+    const double y1 = fma(-fma(y2, y0, -x), w, y0);
+    const double y = fma(-fma(y1 * y1, y1, -x), w, y1);
+    return x >= 1e-24 ? y : (x != x ? x : 0.0);
+#else
+    return x >= 1e-24 ? cbrt(x) : (x != x ? x : 0.0);
+#endif
+}
+// exp(x) for any x (clamped to +-700; NaN propagates): Cody-Waite reduction, degree-12 Estrin, exponent add.
+HB_HD double exp_lean(double x) {
+#if defined(__CUDA_ARCH__)
+    const double xc = x < -700. ? -700. : x > 700. ? 700. : x;
+    const double t = fma(xc, hb_expc[14], hb_expc[15]);
+    const double k = t - hb_expc[15];
+    double r = fma(-k, hb_expc[16], xc);
+    r = fma(-k, hb_expc[17], r);
+    const double r2 = r * r, r4 = r2 * r2, r8 = r4 * r4;
+    const double q0 = fma(hb_expc[1], r, hb_expc[0]), q1 = fma(hb_expc[3], r, hb_expc[2]);
+    const double q2 = fma(hb_expc[5], r, hb_expc[4]), q3 = fma(hb_expc[7], r, hb_expc[6]);
+    const double q4 = fma(hb_expc[9], r, hb_expc[8]), q5 = fma(hb_expc[11], r, hb_expc[10]);
+    const double s0 = fma(q1, r2, q0), s1 = fma(q3, r2, q2), s2 = fma(q5, r2, q4);
+    const double lo = fma(s1, r4, s0), hi = fma(hb_expc[12], r4, s2);
+    const double p = fma(hi, r8, lo);
+    const int ki = __double2loint(t);   // k as an integer (low word of the shifted sum)
+    const double res = __hiloint2double(__double2hiint(p) + (ki << 20), __double2loint(p));
+    return x == x ? res : x;
+#else
+    return exp(x);
+#endif
+}
+
 HB_HD void sub_weather(double t_out, double wdir_deg, double wspeed, SubWeather& w) {
     w.t_out = t_out;
     w.sqrt_ws = sqrt(wspeed);
@@ -181,6 +247,14 @@ HB_HD double tarp_natural(double t_air, double t_surf, double kpos, double kneg)
     const double ad = fabs(d);
     const double k = ad < 1e-3 ? 1.31 : d > 0. ? kpos : kneg;
     const double h = k * fast_cbrt(ad);
+    return h < 0.1 ? 0.1 : h;
+}
+
+// the same for d = t_air − t_surf, branch-free (lean face path)
+HB_HD double tarp_lean(double d, double kpos, double kneg) {
+    const double ad = fabs(d);
+    const double k = ad < 1e-3 ? 1.31 : d > 0. ? kpos : kneg;
+    const double h = k * cbrt_lean(ad);
     return h < 0.1 ? 0.1 : h;
 }
 
@@ -524,27 +598,48 @@ HB_HD double zone_inv_c(const ZoneC& z, double tz) {
     const double tk = tz + 273.15;
     return (8314.46261815324 * tk) * fast_rcp(z.vol * (101325. * 28.97) * (1002.7370 + 1.2324e-2 * tk));
 }
-// model.rs:650-674: T' = a/b + (T − a/b)·exp(−b·dt/c) when |b| > 1e-9
+// model.rs:650-674: T' = a/b + (T − a/b)·exp(−b·dt/c) when |b| > 1e-9.  LEAN: branch-free, short-chain arithmetic.
+template <bool LEAN = false>
 HB_HD double zone_advance(double tz, double dt, double inv_cc, double a, double b) {
-    double tn = tz;
-    if (fabs(b) > 1e-9) {
-        const double ab = a * fast_rcp(b);   // b > 0: sums of h·A and ρ·V̇·cp
-        tn = ab + (tz - ab) * exp(-b * dt * inv_cc);
+    if constexpr (LEAN) {
+        const double ab = a * rcp_lean(b);
+        const double tn = ab + (tz - ab) * exp_lean(-b * dt * inv_cc);
+        return fabs(b) > 1e-9 ? tn : tz;
+    } else {
+        double tn = tz;
+        if (fabs(b) > 1e-9) {
+            const double ab = a * fast_rcp(b);   // b > 0: sums of h·A and ρ·V̇·cp
+            tn = ab + (tz - ab) * exp(-b * dt * inv_cc);
+        }
+        return tn;
     }
-    return tn;
 }
-// pub_* are the per-wall contributions of the tile, zf/zb the walls' zone indices.
-HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const double* pub_hA_f, const double* pub_hAT_f,
-                         const double* pub_hA_b, const double* pub_hAT_b, const int32_t* zf, const int32_t* zb) {
-    double a, b;
-    zone_sources(z, a, b);
-    const double inv_cc = zone_inv_c(z, tz);
+template <bool LEAN = false>
+HB_HD double zone_inv_c_t(double vol, double tz) {
+    const double tk = tz + 273.15;
+    const double den = vol * (101325. * 28.97) * (1002.7370 + 1.2324e-2 * tk);
+    return (8314.46261815324 * tk) * (LEAN ? rcp_lean(den) : fast_rcp(den));
+}
+// The zone update with the non-surface sources (a0, b0 of zone_sources) already known.
+template <bool LEAN = false>
+HB_HD double zone_update_ab(const ZoneC& z, int zi, double tz, double dt, double a, double b, const double* pub_hA_f,
+                            const double* pub_hAT_f, const double* pub_hA_b, const double* pub_hAT_b,
+                            const int32_t* zf, const int32_t* zb) {
+    const double inv_cc = zone_inv_c_t<LEAN>(z.vol, tz);
 #pragma unroll 1
     for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
         if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
         if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
     }
-    return zone_advance(tz, dt, inv_cc, a, b);
+    return zone_advance<LEAN>(tz, dt, inv_cc, a, b);
+}
+// pub_* are the per-wall contributions of the tile, zf/zb the walls' zone indices.
+template <bool LEAN = false>
+HB_HD double zone_update(const ZoneC& z, int zi, double tz, double dt, const double* pub_hA_f, const double* pub_hAT_f,
+                         const double* pub_hA_b, const double* pub_hAT_b, const int32_t* zf, const int32_t* zb) {
+    double a, b;
+    zone_sources(z, a, b);
+    return zone_update_ab<LEAN>(z, zi, tz, dt, a, b, pub_hA_f, pub_hAT_f, pub_hA_b, pub_hAT_b, zf, zb);
 }
 
 // ------------------------------------------------------------------------------------------------------------
