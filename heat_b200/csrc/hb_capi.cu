@@ -77,6 +77,7 @@ struct hb_handle {
     struct Group {
         int G, W, var;
         int n_tiles;
+        int s_max = 1;   // most sub-steps of a tile of the group
         DevBuf<int32_t> ids;   // tile ids, heaviest first
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;
@@ -165,7 +166,7 @@ void build_device(hb_handle* h) {
     std::map<std::tuple<int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
-        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_END) ? 3 : 0;
+        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_END) ? 3 : 0;
         // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
         by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.G, var, t.W}].push_back((int32_t)ti);
     }
@@ -181,6 +182,7 @@ void build_device(hb_handle* h) {
         std::stable_sort(kv.second.begin(), kv.second.end(),
                          [&](int32_t a, int32_t b) { return B.tiles[a].S > B.tiles[b].S; });
         grp->n_tiles = (int)kv.second.size();
+        grp->s_max = B.tiles[kv.second.front()].S;
         grp->ids.upload(kv.second, st);
         HB_CUDA(cudaStreamCreateWithPriority(&grp->stream, cudaStreamNonBlocking, std::max(prio_hi, std::min(prio_lo, prio_hi + cls))));
         HB_CUDA(cudaEventCreateWithFlags(&grp->done, cudaEventDisableTiming));
@@ -194,7 +196,7 @@ void build_device(hb_handle* h) {
 namespace hb {
 // one translation unit per lanes-per-wall tier (hb_march_tier.cu compiled with -DHB_TIER=G) so they build in parallel
 #define HB_DECL_TIER(N) \
-    cudaError_t launch_march_##N(int var, int W, int n_tiles, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+    cudaError_t launch_march_##N(int var, int W, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
 HB_DECL_TIER(1) HB_DECL_TIER(2) HB_DECL_TIER(4) HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(32)
 #undef HB_DECL_TIER
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
@@ -223,14 +225,14 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         }
         cudaError_t e;
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
-        const int var = g.var == 0 && !P.single_site ? 3 : g.var;
+        const int var = (g.var == 0 || g.var == 3) && !P.single_site ? 4 : g.var;
         switch (g.G) {
-            case 1: e = hb::launch_march_1(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 2: e = hb::launch_march_2(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 4: e = hb::launch_march_4(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 8: e = hb::launch_march_8(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            case 16: e = hb::launch_march_16(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
-            default: e = hb::launch_march_32(var, g.W, g.n_tiles, g.stream, V, P, g.ids.p); break;
+            case 1: e = hb::launch_march_1(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 2: e = hb::launch_march_2(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 4: e = hb::launch_march_4(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 8: e = hb::launch_march_8(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 16: e = hb::launch_march_16(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            default: e = hb::launch_march_32(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
         }
         HB_CUDA(e);
         h->launches += 1;

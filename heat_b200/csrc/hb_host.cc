@@ -264,7 +264,7 @@ void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int
     P.wind_speed_modifier = wind_modifier(s.centroid_z, terrain);
 }
 
-constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END;   // tiles are uniform in these
+constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN;   // tiles are uniform in these
 
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
@@ -359,14 +359,14 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             }
         }
         if (M.variant == TILE_EXT && ends_only) M.variant = TILE_END;
-        // the lean face kernel leaves out film-coefficient overrides and AmbientTemperature back faces: such models
-        // take the general face kernel (the TILE_END one, which handles massive ends as well)
-        if (M.variant == 0)
+        // the lean face kernels leave out film-coefficient overrides and AmbientTemperature back faces: such models
+        // take the general face kernel (which handles massive and no-mass ends alike)
+        if (M.variant == 0 || M.variant == TILE_END)
             for (int k = 0; k < M.n_surfaces; ++k) {
                 const hb_surface& s = B.surfaces[M.surface_begin + k];
                 if (s.back_kind == HB_BOUNDARY_AMBIENT || s.front_hs_override == s.front_hs_override ||
                     s.back_hs_override == s.back_hs_override)
-                    M.variant = TILE_END;
+                    M.variant = TILE_END | TILE_GEN;
             }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)

@@ -25,7 +25,9 @@
 
 namespace hb {
 
-constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3;
+constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4;
+// hb_face_kernel modes: lean (all ends massive), lean with no-mass end nodes, general
+constexpr int kFaceLean = 0, kFaceLeanEnd = 1, kFaceGen = 2;
 
 template <int G, int W, int VAR>
 __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
@@ -432,9 +434,12 @@ __device__ __forceinline__ void node_rk4(double (&T)[NL], const double (&A)[NL],
     }
 }
 
-template <int G, int W, bool END>
+template <int G, int W, int MODE>
 __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     hb_face_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+    constexpr bool END = MODE != kFaceLean;    // single-node no-mass chunks at the ends of walls are possible
+    constexpr bool LEAN = MODE != kFaceGen;    // one weather table per tile, no film override, no AmbientTemperature back
+    extern __shared__ double s_dyn[];
     constexpr int NT = G * W;                   // node lanes (the tile's slab stride)
     constexpr int TPB = face_threads(G, W);     // a tile of 32 node lanes gets a second warp for the back faces
     constexpr int NL = kNL;
@@ -451,7 +456,8 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     __shared__ int32_t s_zf[W], s_zb[W];
     __shared__ double s_end[4][W];      // node 0, node 1, node n-2, node n-1
     __shared__ double s_link[6][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
-    __shared__ SubWeather s_w[2][kMaxSubsteps];
+    // sub-step weather of two consecutive main steps, [2][S] (dynamic: 2·S_max(group) rows, launch_face)
+    SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn);
     __shared__ FaceC s_fc[2][W];        // per-face constants: read from shared memory where they are used
 
     const int S = tile.S;
@@ -577,7 +583,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
             } else {
                 t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
             }
-            sub_weather(t_out, wdir, wspeed, s_w[step & 1][s]);
+            sub_weather(t_out, wdir, wspeed, s_w[(step & 1) * S + s]);
         }
     };
     // what the caller writes into SimulationState before a main step + the per-step derived quantities
@@ -605,10 +611,10 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
     };
     // border conditions of sub-step s of main step `step` → links for the node lanes
     auto pre = [&](int step, int s) {
-        if constexpr (!END) {
+        if constexpr (LEAN) {
             // lean: single-site weather table, no film override, no AmbientTemperature back face, massive ends —
             // straight-line and branch-free (face_pre's arithmetic in face_pre's order)
-            const SubWeather sw = s_w[step & 1][s];
+            const SubWeather sw = s_w[(step & 1) * S + s];
             const int fl = c.fl;
             const bool is_out = fl & FC_OUT;
             const bool leeward =
@@ -622,6 +628,12 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
             if (h != h) w.status |= ST_NAN_H;
             const double xr = 273.15 + (trad + w.ts) / 2.;
             const double rad = c.eps4s * ((xr * xr) * xr);
+            if constexpr (END) {
+                if (fl & FC_NM)
+                    w.ts = solve_end_node<true>(w.air, h, rad, trad, c.u_nb, s_end[back ? 2 : 1][j],
+                                                c.alpha_end * w.solar, w.ts, w.nm_iters, w.status);
+                s_link[back ? 5 : 4][j] = w.ts;
+            }
             const double hs = h > 1e-12 ? h : 1e-12;
             s_link[back ? 2 : 0][j] = w.air + (rad * (trad - w.ts) + c.alpha_end * w.solar) * rcp_lean(hs);
             s_link[back ? 3 : 1][j] = hs * c.v_end;
@@ -629,7 +641,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
         }
         SubWeather sw;
         if (P.single_site) {
-            sw = s_w[step & 1][s];
+            sw = s_w[(step & 1) * S + s];
         } else {
             const double* wtab = P.weather + (int64_t)c.site * P.weather_rows * 3;
             const double* w0 = wtab + (int64_t)step * 3;
@@ -707,7 +719,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
             // ================= face role: post(s) → zones → pre(s+1) =================
             if (face_warp) {   // warp-uniform
                 double hA = 0., hAT = 0.;
-                if constexpr (!END) {
+                if constexpr (LEAN) {
                     if (face_lane) {   // face_post's arithmetic, unpredicated
                         const double ts = s_end[back ? 3 : 0][j];
                         const double hn = tarp_lean(w.air - ts, c.kpos, c.kneg);
@@ -727,7 +739,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
                 }
                 HB_CLK(3)
                 if (simple) {
-                    if constexpr (!END) {   // the lane's own wall is the zone's only surface (back face)
+                    if constexpr (LEAN) {   // the lane's own wall is the zone's only surface (back face)
                         const double inv_cc = zone_inv_c_t<true>(zvol, zT);
                         const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT, zb0 + hA);
                         if (szone) {
@@ -752,7 +764,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
                         if (back || front_waits) pair_sync(); else pair_arrive();
                     }
                     if (szone) {
-                        const double tn = zone_update_ab<!END>(s_zc[j], j, s_zT[j], dt, za0, zb0, s_pub[0], s_pub[1],
+                        const double tn = zone_update_ab<LEAN>(s_zc[j], j, s_zT[j], dt, za0, zb0, s_pub[0], s_pub[1],
                                                                s_pub[2], s_pub[3], s_zf, s_zb);
                         if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + s_zc[j].sb], ST_NAN_ZONE);
                         s_zT[j] = tn;
@@ -765,7 +777,7 @@ __global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
                     }
                 }
                 HB_CLK(4)
-                if ((END ? fwall : face_lane) && s + 1 < S) pre(step, s + 1);
+                if ((LEAN ? face_lane : fwall) && s + 1 < S) pre(step, s + 1);
                 HB_CLK(5)
             }
         }

@@ -727,10 +727,11 @@ HB_HD double face_h(const FaceC& c, const FaceS& w, double ts_env, int& status) 
 }
 // One no-mass end node (chunk (0,1) or (n-1,n)): damped fixed point of surface.rs:790-898 on a 1x1 system.
 //   K = -(h + u),  q = air·h + rad·(trad - T) + u·T_neighbour (+ absorbed solar)
+template <bool LEAN = false>
 HB_HD double solve_end_node(double air, double h, double rad, double trad, double u, double t_nb, double sol, double t,
                             unsigned long long& iters, int& status) {
     const double dd = -h - u;
-    const double r = 1.0 / dd;
+    const double r = LEAN ? -fast_rcp(-dd) : 1.0 / dd;
     const double qn = u * t_nb;
     double old_err = 99999.;
     int count = 0;
