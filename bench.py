@@ -117,6 +117,20 @@ def cpu_reference_rate(desc, weather, inputs, n_models: int, hours: int, threads
     return updates / dt, updates, dt
 
 
+CPU_SAMPLE_SECONDS = 20.0   # CPU work per bounded sample of the workload
+
+
+def cpu_sample_size(desc, weather, inputs, hours: int, threads: int):
+    """Number of leading models of the workload (x `h` hourly steps) that keep all host threads busy for about
+    CPU_SAMPLE_SECONDS: a pilot of 2 models per thread sets the scale."""
+    h = min(hours, 2190)
+    n0 = min(desc.n_models, 2 * threads)
+    _, _, dt0 = cpu_reference_rate(desc, weather, inputs, n0, h, threads)
+    n = int(n0 * CPU_SAMPLE_SECONDS / max(dt0, 1e-3))
+    n = max(n0, min(desc.n_models, (n // threads) * threads or threads))
+    return n, h
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -134,8 +148,7 @@ def main():
         if rank != 0:
             return
         desc, gains, wname = make_workload(a.workload, a.units, 0)
-        n_sample = min(desc.n_models, 2 * cores)
-        h_sample = min(hours, 2190)
+        n_sample, h_sample = cpu_sample_size(desc, weather, inputs, hours, cores)
         vals = []
         for it in range(a.warmup + a.steps):
             rate, updates, dt = cpu_reference_rate(desc, weather, inputs, n_sample, h_sample, cores)
@@ -216,33 +229,15 @@ def main():
     h2d = weather.nbytes + inputs.nbytes
     d2h = final.nbytes + 12 * 8
 
-    t_step = float(np.mean(ms)) * 1e-3
-    t_e2e = float(np.mean(e2e_s))
-    reduced = None
-    if dist is not None:
-        import torch
-        tt = torch.tensor([t_step, t_e2e], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_step, t_e2e = float(tt[0]), float(tt[1])
-        up = torch.tensor([float(updates_per_step)], device="cuda", dtype=torch.float64)
-        dist.all_reduce(up, op=dist.ReduceOp.SUM)
-        total_updates = float(up[0])
-        # final ensemble energy / temperature reductions over NVLink (the path's only collective)
-        sums = torch.tensor([stats.sum_zone_t, stats.sum_node_t, stats.front_conv_energy_j, stats.back_conv_energy_j,
-                             float(stats.n_zones), float(stats.n_nodes)], device="cuda", dtype=torch.float64)
-        mins = torch.tensor([stats.min_zone_t, stats.min_node_t], device="cuda", dtype=torch.float64)
-        maxs = torch.tensor([stats.max_zone_t, stats.max_node_t], device="cuda", dtype=torch.float64)
-        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-        dist.all_reduce(mins, op=dist.ReduceOp.MIN)
-        dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
-        reduced = {"mean_zone_t": float(sums[0] / sums[4]), "mean_node_t": float(sums[1] / sums[5]),
-                   "front_conv_energy_j": float(sums[2]), "back_conv_energy_j": float(sums[3]),
-                   "min_node_t": float(mins[1]), "max_node_t": float(maxs[1])}
-    else:
-        total_updates = float(updates_per_step)
-        reduced = {"mean_zone_t": stats.sum_zone_t / stats.n_zones, "mean_node_t": stats.sum_node_t / stats.n_nodes,
-                   "front_conv_energy_j": stats.front_conv_energy_j, "back_conv_energy_j": stats.back_conv_energy_j,
-                   "min_node_t": stats.min_node_t, "max_node_t": stats.max_node_t}
+    from heat_b200.dist import EnsembleStats, combine_stats, max_over_ranks, sum_over_ranks
+    dev = "cuda" if dist is not None else None
+    # slowest rank's time; units of all ranks; the path's only collective: the final ensemble statistics (NCCL)
+    t_step, t_e2e = max_over_ranks([float(np.mean(ms)) * 1e-3, float(np.mean(e2e_s))], dev)
+    total_updates = sum_over_ranks([float(updates_per_step)], dev)[0]
+    es = combine_stats(EnsembleStats.from_c(stats), dev)
+    reduced = {"mean_zone_t": es.mean_zone_t, "mean_node_t": es.mean_node_t,
+               "front_conv_energy_j": es.front_conv_energy_j, "back_conv_energy_j": es.back_conv_energy_j,
+               "min_node_t": es.min_node_t, "max_node_t": es.max_node_t, "status_flags": es.status_flags}
 
     if rank == 0:
         peaks = {}
@@ -274,8 +269,7 @@ def main():
             "gpu_launches": int(gpu_launches), "clocks": clocks,
         }
         if world == 1 and not a.no_cpu_baseline:
-            n_sample = min(desc.n_models, 2 * cores)
-            h_sample = min(hours, 2190)
+            n_sample, h_sample = cpu_sample_size(desc, weather, inputs, hours, cores)
             rate, upd, dt = cpu_reference_rate(desc, weather, inputs, n_sample, h_sample, cores)
             out["cpu_baseline"] = {"value": rate, "unit": "updates/s", "cores": cores, "kind": "port",
                                    "sample": f"first {n_sample} models x {h_sample} hourly steps, {dt:.1f} s"}

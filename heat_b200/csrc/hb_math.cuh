@@ -731,10 +731,31 @@ template <bool LEAN = false>
 HB_HD double solve_end_node(double air, double h, double rad, double trad, double u, double t_nb, double sol, double t,
                             unsigned long long& iters, int& status) {
     const double dd = -h - u;
-    const double r = LEAN ? -fast_rcp(-dd) : 1.0 / dd;
     const double qn = u * t_nb;
     double old_err = 99999.;
     int count = 0;
+    if constexpr (LEAN) {
+        // the update x(t) = K⁻¹(−q(t)) is affine in t: x = alpha + beta·t.  Same iteration and the same stopping
+        // rules, on a chain of three dependent operations per pass.
+        const double r = -fast_rcp(h + u);
+        const double beta = rad * r;
+        const double alpha = -((((air * h + rad * trad) + qn) + sol) * r);
+        while (true) {
+            ++iters;
+            const double x = fma(beta, t, alpha);
+            const double err = fabs(x - t);
+            if (err > old_err) break;
+            if (err != err) { status |= ST_NAN_ERR; break; }
+            t = (t + x) * 0.5;
+            const double tol = count < 100 ? 0.01 : 0.5;
+            if (err < tol) break;
+            old_err = err;
+            ++count;
+            if (count > 100000) { status |= ST_ITER_CAP; break; }
+        }
+        return t;
+    }
+    const double r = 1.0 / dd;
     while (true) {
         ++iters;
         const double rhs = -(((air * h + rad * (trad - t)) + qn) + sol);
