@@ -434,8 +434,11 @@ __device__ __forceinline__ void node_rk4(double (&T)[NL], const double (&A)[NL],
     }
 }
 
+#ifndef HB_FACE_OCC
+#define HB_FACE_OCC 512   // resident threads per SM the face kernel is compiled for (512: 128 registers per thread)
+#endif
 template <int G, int W, int MODE>
-__global__ void __launch_bounds__(face_threads(G, W), 512 / face_threads(G, W))
+__global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads(G, W))
     hb_face_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     constexpr bool END = MODE != kFaceLean;    // single-node no-mass chunks at the ends of walls are possible
     constexpr bool LEAN = MODE != kFaceGen;    // one weather table per tile, no film override, no AmbientTemperature back
