@@ -264,7 +264,12 @@ void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int
     P.wind_speed_modifier = wind_modifier(s.centroid_z, terrain);
 }
 
-constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN;   // tiles are uniform in these
+// Single pane: two nodes, both without mass, one chunk (0, 2), no cavity.
+inline bool is_pane(const SurfacePlan& P) {
+    return P.n_nodes == 2 && P.cavities.empty() && P.nomass_chunks.size() == 2 && P.nomass_chunks[0] == 0 &&
+           P.nomass_chunks[1] == 2;
+}
+constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE;   // tiles are uniform in these
 
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
@@ -347,26 +352,45 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         ModelPlan& M = B.models[m];
         if (M.nmax > kMaxNodes) fail("surface has more nodes than the supported maximum (254)");
         M.variant = 0;
-        bool ends_only = true;   // every no-mass chunk is one node at an end of a wall of >= 3 nodes
+        // `rest`: variant of the model without its single panes; a model whose other walls suit the face kernel keeps
+        // its panes there too (both faces of a wall in one warp: tiles of at most 16 walls, >= 2 lanes per wall)
+        int rest = 0;
+        bool ends_only = true;   // every no-mass chunk is one node at an end of a wall of >= 3 nodes (panes aside)
+        bool panes = false;
         for (int k = 0; k < M.n_surfaces; ++k) {
             const SurfacePlan& P = B.plans[M.surface_begin + k];
-            if (!P.nomass_chunks.empty() || !P.cavities.empty()) M.variant |= TILE_EXT;
-            if (!P.cavities.empty()) M.variant |= TILE_CAV;
-            if (P.distributed_solar) M.variant |= TILE_EXT | TILE_DIST;
+            int v = 0;
+            if (!P.nomass_chunks.empty() || !P.cavities.empty()) v |= TILE_EXT;
+            if (!P.cavities.empty()) v |= TILE_CAV;
+            if (P.distributed_solar) v |= TILE_EXT | TILE_DIST;
+            M.variant |= v;
+            if (is_pane(P)) {
+                panes = true;
+                continue;
+            }
+            rest |= v;
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2) {
                 const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
                 if (fin - ini != 1 || P.n_nodes < 3 || (ini != 0 && fin != P.n_nodes)) ends_only = false;
             }
         }
-        if (M.variant == TILE_EXT && ends_only) M.variant = TILE_END;
+        if (panes && (rest == 0 || rest == TILE_EXT) && ends_only) {
+            const int nmax2 = std::max<int>(M.nmax, kNL - 1);
+            if (walls_for_model(group_of_nodes(nmax2), M.n_surfaces, M.n_zones) <= 16) {
+                M.nmax = nmax2;
+                M.variant = TILE_END | TILE_PANE;
+            }
+        } else if (M.variant == TILE_EXT && ends_only) {
+            M.variant = TILE_END;
+        }
         // the lean face kernels leave out film-coefficient overrides and AmbientTemperature back faces: such models
-        // take the general face kernel (which handles massive and no-mass ends alike)
-        if (M.variant == 0 || M.variant == TILE_END)
+        // take the general face kernel (which handles massive ends, no-mass ends and panes alike)
+        if (M.variant == 0 || (M.variant & TILE_END))
             for (int k = 0; k < M.n_surfaces; ++k) {
                 const hb_surface& s = B.surfaces[M.surface_begin + k];
                 if (s.back_kind == HB_BOUNDARY_AMBIENT || s.front_hs_override == s.front_hs_override ||
                     s.back_hs_override == s.back_hs_override)
-                    M.variant = TILE_END | TILE_GEN;
+                    M.variant |= TILE_END | TILE_GEN;
             }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)
@@ -457,7 +481,7 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
     H.site.assign(NS, 0); H.desc_index.assign(NS, 0); H.nm_off.assign(NS + 1, 0); H.cav_off.assign(NS + 1, 0);
     H.nm_pairs.clear(); H.cav.clear();
     for (auto* v : {&H.area, &H.nx, &H.ny, &H.cos_tilt, &H.forced_c, &H.eps_f, &H.eps_b, &H.amb_f, &H.amb_b, &H.af0,
-                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.energy_f, &H.energy_b})
+                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.ax_f, &H.ax_b, &H.energy_f, &H.energy_b})
         v->assign(NS, 0.);
     H.hs_ov_f.assign(NS, NAN); H.hs_ov_b.assign(NS, NAN);
     H.nodeT.assign(B.node_slab_len, 0.); H.coefA.assign(B.node_slab_len, 0.); H.coefB.assign(B.node_slab_len, 0.);
@@ -485,6 +509,8 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
         if (tile.flags & TILE_END)
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2)
                 H.flags[g] |= P.nomass_chunks[c] == 0 ? (1 << 10) : (1 << 11);
+        const bool pane = (tile.flags & TILE_PANE) && is_pane(P);
+        if (pane) H.flags[g] |= (1 << 10) | (1 << 11) | (1 << 12);
         H.u_f[g] = n > 1 ? P.u[0] : 0.;
         H.u_b[g] = n > 1 ? P.u[n - 2] : 0.;
         const int zone_local0 = M.n_zones ? B.dev_zone_of[M.zone_begin] - tile.zone_begin : 0;
@@ -522,9 +548,13 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
         }
         H.v0[g] = vof(0);
         H.vL[g] = vof(n - 1);
-        if (!P.distributed_solar) {  // distributed: every absorptance goes through the per-node source term
+        if (!P.distributed_solar || pane) {  // distributed: every absorptance goes through the per-node source term
             H.af0[g] = P.front_alpha[0];
             H.abL[g] = P.back_alpha[n - 1];
+        }
+        if (pane) {
+            H.ax_f[g] = P.back_alpha[0];
+            H.ax_b[g] = P.front_alpha[n - 1];
         }
         H.sc[0 * NS + g] = kInitialH;
         H.sc[1 * NS + g] = kInitialH;
@@ -566,7 +596,7 @@ DevView HostArrays::view(const BatchPlan& B) {
     V.site = site.data(); V.desc_index = desc_index.data(); V.area = area.data(); V.nx = nx.data(); V.ny = ny.data();
     V.cos_tilt = cos_tilt.data(); V.forced_c = forced_c.data(); V.eps_f = eps_f.data(); V.eps_b = eps_b.data();
     V.amb_f = amb_f.data(); V.amb_b = amb_b.data(); V.hs_ov_f = hs_ov_f.data(); V.hs_ov_b = hs_ov_b.data();
-    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data();
+    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data(); V.ax_f = ax_f.data(); V.ax_b = ax_b.data();
     V.nm_off = nm_off.data(); V.nm_pairs = nm_pairs.data(); V.cav_off = cav_off.data(); V.cav = cav.data();
     V.nodeT = nodeT.data(); V.coefA = coefA.data(); V.coefB = coefB.data();
     V.ext_u = ext_u.data(); V.ext_mass = ext_mass.data(); V.ext_af = ext_af.data(); V.ext_ab = ext_ab.data();

@@ -90,6 +90,7 @@ enum : int32_t {
     TILE_DIST = 2,   // some wall absorbs solar radiation on inner nodes (transparent layers)
     TILE_CAV = 4,    // some wall has a gas cavity (temperature-dependent link)
     TILE_END = 8,    // the only no-mass chunks are single nodes at the ends of walls (solved by the face lanes)
+    TILE_PANE = 32,  // face-kernel tile with single-pane windows (two no-mass nodes solved jointly by the face lanes)
     TILE_GEN = 16,   // face-kernel tile with a film-coefficient override or an AmbientTemperature back boundary
 };
 

@@ -25,9 +25,10 @@
 
 namespace hb {
 
-constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4;
-// hb_face_kernel modes: lean (all ends massive), lean with no-mass end nodes, general
-constexpr int kFaceLean = 0, kFaceLeanEnd = 1, kFaceGen = 2;
+constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4, kVarPane = 5;
+// hb_face_kernel modes: lean (all ends massive), lean with no-mass end nodes, general (everything), lean with
+// no-mass end nodes and single panes
+constexpr int kFaceLean = 0, kFaceLeanEnd = 1, kFaceGen = 2, kFacePane = 3;
 
 template <int G, int W, int VAR>
 __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
@@ -448,6 +449,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     constexpr int NL = kNL;
     constexpr int NWARP = TPB / 32;
     constexpr bool ONE = 2 * W <= 32;           // front faces on lanes [0, W), back faces on lanes [W, 2W) of ONE warp
+    constexpr bool PANE = ONE && (MODE == kFaceGen || MODE == kFacePane);   // panes: both faces in one warp
     static_assert(NT >= 32 && NT % 32 == 0 && W <= 32 && (ONE || NWARP >= 2), "tile shape");
     const Tile tile = V.tiles[tile_ids[blockIdx.x]];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -545,8 +547,10 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
         WallC wc;
         load_wallc(V, sg, P.single_site != 0, wc);
         const int flg = V.flags[sg];
-        const bool nm = END && ((flg >> (back ? 11 : 10)) & 1);
-        load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][j]);
+        const bool pane = PANE && ((flg >> 12) & 1);
+        const bool nm = END && !pane && ((flg >> (back ? 11 : 10)) & 1);
+        load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][j], pane, back ? V.abL[sg] : V.af0[sg],
+                   back ? V.ax_b[sg] : V.ax_f[sg]);
         w.h = V.sc[(0 + kf) * NS + sg]; w.flow = V.sc[(2 + kf) * NS + sg];
         w.sol = V.sc[(4 + kf) * NS + sg]; w.ir = V.sc[(6 + kf) * NS + sg];
         if (back) {
@@ -612,6 +616,24 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
         }
         face_begin_main_step(c, w, sol_front);
     };
+    // A pane's two faces (lanes j and W + j of this warp) exchange their border conditions and both solve the wall's
+    // 2x2 no-mass system (solve_pane) with identical inputs; each keeps its own node.
+    const unsigned pre_mask = __ballot_sync(0xffffffffu, LEAN ? face_lane : fwall);   // lanes that run pre()
+    auto pane_solve = [&](double h, double rad, double trad) {
+        const double sol_own = c.alpha_end * w.solar + c.alpha_x * __shfl_xor_sync(pre_mask, w.solar, W);
+        const double p_air = __shfl_xor_sync(pre_mask, w.air, W), p_h = __shfl_xor_sync(pre_mask, h, W);
+        const double p_rad = __shfl_xor_sync(pre_mask, rad, W), p_trad = __shfl_xor_sync(pre_mask, trad, W);
+        const double p_ts = __shfl_xor_sync(pre_mask, w.ts, W), p_sol = __shfl_xor_sync(pre_mask, sol_own, W);
+        if (c.fl & FC_PANE) {
+            double t0 = back ? p_ts : w.ts, t1 = back ? w.ts : p_ts;
+            unsigned long long it = 0;
+            solve_pane<LEAN>(back ? p_air : w.air, back ? p_h : h, back ? p_rad : rad, back ? p_trad : trad,
+                             back ? p_sol : sol_own, back ? w.air : p_air, back ? h : p_h, back ? rad : p_rad,
+                             back ? trad : p_trad, back ? sol_own : p_sol, c.u_nb, t0, t1, it, w.status);
+            if (!back) w.nm_iters += it;   // the chunk's iterations are counted once
+            w.ts = back ? t1 : t0;
+        }
+    };
     // border conditions of sub-step s of main step `step` → links for the node lanes
     auto pre = [&](int step, int s) {
         if constexpr (LEAN) {
@@ -632,6 +654,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
             const double xr = 273.15 + (trad + w.ts) / 2.;
             const double rad = c.eps4s * ((xr * xr) * xr);
             if constexpr (END) {
+                if constexpr (PANE) pane_solve(h, rad, trad);
                 if (fl & FC_NM)
                     w.ts = solve_end_node<true>(w.air, h, rad, trad, c.u_nb, s_end[back ? 2 : 1][j],
                                                 c.alpha_end * w.solar, w.ts, w.nm_iters, w.status);
@@ -671,7 +694,10 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
         if constexpr (END)
             if (c.fl & FC_NM) t_nb = s_end[back ? 2 : 1][j];
         double ghost, link;
-        face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, link);
+        FaceEnv e;
+        face_env(c, w, sw, zone_t, t_front, ts_front, e);
+        if constexpr (PANE) pane_solve(e.h, e.rad, e.trad);
+        face_links(c, w, e, t_nb, ghost, link);
         s_link[back ? 2 : 0][j] = ghost;
         s_link[back ? 3 : 1][j] = link;
         if constexpr (END) s_link[back ? 5 : 4][j] = w.ts;
@@ -680,7 +706,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     fill_weather(0);
     if (fwall) main_step_inputs(0);
     __syncthreads();
-    if (fwall) pre(0, 0);
+    if (LEAN ? face_lane : fwall) pre(0, 0);
 
 #ifdef HB_PHASE_CLOCKS
     long long clk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -799,9 +825,9 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
             }
             ++rec;
         }
-        if (fwall && step + 1 < P.n_steps) {
-            main_step_inputs(step + 1);
-            pre(step + 1, 0);
+        if (step + 1 < P.n_steps) {
+            if (fwall) main_step_inputs(step + 1);
+            if (LEAN ? face_lane : fwall) pre(step + 1, 0);
         }
     }
 

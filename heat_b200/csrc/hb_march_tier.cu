@@ -61,6 +61,7 @@ cudaError_t HB_CAT(launch_march_, HB_TIER)(int var, int W, int n_tiles, int s_ma
         case kVarPlain: return launch_face_w<G, kFaceLean>(W, n_tiles, s_max, st, V, P, ids);
         case kVarEnd: return launch_face_w<G, kFaceLeanEnd>(W, n_tiles, s_max, st, V, P, ids);
         case kVarGen: return launch_face_w<G, kFaceGen>(W, n_tiles, s_max, st, V, P, ids);
+        case kVarPane: return launch_face_w<G, kFacePane>(W, n_tiles, s_max, st, V, P, ids);
         case kVarExt: return W == WL ? launch_variant<G, WL, kVarExt>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
         default: return W == WL ? launch_variant<G, WL, kVarDist>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
     }

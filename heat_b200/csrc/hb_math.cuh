@@ -651,6 +651,7 @@ enum : int32_t {
     FC_OUT = 1, FC_SPACE = 2, FC_BACK = 4, FC_TILTED = 8, FC_OV = 16, FC_NM = 32,
     FC_BACK_AMB = 64,        // back face, Boundary::AmbientTemperature: built from FRONT values (surface.rs:672-685)
     FC_FRONT_OUT = 128, FC_FRONT_SPACE = 256,   // kind of the wall's front boundary (needed by FC_BACK_AMB)
+    FC_PANE = 512,           // face of a two-node all-no-mass wall (single glass pane): both faces solve one 2x2 system
 };
 // Constants of one face of one wall.
 struct FaceC {
@@ -659,6 +660,7 @@ struct FaceC {
     double area;
     double v_end;          // dt/C of the face's end node (0: no mass)
     double alpha_end;      // solar absorptance landing on the end node from this side
+    double alpha_x;        // … and from the OTHER side's irradiance (FC_PANE: distributed absorption, else 0)
     double amb;            // AmbientTemperature of this boundary
     double ov;             // film-coefficient override (debug-only field of the reference) when FC_OV
     double forced_c, nx, ny;
@@ -667,7 +669,8 @@ struct FaceC {
     double amb_front;      // FC_BACK_AMB: the front boundary's ambient temperature
     int32_t fl, zone, zone_front, site, desc_index, n;
 };
-HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f) {
+HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f, bool pane = false,
+                      double alpha_own = 0., double alpha_x = 0.) {
     const int wf = c.fl;
     int fl = back ? FC_BACK : 0;
     if (wf & (back ? WF_B_OUT : WF_F_OUT)) fl |= FC_OUT;
@@ -678,13 +681,15 @@ HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f)
     if (wf & WF_F_OUT) fl |= FC_FRONT_OUT;
     if (wf & WF_F_SPACE) fl |= FC_FRONT_SPACE;
     if (nm) fl |= FC_NM;
+    if (pane) fl |= FC_PANE;
     f.fl = fl;
     f.kpos = back ? c.kpos_b : c.kpos_f;
     f.kneg = back ? c.kneg_b : c.kneg_f;
     f.eps4s = back ? c.eps4s_b : c.eps4s_f;
     f.area = c.area;
     f.v_end = back ? c.vL : c.v0;
-    f.alpha_end = back ? c.abL : c.af0;
+    f.alpha_end = pane ? alpha_own : back ? c.abL : c.af0;
+    f.alpha_x = pane ? alpha_x : 0.;
     f.amb = back ? c.amb_b : c.amb_f;
     f.ov = back ? c.ov_b : c.ov_f;
     f.forced_c = c.forced_c; f.nx = c.nx; f.ny = c.ny;
@@ -776,22 +781,67 @@ HB_HD double solve_end_node(double air, double h, double rad, double trad, doubl
 // t_front/ts_front: air temperature and end-node temperature of the wall's FRONT face (FC_BACK_AMB only);
 // t_nb: neighbour node of a no-mass end node (FC_NM).  Returns ghost temperature and link coefficient for the
 // march, and (FC_NM) the end node's new temperature in w.ts.
-HB_HD void face_pre(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
-                    double t_nb, double& ghost, double& link) {
+struct FaceEnv {
+    double h, rad, trad;   // film coefficient, radiative coefficient, radiant temperature (old surface temperatures)
+};
+HB_HD void face_env(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
+                    FaceEnv& e) {
     const int fl = c.fl;
     const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(c.nx, sw.sin_wd), mul_rn(c.ny, sw.cos_wd)) > 0.0);
     w.forced = c.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
     w.air = (fl & FC_OUT) ? sw.t_out : (fl & FC_SPACE) ? zone_t : c.amb;
-    const double trad = (fl & FC_OUT) ? w.trad_out : (fl & FC_BACK_AMB) ? t_front : w.air;
+    e.trad = (fl & FC_OUT) ? w.trad_out : (fl & FC_BACK_AMB) ? t_front : w.air;
     const double ts_env = (fl & FC_BACK_AMB) ? ts_front : w.ts;
-    const double h = face_h(c, w, ts_env, w.status);
-    const double xr = 273.15 + (trad + ts_env) / 2.;
-    const double rad = c.eps4s * ((xr * xr) * xr);
-    if (fl & FC_NM)
-        w.ts = solve_end_node(w.air, h, rad, trad, c.u_nb, t_nb, c.alpha_end * w.solar, w.ts, w.nm_iters, w.status);
-    const double hs = h > 1e-12 ? h : 1e-12;
-    ghost = w.air + (rad * (trad - w.ts) + c.alpha_end * w.solar) * fast_rcp(hs);
+    e.h = face_h(c, w, ts_env, w.status);
+    const double xr = 273.15 + (e.trad + ts_env) / 2.;
+    e.rad = c.eps4s * ((xr * xr) * xr);
+}
+HB_HD void face_links(const FaceC& c, FaceS& w, const FaceEnv& e, double t_nb, double& ghost, double& link) {
+    if (c.fl & FC_NM)
+        w.ts = solve_end_node(w.air, e.h, e.rad, e.trad, c.u_nb, t_nb, c.alpha_end * w.solar, w.ts, w.nm_iters,
+                              w.status);
+    const double hs = e.h > 1e-12 ? e.h : 1e-12;
+    ghost = w.air + (e.rad * (e.trad - w.ts) + c.alpha_end * w.solar) * fast_rcp(hs);
     link = hs * c.v_end;
+}
+HB_HD void face_pre(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
+                    double t_nb, double& ghost, double& link) {
+    FaceEnv e;
+    face_env(c, w, sw, zone_t, t_front, ts_front, e);
+    face_links(c, w, e, t_nb, ghost, link);
+}
+// A single pane (two no-mass nodes, chunk (0, 2)): solve_nomass for m = 2 written out — tridiagonal elimination of
+//   [-(u+h_f)  u; u  -(u+h_b)] x = -(q + absorbed solar)  inside the damped fixed point (surface.rs:790-898).
+// sol0/sol1: absorbed solar of node 0 / node 1 (front_alpha·I_front + back_alpha·I_back, discretization.rs).
+template <bool LEAN = false>
+HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, double sol0, double air_b, double h_b,
+                      double rad_b, double trad_b, double sol1, double u, double& t0, double& t1,
+                      unsigned long long& iters, int& status) {
+    const double dd0 = -u - h_f, dd1 = -u - h_b;
+    const double i0 = LEAN ? -fast_rcp(-dd0) : 1.0 / dd0;
+    const double f = LEAN ? u * i0 : u / dd0;
+    const double dd1e = dd1 - f * u;
+    const double i1 = LEAN ? -fast_rcp(-dd1e) : 1.0 / dd1e;
+    double old_err = 99999.;
+    int count = 0;
+    while (true) {
+        ++iters;
+        const double r0 = -((air_f * h_f + rad_f * (trad_f - t0)) + sol0);
+        double r1 = -((air_b * h_b + rad_b * (trad_b - t1)) + sol1);
+        r1 -= f * r0;
+        const double x1 = LEAN ? r1 * i1 : r1 / dd1e;
+        const double x0 = LEAN ? (r0 - u * x1) * i0 : (r0 - u * x1) / dd0;
+        const double err = fabs(x0 - t0) + fabs(x1 - t1);
+        if (err > old_err) break;
+        if (err != err) { status |= ST_NAN_ERR; break; }
+        t0 = (t0 + x0) * 0.5;
+        t1 = (t1 + x1) * 0.5;
+        const double tol = count < 100 ? 0.01 : 0.5;
+        if (err / 2.0 < tol) break;
+        old_err = err;
+        ++count;
+        if (count > 100000) { status |= ST_ITER_CAP; break; }
+    }
 }
 // After the nodes marched (scalar_post for one face): new film coefficient, convective flow, energy integral and
 // this face's contribution (h·A, h·A·T_s) to calculate_zones_abc.

@@ -324,8 +324,10 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             load_wallc(V, sg, P.single_site != 0, c);
             const int flg = V.flags[sg];
             for (int k = 0; k < 2; ++k) {
-                const bool nm = END && ((flg >> (k ? 11 : 10)) & 1);
-                load_facec(c, k == 1, k ? V.u_b[sg] : V.u_f[sg], nm, fc[2 * t + k]);
+                const bool pane = (tile.flags & TILE_PANE) && ((flg >> 12) & 1);
+                const bool nm = END && !pane && ((flg >> (k ? 11 : 10)) & 1);
+                load_facec(c, k == 1, k ? V.u_b[sg] : V.u_f[sg], nm, fc[2 * t + k], pane, k ? V.abL[sg] : V.af0[sg],
+                           k ? V.ax_b[sg] : V.ax_f[sg]);
                 FaceS w{};
                 w.h = V.sc[(0 + k) * NS + sg]; w.flow = V.sc[(2 + k) * NS + sg];
                 w.sol = V.sc[(4 + k) * NS + sg]; w.ir = V.sc[(6 + k) * NS + sg];
@@ -392,6 +394,8 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
         for (int s = 0; s < S; ++s) {
             for (int t = 0; t < W; ++t) {
                 if (!have[t]) continue;
+                FaceEnv env[2];
+                double t_nb[2] = {0., 0.};
                 for (int k = 0; k < 2; ++k) {
                     const FaceC& c = fc[2 * t + k];
                     FaceS& w = fs[2 * t + k];
@@ -399,14 +403,30 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                     if (P.single_site) sw = swt[s];
                     else weather_at(c.site, step, s, sw);
                     const double zone_t = c.zone >= 0 ? zT[c.zone] : 0.;
-                    double t_front = 0., ts_front = 0., t_nb = 0.;
+                    double t_front = 0., ts_front = 0.;
                     if (c.fl & FC_BACK_AMB) {
                         t_front = (c.fl & FC_FRONT_OUT) ? sw.t_out : (c.fl & FC_FRONT_SPACE) ? zT[c.zone_front] : c.amb_front;
                         ts_front = e0[t];
                     }
-                    if (c.fl & FC_NM) t_nb = k ? e2[t] : e1[t];
+                    if (c.fl & FC_NM) t_nb[k] = k ? e2[t] : e1[t];
+                    face_env(c, w, sw, zone_t, t_front, ts_front, env[k]);
+                }
+                if (fc[2 * t].fl & FC_PANE) {   // the two faces of a pane solve one 2x2 system (hb_face_kernel: pane_solve)
+                    FaceS &wf = fs[2 * t], &wb = fs[2 * t + 1];
+                    const FaceC &cf = fc[2 * t], &cb = fc[2 * t + 1];
+                    const double sol0 = cf.alpha_end * wf.solar + cf.alpha_x * wb.solar;
+                    const double sol1 = cb.alpha_end * wb.solar + cb.alpha_x * wf.solar;
+                    double t0 = wf.ts, t1 = wb.ts;
+                    solve_pane(wf.air, env[0].h, env[0].rad, env[0].trad, sol0, wb.air, env[1].h, env[1].rad, env[1].trad,
+                               sol1, cf.u_nb, t0, t1, wf.nm_iters, wf.status);
+                    wf.ts = t0;
+                    wb.ts = t1;
+                }
+                for (int k = 0; k < 2; ++k) {
+                    const FaceC& c = fc[2 * t + k];
+                    FaceS& w = fs[2 * t + k];
                     double ghost, lk;
-                    face_pre(c, w, sw, zone_t, t_front, ts_front, t_nb, ghost, lk);
+                    face_links(c, w, env[k], t_nb[k], ghost, lk);
                     link[(k ? 2 : 0) * W + t] = ghost;
                     link[(k ? 3 : 1) * W + t] = lk;
                     link[(k ? 5 : 4) * W + t] = w.ts;
