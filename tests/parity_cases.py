@@ -135,3 +135,74 @@ def run_gpu(name: str, max_steps: int | None = None, record_state: bool = False)
     if record_state:
         return zone, final, states, b
     return zone, final
+
+
+def _general_mode_buildings(n):
+    """Buildings that need the general face mode: per-model weather sites and a film-coefficient override on the roof
+    of every third building (windows stay single panes)."""
+    from heat_b200 import cases
+
+    d, gains = cases.shoebox_ensemble(n, seed=11, steps_per_hour=2)
+    surf = d.surfaces.reshape(n, 7)
+    surf["back_hs_override"][::3, 4] = 6.5
+    w0, i0 = cases.synthetic_weather(7)
+    w1 = w0.copy()
+    w1[:, 0] += 4.0
+    w1[:, 1] = np.mod(w1[:, 1] + 90.0, 360.0)
+    w1[:, 2] *= 0.5
+    i1 = i0.copy()
+    i1[:, 0] *= 0.7
+    weather = np.ascontiguousarray(np.stack([w0, w1]))
+    inputs = np.ascontiguousarray(np.stack([i0[:6], i1[:6]]))
+    site = (np.arange(n) % 2).astype(np.int32)
+    return d, gains, weather, inputs, site
+
+
+def check_general_mode_buildings(batch_cls, n=8):
+    import oracle_py as O
+
+    d, gains, weather, inputs, site = _general_mode_buildings(n)
+    n_steps = 6
+    b = batch_cls(d)
+    b.set_zone_inputs(q_internal=gains)
+    b.march_series(n_steps, weather, weather_mode=1, inputs=inputs, input_mode=1, model_site=site)
+    got = b.get_state()
+    off = 0
+    for m in range(d.n_models):
+        om = O.OracleModel(d, m)
+        om.set_zone_inputs(q_internal=gains[m:m + 1])
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather[site[m]], weather_mode=1, inputs=inputs[site[m]], input_mode=1)
+        mine = got[off:off + len(so)]
+        assert abs(mine[0] - so[0]) <= 1e-6
+        for s in range(7):
+            o = om.state_offset(s)
+            nn = om.n_nodes(s)
+            assert np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max() <= 1e-6
+        off += len(so)
+
+
+def check_multi_site_walls(batch_cls, n=48):
+    """Walls (massive and with no-mass layers) under per-model weather sites: general face mode / general kernel."""
+    import oracle_py as O
+
+    d = cases.wall_ensemble(n, seed=21, mixed_fraction=0.5, steps_per_hour=1, max_nodes=120)
+    w0, i0 = cases.synthetic_weather(9)
+    w1 = w0.copy()
+    w1[:, 0] -= 6.0
+    w1[:, 1] = np.mod(w1[:, 1] + 135.0, 360.0)
+    weather = np.ascontiguousarray(np.stack([w0, w1]))
+    n_steps = 8
+    inputs = np.ascontiguousarray(np.stack([i0[:n_steps], 0.5 * i0[:n_steps]]))
+    site = ((np.arange(n) // 3) % 2).astype(np.int32)
+    b = batch_cls(d)
+    b.march_series(n_steps, weather, weather_mode=1, inputs=inputs, input_mode=1, model_site=site)
+    got = b.get_state()
+    off = 0
+    for m in range(d.n_models):
+        om = O.OracleModel(d, m)
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather[site[m]], weather_mode=1, inputs=inputs[site[m]], input_mode=1)
+        mine = got[off:off + len(so)]
+        assert max(np.abs(mine[9:] - so[9:]).max(), abs(mine[0] - so[0])) <= 1e-6, m
+        off += len(so)

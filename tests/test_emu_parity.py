@@ -92,3 +92,11 @@ def test_emulated_shoebox_buildings():
             assert np.abs(mine[o + 8:o + 8 + n] - so[o + 8:o + 8 + n]).max() <= TOL
             assert np.abs(mine[o:o + 4] - so[o:o + 4]).max() <= 1e-5
         off += len(so)
+
+
+def test_emulated_general_face_mode_buildings():
+    pc.check_general_mode_buildings(emu_py.EmuBatch)
+
+
+def test_emulated_multi_site_walls():
+    pc.check_multi_site_walls(emu_py.EmuBatch)

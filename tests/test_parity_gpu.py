@@ -136,6 +136,19 @@ def test_shoebox_buildings_match_oracle():
     assert worst <= TOL, worst
 
 
+def test_general_face_mode_buildings_match_oracle():
+    """Per-model weather sites + a film-coefficient override: the general face-kernel mode, with single-pane windows."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_general_mode_buildings(ThermalBatch, n=20)
+
+
+def test_multi_site_walls_match_oracle():
+    from heat_b200.model import ThermalBatch
+
+    pc.check_multi_site_walls(ThermalBatch)
+
+
 def test_reduce_matches_state():
     from heat_b200 import cases
     from heat_b200.model import ThermalBatch
