@@ -166,7 +166,8 @@ void build_device(hb_handle* h) {
     std::map<std::tuple<int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
-        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5 : (t.flags & hb::TILE_END) ? 3 : 0;
+        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5
+                        : (t.flags & hb::TILE_END) ? ((t.flags & hb::TILE_SIMPLE) ? 7 : 3) : ((t.flags & hb::TILE_SIMPLE) ? 6 : 0);
         // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
         by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.G, var, t.W}].push_back((int32_t)ti);
     }
@@ -225,7 +226,7 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         }
         cudaError_t e;
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
-        const int var = (g.var == 0 || g.var == 3 || g.var == 5) && !P.single_site ? 4 : g.var;
+        const int var = (g.var == 0 || g.var == 3 || g.var >= 5) && !P.single_site ? 4 : g.var;
         switch (g.G) {
             case 1: e = hb::launch_march_1(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
             case 2: e = hb::launch_march_2(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;

@@ -269,7 +269,7 @@ inline bool is_pane(const SurfacePlan& P) {
     return P.n_nodes == 2 && P.cavities.empty() && P.nomass_chunks.size() == 2 && P.nomass_chunks[0] == 0 &&
            P.nomass_chunks[1] == 2;
 }
-constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE;   // tiles are uniform in these
+constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE;   // tiles are uniform in these
 
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
@@ -392,6 +392,11 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
                     s.back_hs_override == s.back_hs_override)
                     M.variant |= TILE_END | TILE_GEN;
             }
+        // one wall with its own zone behind it: the zone is advanced in the back-face lane's registers
+        if ((M.variant == 0 || M.variant == TILE_END) && M.n_surfaces == 1 && M.n_zones == 1) {
+            const hb_surface& s = B.surfaces[M.surface_begin];
+            if (s.back_kind == HB_BOUNDARY_SPACE && s.front_kind != HB_BOUNDARY_SPACE) M.variant |= TILE_SIMPLE;
+        }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)
             fail("model larger than one tile (" + std::to_string(Wmax) + " surfaces / zones at this wall size)");

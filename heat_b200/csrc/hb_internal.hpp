@@ -91,6 +91,7 @@ enum : int32_t {
     TILE_CAV = 4,    // some wall has a gas cavity (temperature-dependent link)
     TILE_END = 8,    // the only no-mass chunks are single nodes at the ends of walls (solved by the face lanes)
     TILE_PANE = 32,  // face-kernel tile with single-pane windows (two no-mass nodes solved jointly by the face lanes)
+    TILE_SIMPLE = 64,  // face-kernel tile whose models are one wall with its own zone behind it (zone j <-> wall j)
     TILE_GEN = 16,   // face-kernel tile with a film-coefficient override or an AmbientTemperature back boundary
 };
 

@@ -25,7 +25,8 @@
 
 namespace hb {
 
-constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4, kVarPane = 5;
+constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4, kVarPane = 5, kVarPlainSimple = 6,
+              kVarEndSimple = 7;
 // hb_face_kernel modes: lean (all ends massive), lean with no-mass end nodes, general (everything), lean with
 // no-mass end nodes and single panes
 constexpr int kFaceLean = 0, kFaceLeanEnd = 1, kFaceGen = 2, kFacePane = 3;
@@ -362,6 +363,9 @@ __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V
 //     neighbouring lanes while the six inner slots are computed.
 // ----------------------------------------------------------------------------------------------------------------
 #ifdef HB_PHASE_CLOCKS
+#ifndef HB_CLK_MIN_S
+#define HB_CLK_MIN_S 100   // tiles with at least this many sub-steps report (they run alone on their SM at the end)
+#endif
 __device__ unsigned long long hb_phase_clk[8];   // wait B1, node, wait B2, post, zone, pre, -, sub-steps
 #define HB_CLK(k) { const long long _t = clock64(); clk[k] += _t - tlast; tlast = _t; }
 #else
@@ -438,7 +442,7 @@ __device__ __forceinline__ void node_rk4(double (&T)[NL], const double (&A)[NL],
 #ifndef HB_FACE_OCC
 #define HB_FACE_OCC 512   // resident threads per SM the face kernel is compiled for (512: 128 registers per thread)
 #endif
-template <int G, int W, int MODE>
+template <int G, int W, int MODE, bool SIMPLE>
 __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads(G, W))
     hb_face_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     constexpr bool END = MODE != kFaceLean;    // single-node no-mass chunks at the ends of walls are possible
@@ -457,7 +461,8 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
 
     __shared__ ZoneC s_zc[W];
     __shared__ double s_zT[W];
-    __shared__ double s_pub[4][W];      // h·A and h·A·T_s of the front face, then of the back face
+    __shared__ double s_pub[4][W];      // h·A and h·A·T_s of the front face, then of the back face (general mode)
+    __shared__ double2 s_pub2[2][W];    // (h·A, h·A·T_s) of the front / back face (lean modes)
     __shared__ int32_t s_zf[W], s_zb[W];
     __shared__ double s_end[4][W];      // node 0, node 1, node n-2, node n-1
     __shared__ double s_link[6][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
@@ -569,8 +574,23 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     }
     // the front warp has to wait for the zone update only if one of its faces looks at a zone
     const bool front_waits = __syncthreads_or(any_front_zone ? 1 : 0) != 0;
-    const bool simple = __syncthreads_and(simple_ok ? 1 : 0) != 0 && !front_waits;
+    // SIMPLE tiles (TILE_SIMPLE, decided on the host): every zone has exactly one wall, wall j <-> zone j, whose
+    // back face looks at it, and no front face looks at a zone.  The kernel re-checks and reports a mismatch.
+    constexpr bool simple = SIMPLE;
+    if (SIMPLE && !(__syncthreads_and(simple_ok ? 1 : 0) != 0 && !front_waits) && tid == 0)
+        atomicOr(&V.status[tile.surface_begin], ST_NAN_ZONE);
     if (fwall) w.ts = s_end[back ? 3 : 0][j];
+    // zone lanes: which faces of the tile look at my zone (bit j of zmf / zmb: front / back face of wall j)
+    unsigned zmf = 0, zmb = 0;
+    int zsb = 0, zcnt = 0;
+    if (!SIMPLE && szone) {
+        zsb = s_zc[j].sb;
+        zcnt = s_zc[j].se - zsb;
+        for (int q = zsb; q < zsb + zcnt; ++q) {
+            if (s_zf[q] == j) zmf |= 1u << q;
+            if (s_zb[q] == j) zmb |= 1u << q;
+        }
+    }
     const double ir_state = w.ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
 
     // sub-step weather of main step `step` into buffer step & 1 (all threads of the block)
@@ -767,7 +787,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
                     face_post(c, w, ts, ts_front, dt, hA, hAT);
                 }
                 HB_CLK(3)
-                if (simple) {
+                if constexpr (simple) {
                     if constexpr (LEAN) {   // the lane's own wall is the zone's only surface (back face)
                         const double inv_cc = zone_inv_c_t<true>(zvol, zT);
                         const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT, zb0 + hA);
@@ -781,6 +801,45 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
                         const double tn = zone_advance(zT, dt, inv_cc, a, b);
                         if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
                         zT = tn;
+                    }
+                } else if (LEAN) {
+                    // the faces publish (h·A, h·A·T_s) as one 16-byte store; a zone lane sums its surfaces with a
+                    // fixed, fully unrolled window of 8 (all loads in flight at once, four independent partial
+                    // sums) — deterministic; differs from the reference's sequential order by rounding only
+                    if (fwall) s_pub2[kf][j] = make_double2(hA, hAT);
+                    if constexpr (ONE) {
+                        __syncwarp();
+                    } else {
+                        if (back || front_waits) pair_sync(); else pair_arrive();
+                    }
+                    if (szone) {
+                        double af = 0., bf = 0., ab = 0., bb = 0.;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int jj = zsb + q < W ? zsb + q : W - 1;
+                            const double2 vf = s_pub2[0][jj], vb = s_pub2[1][jj];
+                            const bool uf = q < zcnt && ((zmf >> jj) & 1u), ub = q < zcnt && ((zmb >> jj) & 1u);
+                            bf += uf ? vf.x : 0.;
+                            af += uf ? vf.y : 0.;
+                            bb += ub ? vb.x : 0.;
+                            ab += ub ? vb.y : 0.;
+                        }
+                        for (int q = 8; q < zcnt; ++q) {
+                            const int jj = zsb + q;
+                            const double2 vf = s_pub2[0][jj], vb = s_pub2[1][jj];
+                            if ((zmf >> jj) & 1u) { bf += vf.x; af += vf.y; }
+                            if ((zmb >> jj) & 1u) { bb += vb.x; ab += vb.y; }
+                        }
+                        const double inv_cc = zone_inv_c_t<true>(zvol, zT);
+                        const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + (af + ab), zb0 + (bf + bb));
+                        if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + zsb], ST_NAN_ZONE);
+                        s_zT[j] = tn;
+                        zT = tn;
+                    }
+                    if constexpr (ONE) {
+                        __syncwarp();
+                    } else {
+                        if (front_waits) pair_sync(); else if (back) __syncwarp();
                     }
                 } else {
                     if (fwall) {
@@ -832,7 +891,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     }
 
 #ifdef HB_PHASE_CLOCKS
-    if (szone && j == 0 && S >= 100)
+    if (szone && j == 0 && S >= HB_CLK_MIN_S)
         for (int q = 0; q < 8; ++q) atomicAdd(&hb_phase_clk[q], (unsigned long long)clk[q]);
 #endif
     // ---- write the state back ----

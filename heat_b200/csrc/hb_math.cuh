@@ -626,10 +626,27 @@ HB_HD double zone_update_ab(const ZoneC& z, int zi, double tz, double dt, double
                             const double* pub_hAT_f, const double* pub_hA_b, const double* pub_hAT_b,
                             const int32_t* zf, const int32_t* zb) {
     const double inv_cc = zone_inv_c_t<LEAN>(z.vol, tz);
+    if constexpr (LEAN) {
+        // four independent partial sums (front/back x a/b), loads issued ahead of the adds: the sums differ from the
+        // reference's strictly sequential order by rounding only
+        double af = 0., bf = 0., ab = 0., bb = 0.;
+#pragma unroll 4
+        for (int j = z.sb; j < z.se; ++j) {
+            const bool f = zf[j] == zi, k = zb[j] == zi;
+            const double haf = pub_hA_f[j], hatf = pub_hAT_f[j], hab = pub_hA_b[j], hatb = pub_hAT_b[j];
+            af += f ? hatf : 0.;
+            bf += f ? haf : 0.;
+            ab += k ? hatb : 0.;
+            bb += k ? hab : 0.;
+        }
+        a += af + ab;
+        b += bf + bb;
+    } else {
 #pragma unroll 1
-    for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
-        if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
-        if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
+        for (int j = z.sb; j < z.se; ++j) {   // surfaces then fenestrations, front face before back face
+            if (zf[j] == zi) { a += pub_hAT_f[j]; b += pub_hA_f[j]; }
+            if (zb[j] == zi) { a += pub_hAT_b[j]; b += pub_hA_b[j]; }
+        }
     }
     return zone_advance<LEAN>(tz, dt, inv_cc, a, b);
 }
@@ -822,6 +839,31 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
     const double f = LEAN ? u * i0 : u / dd0;
     const double dd1e = dd1 - f * u;
     const double i1 = LEAN ? -fast_rcp(-dd1e) : 1.0 / dd1e;
+    if constexpr (LEAN) {
+        // the elimination is affine in (t0, t1): x1 = c1 + m10 t0 + m11 t1, x0 = c0 + n00 t0 + n01 x1 — the same
+        // iteration and stopping rules on a chain of three dependent operations per pass
+        const double k0 = -((air_f * h_f + rad_f * trad_f) + sol0), k1 = -((air_b * h_b + rad_b * trad_b) + sol1);
+        const double c1 = (k1 - f * k0) * i1, m10 = -(f * rad_f) * i1, m11 = rad_b * i1;
+        const double c0 = k0 * i0, n00 = rad_f * i0, n01 = -(u * i0);
+        double old_err = 99999.;
+        int count = 0;
+        while (true) {
+            ++iters;
+            const double x1 = fma(m11, t1, fma(m10, t0, c1));
+            const double x0 = fma(n01, x1, fma(n00, t0, c0));
+            const double err = fabs(x0 - t0) + fabs(x1 - t1);
+            if (err > old_err) break;
+            if (err != err) { status |= ST_NAN_ERR; break; }
+            t0 = (t0 + x0) * 0.5;
+            t1 = (t1 + x1) * 0.5;
+            const double tol = count < 100 ? 0.01 : 0.5;
+            if (err * 0.5 < tol) break;
+            old_err = err;
+            ++count;
+            if (count > 100000) { status |= ST_ITER_CAP; break; }
+        }
+        return;
+    }
     double old_err = 99999.;
     int count = 0;
     while (true) {
