@@ -591,6 +591,14 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
             if (s_zb[q] == j) zmb |= 1u << q;
         }
     }
+    // Segmented form (buildings): every zone is looked at by exactly the back faces of its own surfaces [sb, se) —
+    // contiguous lanes of this warp — so all zones are summed at once by a segmented shuffle scan.
+    int seg_last = -1;   // last lane of the segment this (back, zone-facing) face belongs to
+    bool seg_ok_lane = LEAN && ONE && !SIMPLE;
+    if (!SIMPLE && szone)
+        seg_ok_lane = seg_ok_lane && zmf == 0 && zcnt <= 16 && zmb == (((1u << zcnt) - 1u) << zsb);
+    if (!SIMPLE && fwall && back && c.zone >= 0) seg_last = W + s_zc[c.zone].se - 1;
+    const bool seg_ok = !SIMPLE && __syncthreads_and(seg_ok_lane ? 1 : 0) != 0;
     const double ir_state = w.ir;   // front face: IR slot as found in the state (HB_IR_NET_GAIN with ε ≤ 1e-3)
 
     // sub-step weather of main step `step` into buffer step & 1 (all threads of the block)
@@ -802,6 +810,24 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
                         if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
                         zT = tn;
                     }
+                } else if (LEAN && ONE && seg_ok) {
+                    double va = hAT, vb = hA;
+#pragma unroll
+                    for (int o = 1; o <= 8; o <<= 1) {
+                        const double ta = __shfl_down_sync(0xffffffffu, va, o), tb = __shfl_down_sync(0xffffffffu, vb, o);
+                        if (lane + o <= seg_last) { va += ta; vb += tb; }
+                    }
+                    const int src = szone && zcnt > 0 ? W + zsb : lane;
+                    const double asum = __shfl_sync(0xffffffffu, va, src), bsum = __shfl_sync(0xffffffffu, vb, src);
+                    if (szone) {
+                        const double inv_cc = zone_inv_c_t<true>(zvol, zT);
+                        const double tn = zone_advance<true>(zT, dt, inv_cc, zcnt > 0 ? za0 + asum : za0,
+                                                             zcnt > 0 ? zb0 + bsum : zb0);
+                        if (tn != tn) atomicOr(&V.status[(int64_t)tile.surface_begin + zsb], ST_NAN_ZONE);
+                        s_zT[j] = tn;
+                        zT = tn;
+                    }
+                    __syncwarp();
                 } else if (LEAN) {
                     // the faces publish (h·A, h·A·T_s) as one 16-byte store; a zone lane sums its surfaces with a
                     // fixed, fully unrolled window of 8 (all loads in flight at once, four independent partial
