@@ -286,6 +286,55 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     return D.BatchDesc(layers, off.astype(np.int32), zo, so, volume, surfaces.reshape(-1), steps_per_hour), gains
 
 
+def two_zone_ensemble(n_buildings: int, seed: int = 44, *, steps_per_hour: int = 2):
+    """`n_buildings` two-zone buildings: zones 0 and 1 with four outdoor walls each and one partition whose front face
+    looks at zone 0 and whose back face looks at zone 1 (a surface between two spaces, model.rs:79-96), plus a
+    single-pane window on zone 1.  Returns (BatchDesc, q_internal[2·n_buildings])."""
+    rng = SplitMix64(seed)
+    n = n_buildings
+    n_lay = 1 + (rng.next_u64(n) % np.uint64(2)).astype(np.int64)
+    off = np.zeros(n + 2, np.int64)
+    np.cumsum(n_lay, out=off[1:n + 1])
+    total = int(off[n])
+    off[n + 1] = total + 1
+    k, rho, cp, th = _random_layers(rng, total)
+    layers = np.zeros(total + 1, D.LAYER_DTYPE)
+    layers["kind"] = D.LAYER_SOLID
+    layers["thickness"][:total], layers["conductivity"][:total] = th, k
+    layers["density"][:total], layers["specific_heat"][:total] = rho, cp
+    for f, v in (("front_emissivity", 0.9), ("back_emissivity", 0.85), ("front_solar_abs", 0.6), ("back_solar_abs", 0.5)):
+        layers[f][:total] = v
+    layers["solar_transmittance"] = D.NAN
+    layers[total] = glass(0.004, 0.7, 0.84, 0.15)
+    volume = rng.uniform(2 * n, 40.0, 300.0)
+    gains = rng.uniform(2 * n, 0.0, 400.0)
+    NSURF = 10
+    surfaces = np.zeros((n, NSURF), D.SURFACE_DTYPE)
+    surfaces["construction"] = np.arange(n)[:, None]
+    surfaces["front_kind"], surfaces["back_kind"] = D.BOUNDARY_OUTDOOR, D.BOUNDARY_SPACE
+    surfaces["front_zone"] = -1
+    surfaces["back_zone"][:, 0:4] = 0
+    surfaces["back_zone"][:, 4:8] = 1
+    surfaces["front_kind"][:, 8] = D.BOUNDARY_SPACE       # the partition
+    surfaces["front_zone"][:, 8] = 0
+    surfaces["back_zone"][:, 8] = 1
+    surfaces["construction"][:, 9] = n                     # window on zone 1 (fenestrations come last)
+    surfaces["is_fenestration"][:, 9] = 1
+    surfaces["back_zone"][:, 9] = 1
+    normals = np.array([(0, -1, 0), (1, 0, 0), (0, 1, 0), (0, 0, 1)] * 2 + [(1, 0, 0), (0, -1, 0)], float)
+    surfaces["normal"] = normals[None]
+    area = rng.uniform(n, 6.0, 20.0)
+    surfaces["area"] = area[:, None]
+    surfaces["area"][:, 9] = 0.25 * area
+    surfaces["perimeter"] = 4.0 * np.sqrt(surfaces["area"])
+    surfaces["centroid_z"] = 1.5
+    for f in ("front_hs_override", "back_hs_override", "front_emissivity_override", "back_emissivity_override"):
+        surfaces[f] = D.NAN
+    zo = (np.arange(n + 1, dtype=np.int64) * 2).astype(np.int32)
+    so = (np.arange(n + 1, dtype=np.int64) * NSURF).astype(np.int32)
+    return D.BatchDesc(layers, off.astype(np.int32), zo, so, volume, surfaces.reshape(-1), steps_per_hour), gains
+
+
 def synthetic_weather(n_rows: int, seed: int = 7):
     """Smooth annual + diurnal series: returns weather[n_rows][3] and inputs[n_rows][4]
     (front solar, back solar, front IR, back IR), hourly rows."""

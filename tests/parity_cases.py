@@ -206,3 +206,29 @@ def check_multi_site_walls(batch_cls, n=48):
         mine = got[off:off + len(so)]
         assert max(np.abs(mine[9:] - so[9:]).max(), abs(mine[0] - so[0])) <= 1e-6, m
         off += len(so)
+
+
+def check_two_zone_buildings(batch_cls, n=6, n_steps=6):
+    """Two zones per model coupled by a partition (front face -> zone 0, back face -> zone 1) + a pane on zone 1:
+    the zone sums take the general (non-segmented) path, with more than 8 surfaces per model."""
+    import oracle_py as O
+
+    d, gains = cases.two_zone_ensemble(n, seed=44, steps_per_hour=2)
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    b = batch_cls(d)
+    b.set_zone_inputs(q_internal=gains)
+    b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+    got = b.get_state()
+    off = 0
+    for m in range(d.n_models):
+        om = O.OracleModel(d, m)
+        om.set_zone_inputs(q_internal=gains[2 * m:2 * m + 2])
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        mine = got[off:off + len(so)]
+        assert np.abs(mine[0:2] - so[0:2]).max() <= 1e-6, (m, mine[0:2], so[0:2])
+        for s in range(om.n_surfaces):
+            o = om.state_offset(s)
+            nn = om.n_nodes(s)
+            assert np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max() <= 1e-6, (m, s)
+        off += len(so)

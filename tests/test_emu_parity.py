@@ -100,3 +100,7 @@ def test_emulated_general_face_mode_buildings():
 
 def test_emulated_multi_site_walls():
     pc.check_multi_site_walls(emu_py.EmuBatch)
+
+
+def test_emulated_two_zone_buildings():
+    pc.check_two_zone_buildings(emu_py.EmuBatch)

@@ -149,6 +149,12 @@ def test_multi_site_walls_match_oracle():
     pc.check_multi_site_walls(ThermalBatch)
 
 
+def test_two_zone_buildings_match_oracle():
+    from heat_b200.model import ThermalBatch
+
+    pc.check_two_zone_buildings(ThermalBatch, n=20, n_steps=12)
+
+
 def test_reduce_matches_state():
     from heat_b200 import cases
     from heat_b200.model import ThermalBatch
