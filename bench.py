@@ -69,12 +69,14 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, n_gpus: int):
+        """One sampler for the GPUs 0..n_gpus-1 of the box (run by rank 0 only: one NVML client, not one per rank)."""
+        self.rows, self.proc, self.n_gpus = [], None, n_gpus
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+            ids = ",".join(str(i) for i in range(self.n_gpus))
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", ids, f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
@@ -199,13 +201,14 @@ def main():
     # ---- value: inputs resident in HBM, CUDA-event timing on the launching stream ----
     launches0 = None
     ms = []
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(world) if rank == 0 else None
     for it in range(a.warmup + a.steps):
         batch.set_state(initial)
         batch.flush_l2()
         barrier()
         if it == a.warmup:
-            sampler.start()
+            if sampler:
+                sampler.start()
             launches0 = batch.launch_count
         t = batch.march_series_dev(hours, w_dev, hours + 1, 1, weather_mode=_lib.WEATHER_LINEAR, inputs_dev=i_dev,
                                    input_mode=_lib.INPUT_SITE)
@@ -213,7 +216,7 @@ def main():
         if it >= a.warmup:
             ms.append(t)
     gpu_launches = batch.launch_count - launches0
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
     stats = batch.reduce()
 
     # ---- e2e: the public host-buffer API; H2D of the step's inputs and D2H of its result inside the timed region ----
@@ -234,7 +237,11 @@ def main():
     from heat_b200.dist import EnsembleStats, combine_stats, max_over_ranks, sum_over_ranks
     dev = "cuda" if dist is not None else None
     # slowest rank's time; units of all ranks; the path's only collective: the final ensemble statistics (NCCL)
-    t_step, t_e2e = max_over_ranks([float(np.mean(ms)) * 1e-3, float(np.mean(e2e_s))], dev)
+    t_local = float(np.mean(ms)) * 1e-3
+    by_rank = [0.0] * world
+    by_rank[rank] = t_local * 1e3
+    by_rank = sum_over_ranks(by_rank, dev)   # every rank's own device time, for the record
+    t_step, t_e2e = max_over_ranks([t_local, float(np.mean(e2e_s))], dev)
     total_updates = sum_over_ranks([float(updates_per_step)], dev)[0]
     es = combine_stats(EnsembleStats.from_c(stats), dev)
     reduced = {"mean_zone_t": es.mean_zone_t, "mean_node_t": es.mean_node_t,
@@ -259,7 +266,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": wname, "hours": hours, "steps_per_hour": 1, "weather": "linear between hourly rows",
                        "updates_per_step_per_gpu": int(updates_per_step), "nodes_per_gpu": int(batch.nodes),
-                       "l2": "flushed between timed iterations (256 MiB write)", "ensemble_stats": reduced},
+                       "l2": "flushed between timed iterations (256 MiB write)",
+                       "ms_per_step_by_rank": [round(x, 2) for x in by_rank], "ensemble_stats": reduced},
             "roofline": {"bound": "fp64", "achieved": fp64_achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": fp64_achieved / fp64_peak if fp64_peak else None, "traffic": None,
                          "flop_per_update": FLOP_PER_UPDATE,

@@ -18,6 +18,7 @@ struct DevView {
     const int32_t* n_nodes;   // 0 on padding slots
     const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity,
                               // 10 / 11: node 0 / node n-1 is a single-node no-mass chunk (TILE_END tiles)
+                              // 13 / 14: the front / back end is a TWO-node no-mass chunk (nodes 0,1 / n-2,n-1; 10 / 11 set too)
                               // 12: the wall is a pane (two no-mass nodes, chunk (0,2); TILE_PANE tiles; 10 and 11 set too)
     const int32_t* zone_f;    // tile-local zone index or -1
     const int32_t* zone_b;
@@ -40,6 +41,8 @@ struct DevView {
     const double* vL;         // dt/C of node n-1
     const double* u_f;        // conductance of the link node 0 → 1 (TILE_END)
     const double* u_b;        // conductance of the link node n-2 → n-1
+    const double* u_f2;       // conductance of the link node 1 → 2 (two-node no-mass chunk at the front end)
+    const double* u_b2;       // conductance of the link node n-3 → n-2 (… at the back end)
     const double* ax_f;       // panes (flags bit 12): absorptance of node 0 for the BACK irradiance
     const double* ax_b;       // panes: absorptance of node n-1 for the FRONT irradiance
     const int32_t* nm_off;    // CSR over no-mass chunks: pairs (ini, fin)
@@ -81,7 +84,7 @@ struct HostArrays {
     std::vector<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     std::vector<CavityDev> cav;
     std::vector<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL,
-        u_f, u_b, ax_f, ax_b;
+        u_f, u_b, u_f2, u_b2, ax_f, ax_b;
     std::vector<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     std::vector<unsigned long long> nm_iters;
     std::vector<int32_t> status;

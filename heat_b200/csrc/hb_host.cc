@@ -369,10 +369,13 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
                 continue;
             }
             rest |= v;
+            int nm_nodes = 0;   // no-mass chunks of one or two nodes at the ends, at least one massive node in between
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2) {
                 const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
-                if (fin - ini != 1 || P.n_nodes < 3 || (ini != 0 && fin != P.n_nodes)) ends_only = false;
+                if (fin - ini > 2 || (ini != 0 && fin != P.n_nodes)) ends_only = false;
+                nm_nodes += fin - ini;
             }
+            if (nm_nodes > 0 && P.n_nodes - nm_nodes < 1) ends_only = false;
         }
         if (panes && (rest == 0 || rest == TILE_EXT) && ends_only) {
             const int nmax2 = std::max<int>(M.nmax, kNL - 1);
@@ -486,7 +489,7 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
     H.site.assign(NS, 0); H.desc_index.assign(NS, 0); H.nm_off.assign(NS + 1, 0); H.cav_off.assign(NS + 1, 0);
     H.nm_pairs.clear(); H.cav.clear();
     for (auto* v : {&H.area, &H.nx, &H.ny, &H.cos_tilt, &H.forced_c, &H.eps_f, &H.eps_b, &H.amb_f, &H.amb_b, &H.af0,
-                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.ax_f, &H.ax_b, &H.energy_f, &H.energy_b})
+                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.u_f2, &H.u_b2, &H.ax_f, &H.ax_b, &H.energy_f, &H.energy_b})
         v->assign(NS, 0.);
     H.hs_ov_f.assign(NS, NAN); H.hs_ov_b.assign(NS, NAN);
     H.nodeT.assign(B.node_slab_len, 0.); H.coefA.assign(B.node_slab_len, 0.); H.coefB.assign(B.node_slab_len, 0.);
@@ -513,11 +516,17 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
                      ((P.cavities.empty() ? 0 : 1) << 9);
         if (tile.flags & TILE_END)
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2)
-                H.flags[g] |= P.nomass_chunks[c] == 0 ? (1 << 10) : (1 << 11);
+            {
+                const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
+                H.flags[g] |= ini == 0 ? (1 << 10) : (1 << 11);
+                if (fin - ini == 2 && !is_pane(P)) H.flags[g] |= ini == 0 ? (1 << 13) : (1 << 14);
+            }
         const bool pane = (tile.flags & TILE_PANE) && is_pane(P);
         if (pane) H.flags[g] |= (1 << 10) | (1 << 11) | (1 << 12);
         H.u_f[g] = n > 1 ? P.u[0] : 0.;
         H.u_b[g] = n > 1 ? P.u[n - 2] : 0.;
+        H.u_f2[g] = n > 2 ? P.u[1] : 0.;
+        H.u_b2[g] = n > 2 ? P.u[n - 3] : 0.;
         const int zone_local0 = M.n_zones ? B.dev_zone_of[M.zone_begin] - tile.zone_begin : 0;
         H.zone_f[g] = s.front_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.front_zone : -1;
         H.zone_b[g] = s.back_kind == HB_BOUNDARY_SPACE ? zone_local0 + s.back_zone : -1;
@@ -601,7 +610,7 @@ DevView HostArrays::view(const BatchPlan& B) {
     V.site = site.data(); V.desc_index = desc_index.data(); V.area = area.data(); V.nx = nx.data(); V.ny = ny.data();
     V.cos_tilt = cos_tilt.data(); V.forced_c = forced_c.data(); V.eps_f = eps_f.data(); V.eps_b = eps_b.data();
     V.amb_f = amb_f.data(); V.amb_b = amb_b.data(); V.hs_ov_f = hs_ov_f.data(); V.hs_ov_b = hs_ov_b.data();
-    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data(); V.ax_f = ax_f.data(); V.ax_b = ax_b.data();
+    V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data(); V.u_f2 = u_f2.data(); V.u_b2 = u_b2.data(); V.ax_f = ax_f.data(); V.ax_b = ax_b.data();
     V.nm_off = nm_off.data(); V.nm_pairs = nm_pairs.data(); V.cav_off = cav_off.data(); V.cav = cav.data();
     V.nodeT = nodeT.data(); V.coefA = coefA.data(); V.coefB = coefB.data();
     V.ext_u = ext_u.data(); V.ext_mass = ext_mass.data(); V.ext_af = ext_af.data(); V.ext_ab = ext_ab.data();

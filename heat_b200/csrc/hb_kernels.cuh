@@ -464,8 +464,8 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     __shared__ double s_pub[4][W];      // h·A and h·A·T_s of the front face, then of the back face (general mode)
     __shared__ double2 s_pub2[2][W];    // (h·A, h·A·T_s) of the front / back face (lean modes)
     __shared__ int32_t s_zf[W], s_zb[W];
-    __shared__ double s_end[4][W];      // node 0, node 1, node n-2, node n-1
-    __shared__ double s_link[6][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
+    __shared__ double s_end[6][W];      // node 0, node 1, node n-2, node n-1, node 2, node n-3 (the last two: END)
+    __shared__ double s_link[8][W];     // ghost_f, link_f, ghost_b, link_b, T(node 0), T(node n-1) (END)
     // sub-step weather of two consecutive main steps, [2][S] (dynamic: 2·S_max(group) rows, launch_face)
     SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn);
     __shared__ FaceC s_fc[2][W];        // per-face constants: read from shared memory where they are used
@@ -481,6 +481,7 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     const int iN = n - part * NL;        // lane-local index of the last node's slot (slot n)
     const int iG = n + 1 - part * NL;    // … of the back ghost (slot n+1)
     const int nmf = END ? (V.flags[g] >> 10) & 1 : 0, nmb = END ? (V.flags[g] >> 11) & 1 : 0;
+    const int nmf2 = END ? (V.flags[g] >> 13) & 1 : 0, nmb2 = END ? (V.flags[g] >> 14) & 1 : 0;   // two-node end chunks
     double T[NL], A[NL], B[NL];
     if (node_lane) {
         const int64_t o = tile.node_offset + tid;
@@ -503,16 +504,26 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
     };
     static_assert(NL == 8, "slot() is an 8-way mux");
     const bool has_last = iN >= 0 && iN < NL, has_prev = END && iN - 1 >= 0 && iN - 1 < NL;
+    const bool has_prev2 = END && iN - 2 >= 0 && iN - 2 < NL;
+    double* const p_prev2 = &s_end[5][wl];
     double* const p_last = &s_end[3][wl];
     double* const p_prev = &s_end[2][wl];
     auto publish_ends = [&]() {
         if (part == 0) {
             s_end[0][wl] = T[1];
-            if constexpr (END) s_end[1][wl] = T[2];
+            if constexpr (END) {
+                s_end[1][wl] = T[2];
+                s_end[4][wl] = T[3];
+            }
         }
-        if (has_last) *p_last = slot(iN);
-        if constexpr (END)
-            if (has_prev) *p_prev = slot(iN - 1);
+        // muxes evaluated by every lane (no divergent regions), predicated stores
+        const double v_last = slot(iN & (NL - 1));
+        if (has_last) *p_last = v_last;
+        if constexpr (END) {
+            const double v_prev = slot((iN - 1) & (NL - 1)), v_prev2 = slot((iN - 2) & (NL - 1));
+            if (has_prev) *p_prev = v_prev;
+            if (has_prev2) *p_prev2 = v_prev2;
+        }
     };
     if (node_lane) publish_ends();
 
@@ -554,8 +565,9 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
         const int flg = V.flags[sg];
         const bool pane = PANE && ((flg >> 12) & 1);
         const bool nm = END && !pane && ((flg >> (back ? 11 : 10)) & 1);
+        const bool nm2 = nm && ((flg >> (back ? 14 : 13)) & 1);
         load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, s_fc[kf][j], pane, back ? V.abL[sg] : V.af0[sg],
-                   back ? V.ax_b[sg] : V.ax_f[sg]);
+                   back ? V.ax_b[sg] : V.ax_f[sg], nm2, back ? V.u_b2[sg] : V.u_f2[sg]);
         w.h = V.sc[(0 + kf) * NS + sg]; w.flow = V.sc[(2 + kf) * NS + sg];
         w.sol = V.sc[(4 + kf) * NS + sg]; w.ir = V.sc[(6 + kf) * NS + sg];
         if (back) {
@@ -683,7 +695,12 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
             const double rad = c.eps4s * ((xr * xr) * xr);
             if constexpr (END) {
                 if constexpr (PANE) pane_solve(h, rad, trad);
-                if (fl & FC_NM)
+                if (fl & FC_NM2) {
+                    double t_in = s_end[back ? 2 : 1][j];
+                    solve_end_pair<true>(back, w.air, h, rad, trad, c.alpha_end * w.solar, c.u_nb, c.u_nb2,
+                                         s_end[back ? 5 : 4][j], w.ts, t_in, w.nm_iters, w.status);
+                    s_link[back ? 7 : 6][j] = t_in;
+                } else if (fl & FC_NM)
                     w.ts = solve_end_node<true>(w.air, h, rad, trad, c.u_nb, s_end[back ? 2 : 1][j],
                                                 c.alpha_end * w.solar, w.ts, w.nm_iters, w.status);
                 s_link[back ? 5 : 4][j] = w.ts;
@@ -725,7 +742,10 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
         FaceEnv e;
         face_env(c, w, sw, zone_t, t_front, ts_front, e);
         if constexpr (PANE) pane_solve(e.h, e.rad, e.trad);
-        face_links(c, w, e, t_nb, ghost, link);
+        const double t_nb2 = (END && (c.fl & FC_NM2)) ? s_end[back ? 5 : 4][j] : 0.;
+        face_links(c, w, e, t_nb, t_nb2, ghost, link);
+        if constexpr (END)
+            if (c.fl & FC_NM2) s_link[back ? 7 : 6][j] = t_nb;
         s_link[back ? 2 : 0][j] = ghost;
         s_link[back ? 3 : 1][j] = link;
         if constexpr (END) s_link[back ? 5 : 4][j] = w.ts;
@@ -752,20 +772,27 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
             // ================= node role: RK4 of the massive nodes =================
             if (node_lane) {
                 const double ghost_f = s_link[0][wl], bf = s_link[1][wl], ghost_b = s_link[2][wl], ab = s_link[3][wl];
+                // no-mass end nodes as solved by the face lanes (END): loaded once, placed by selects
+                double tf0 = 0., tb0 = 0., tf1 = 0., tb1 = 0.;
+                if constexpr (END) {
+                    tf0 = s_link[4][wl]; tb0 = s_link[5][wl]; tf1 = s_link[6][wl]; tb1 = s_link[7][wl];
+                }
                 if (part == 0) {
                     T[0] = ghost_f;
                     B[1] = bf;
-                    if constexpr (END)
-                        if (nmf) T[1] = s_link[4][wl];
+                    if constexpr (END) {
+                        T[1] = nmf ? tf0 : T[1];
+                        T[2] = nmf2 ? tf1 : T[2];
+                    }
                 }
 #pragma unroll
                 for (int i = 0; i < NL; ++i) {
-                    if (i == iN) {
-                        A[i] = ab;
-                        if constexpr (END)
-                            if (nmb) T[i] = s_link[5][wl];
+                    A[i] = i == iN ? ab : A[i];
+                    if constexpr (END) {
+                        T[i] = (i == iN && nmb) ? tb0 : T[i];
+                        T[i] = (i == iN - 1 && nmb2) ? tb1 : T[i];
                     }
-                    if (i == iG) T[i] = ghost_b;
+                    T[i] = i == iG ? ghost_b : T[i];
                 }
                 node_rk4<G, NL>(T, A, B);
                 publish_ends();

@@ -668,6 +668,7 @@ enum : int32_t {
     FC_OUT = 1, FC_SPACE = 2, FC_BACK = 4, FC_TILTED = 8, FC_OV = 16, FC_NM = 32,
     FC_BACK_AMB = 64,        // back face, Boundary::AmbientTemperature: built from FRONT values (surface.rs:672-685)
     FC_FRONT_OUT = 128, FC_FRONT_SPACE = 256,   // kind of the wall's front boundary (needed by FC_BACK_AMB)
+    FC_NM2 = 1024,           // FC_NM with a chunk of TWO no-mass nodes at this end (end node + its neighbour)
     FC_PANE = 512,           // face of a two-node all-no-mass wall (single glass pane): both faces solve one 2x2 system
 };
 // Constants of one face of one wall.
@@ -683,11 +684,12 @@ struct FaceC {
     double forced_c, nx, ny;
     double eps;            // emissivity of this face (front: IR net-gain conversion)
     double u_nb;           // conductance of the link between the end node and its neighbour (FC_NM)
+    double u_nb2;          // … between that neighbour and the next node (FC_NM2)
     double amb_front;      // FC_BACK_AMB: the front boundary's ambient temperature
     int32_t fl, zone, zone_front, site, desc_index, n;
 };
 HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f, bool pane = false,
-                      double alpha_own = 0., double alpha_x = 0.) {
+                      double alpha_own = 0., double alpha_x = 0., bool nm2 = false, double u_nb2 = 0.) {
     const int wf = c.fl;
     int fl = back ? FC_BACK : 0;
     if (wf & (back ? WF_B_OUT : WF_F_OUT)) fl |= FC_OUT;
@@ -699,6 +701,7 @@ HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f,
     if (wf & WF_F_SPACE) fl |= FC_FRONT_SPACE;
     if (nm) fl |= FC_NM;
     if (pane) fl |= FC_PANE;
+    if (nm && nm2) fl |= FC_NM2;
     f.fl = fl;
     f.kpos = back ? c.kpos_b : c.kpos_f;
     f.kneg = back ? c.kneg_b : c.kneg_f;
@@ -712,6 +715,7 @@ HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f,
     f.forced_c = c.forced_c; f.nx = c.nx; f.ny = c.ny;
     f.eps = c.eps_f;
     f.u_nb = u_nb;
+    f.u_nb2 = u_nb2;
     f.amb_front = c.amb_f;
     f.zone = back ? c.zb : c.zf;
     f.zone_front = c.zf;
@@ -813,20 +817,6 @@ HB_HD void face_env(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_
     const double xr = 273.15 + (e.trad + ts_env) / 2.;
     e.rad = c.eps4s * ((xr * xr) * xr);
 }
-HB_HD void face_links(const FaceC& c, FaceS& w, const FaceEnv& e, double t_nb, double& ghost, double& link) {
-    if (c.fl & FC_NM)
-        w.ts = solve_end_node(w.air, e.h, e.rad, e.trad, c.u_nb, t_nb, c.alpha_end * w.solar, w.ts, w.nm_iters,
-                              w.status);
-    const double hs = e.h > 1e-12 ? e.h : 1e-12;
-    ghost = w.air + (e.rad * (e.trad - w.ts) + c.alpha_end * w.solar) * fast_rcp(hs);
-    link = hs * c.v_end;
-}
-HB_HD void face_pre(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
-                    double t_nb, double& ghost, double& link) {
-    FaceEnv e;
-    face_env(c, w, sw, zone_t, t_front, ts_front, e);
-    face_links(c, w, e, t_nb, ghost, link);
-}
 // A single pane (two no-mass nodes, chunk (0, 2)): solve_nomass for m = 2 written out — tridiagonal elimination of
 //   [-(u+h_f)  u; u  -(u+h_b)] x = -(q + absorbed solar)  inside the damped fixed point (surface.rs:790-898).
 // sol0/sol1: absorbed solar of node 0 / node 1 (front_alpha·I_front + back_alpha·I_back, discretization.rs).
@@ -884,6 +874,36 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
         ++count;
         if (count > 100000) { status |= ST_ITER_CAP; break; }
     }
+}
+// Two no-mass nodes at an end of a wall (chunk (0,2) or (n-2,n)): the chunk's 2x2 system is solve_pane's with the
+// inner side replaced by the link to the massive neighbour (h := u2, air := T_neighbour, no radiation, no solar);
+// the chunk's first node is the end node at the front, the inner node at the back (solve_nomass's ordering).
+template <bool LEAN = false>
+HB_HD void solve_end_pair(bool back, double air, double h, double rad, double trad, double sol, double u1, double u2,
+                          double t_nb2, double& t_end, double& t_inner, unsigned long long& iters, int& status) {
+    if (back)
+        solve_pane<LEAN>(t_nb2, u2, 0., 0., 0., air, h, rad, trad, sol, u1, t_inner, t_end, iters, status);
+    else
+        solve_pane<LEAN>(air, h, rad, trad, sol, t_nb2, u2, 0., 0., 0., u1, t_end, t_inner, iters, status);
+}
+// t_nb: the end node's neighbour (FC_NM; for FC_NM2 in/out: the chunk's inner node); t_nb2: the massive node behind it.
+HB_HD void face_links(const FaceC& c, FaceS& w, const FaceEnv& e, double& t_nb, double t_nb2, double& ghost,
+                      double& link) {
+    if (c.fl & FC_NM2)
+        solve_end_pair(c.fl & FC_BACK, w.air, e.h, e.rad, e.trad, c.alpha_end * w.solar, c.u_nb, c.u_nb2, t_nb2, w.ts,
+                       t_nb, w.nm_iters, w.status);
+    else if (c.fl & FC_NM)
+        w.ts = solve_end_node(w.air, e.h, e.rad, e.trad, c.u_nb, t_nb, c.alpha_end * w.solar, w.ts, w.nm_iters,
+                              w.status);
+    const double hs = e.h > 1e-12 ? e.h : 1e-12;
+    ghost = w.air + (e.rad * (e.trad - w.ts) + c.alpha_end * w.solar) * fast_rcp(hs);
+    link = hs * c.v_end;
+}
+HB_HD void face_pre(const FaceC& c, FaceS& w, const SubWeather& sw, double zone_t, double t_front, double ts_front,
+                    double t_nb, double& ghost, double& link) {
+    FaceEnv e;
+    face_env(c, w, sw, zone_t, t_front, ts_front, e);
+    face_links(c, w, e, t_nb, 0., ghost, link);
 }
 // After the nodes marched (scalar_post for one face): new film coefficient, convective flow, energy integral and
 // this face's contribution (h·A, h·A·T_s) to calculate_zones_abc.

@@ -293,7 +293,7 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
     std::vector<char> have(W, 0);
     std::vector<ZoneC> zc(W);
     std::vector<double> zT(W, 0.), pub0(W, 0.), pub1(W, 0.), pub2(W, 0.), pub3(W, 0.);
-    std::vector<double> e0(W, 0.), e1(W, 0.), e2(W, 0.), e3(W, 0.), link(6 * W, 0.), ir_state(W, 0.);
+    std::vector<double> e0(W, 0.), e1(W, 0.), e2(W, 0.), e3(W, 0.), e4(W, 0.), e5(W, 0.), link(8 * W, 0.), ir_state(W, 0.);
     std::vector<int32_t> zf(W, -1), zb(W, -1);
     std::vector<SubWeather> swt(kMaxSubsteps);
     for (int tid = 0; tid < NT; ++tid)
@@ -308,10 +308,11 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             const int wl = tid / G, part = tid % G;
             const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
             const int iN = n - part * NL;
-            if (part == 0) { e0[wl] = T[tid * NL + 1]; e1[wl] = T[tid * NL + 2]; }
+            if (part == 0) { e0[wl] = T[tid * NL + 1]; e1[wl] = T[tid * NL + 2]; e4[wl] = T[tid * NL + 3]; }
             for (int i = 0; i < NL; ++i) {
                 if (i == iN) e3[wl] = T[tid * NL + i];
                 if (i == iN - 1) e2[wl] = T[tid * NL + i];
+                if (i == iN - 2) e5[wl] = T[tid * NL + i];
             }
         }
     };
@@ -326,8 +327,9 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             for (int k = 0; k < 2; ++k) {
                 const bool pane = (tile.flags & TILE_PANE) && ((flg >> 12) & 1);
                 const bool nm = END && !pane && ((flg >> (k ? 11 : 10)) & 1);
+                const bool nm2 = nm && ((flg >> (k ? 14 : 13)) & 1);
                 load_facec(c, k == 1, k ? V.u_b[sg] : V.u_f[sg], nm, fc[2 * t + k], pane, k ? V.abL[sg] : V.af0[sg],
-                           k ? V.ax_b[sg] : V.ax_f[sg]);
+                           k ? V.ax_b[sg] : V.ax_f[sg], nm2, k ? V.u_b2[sg] : V.u_f2[sg]);
                 FaceS w{};
                 w.h = V.sc[(0 + k) * NS + sg]; w.flow = V.sc[(2 + k) * NS + sg];
                 w.sol = V.sc[(4 + k) * NS + sg]; w.ir = V.sc[(6 + k) * NS + sg];
@@ -426,7 +428,8 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                     const FaceC& c = fc[2 * t + k];
                     FaceS& w = fs[2 * t + k];
                     double ghost, lk;
-                    face_links(c, w, env[k], t_nb[k], ghost, lk);
+                    face_links(c, w, env[k], t_nb[k], k ? e5[t] : e4[t], ghost, lk);
+                    if (c.fl & FC_NM2) link[(k ? 7 : 6) * W + t] = t_nb[k];
                     link[(k ? 2 : 0) * W + t] = ghost;
                     link[(k ? 3 : 1) * W + t] = lk;
                     link[(k ? 5 : 4) * W + t] = w.ts;
@@ -437,11 +440,13 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                 const int64_t g = (int64_t)tile.surface_begin + wl;
                 const int n = V.n_nodes[g];
                 const int nmf = END ? (V.flags[g] >> 10) & 1 : 0, nmb = END ? (V.flags[g] >> 11) & 1 : 0;
+                const int nmf2 = END ? (V.flags[g] >> 13) & 1 : 0, nmb2 = END ? (V.flags[g] >> 14) & 1 : 0;
                 double* t = &T[tid * NL];
                 if (part == 0) {
                     t[0] = link[0 * W + wl];
                     B[tid * NL + 1] = link[1 * W + wl];
                     if (nmf) t[1] = link[4 * W + wl];
+                    if (nmf2) t[2] = link[6 * W + wl];
                 }
                 for (int i = 0; i < NL; ++i) {
                     if (i == n - part * NL) {
@@ -449,6 +454,7 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                         if (nmb) t[i] = link[5 * W + wl];
                     }
                     if (i == n + 1 - part * NL) t[i] = link[2 * W + wl];
+                    if (i == n - 1 - part * NL && nmb2) t[i] = link[7 * W + wl];
                 }
             }
             auto halos = [&](const std::vector<double>& x) {

@@ -232,3 +232,28 @@ def check_two_zone_buildings(batch_cls, n=6, n_steps=6):
             nn = om.n_nodes(s)
             assert np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max() <= 1e-6, (m, s)
         off += len(so)
+
+
+def check_two_node_end_chunks(batch_cls, n_steps=48):
+    """Two thin no-mass layers at one or both ends of a wall: chunks (0,2) / (n-2,n), solved by the face lanes
+    (solve_end_pair) — such walls must not need the general kernel."""
+    import oracle_py as O
+
+    poly2 = [("polyurethane", 0.01), ("polyurethane", 0.012)]
+    stacks = [poly2 + [("concrete", 0.2)] + poly2, [("concrete", 0.15)] + poly2, poly2 + [("concrete", 0.15)],
+              [("polyurethane", 0.01), ("concrete", 0.15)] + poly2]
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    for cons in stacks:
+        d = cases.single_zone_test_building(cons, zone_volume=600.0, surface_height=3.0, surface_width=20.0,
+                                            emissivity=0.9, solar_absorbtance=0.7, steps_per_hour=4,
+                                            back_emissivity_override=0.0)
+        b = batch_cls(d)
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        got = b.get_state()
+        om = O.OracleModel(d, 0)
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        assert abs(got[0] - so[0]) <= 1e-6, cons
+        assert np.abs(got[9:] - so[9:]).max() <= 1e-6, cons
+        iters = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
+        assert iters == om.nomass_iterations, cons

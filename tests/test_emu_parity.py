@@ -104,3 +104,7 @@ def test_emulated_multi_site_walls():
 
 def test_emulated_two_zone_buildings():
     pc.check_two_zone_buildings(emu_py.EmuBatch)
+
+
+def test_emulated_two_node_end_chunks():
+    pc.check_two_node_end_chunks(emu_py.EmuBatch)

@@ -155,6 +155,12 @@ def test_two_zone_buildings_match_oracle():
     pc.check_two_zone_buildings(ThermalBatch, n=20, n_steps=12)
 
 
+def test_two_node_end_chunks_match_oracle():
+    from heat_b200.model import ThermalBatch
+
+    pc.check_two_node_end_chunks(ThermalBatch)
+
+
 def test_reduce_matches_state():
     from heat_b200 import cases
     from heat_b200.model import ThermalBatch
