@@ -516,13 +516,15 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
                 s_end[4][wl] = T[3];
             }
         }
-        // muxes evaluated by every lane (no divergent regions), predicated stores
-        const double v_last = slot(iN & (NL - 1));
-        if (has_last) *p_last = v_last;
         if constexpr (END) {
+            // three muxes evaluated by every lane (one region instead of three divergent ones), predicated stores
+            const double v_last = slot(iN & (NL - 1));
             const double v_prev = slot((iN - 1) & (NL - 1)), v_prev2 = slot((iN - 2) & (NL - 1));
+            if (has_last) *p_last = v_last;
             if (has_prev) *p_prev = v_prev;
             if (has_prev2) *p_prev2 = v_prev2;
+        } else {
+            if (has_last) *p_last = slot(iN);
         }
     };
     if (node_lane) publish_ends();
@@ -777,13 +779,15 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
                 if constexpr (END) {
                     tf0 = s_link[4][wl]; tb0 = s_link[5][wl]; tf1 = s_link[6][wl]; tb1 = s_link[7][wl];
                 }
-                if (part == 0) {
+                if constexpr (END) {
+                    const bool first = part == 0;
+                    T[0] = first ? ghost_f : T[0];
+                    B[1] = first ? bf : B[1];
+                    T[1] = (first && nmf) ? tf0 : T[1];
+                    T[2] = (first && nmf2) ? tf1 : T[2];
+                } else if (part == 0) {
                     T[0] = ghost_f;
                     B[1] = bf;
-                    if constexpr (END) {
-                        T[1] = nmf ? tf0 : T[1];
-                        T[2] = nmf2 ? tf1 : T[2];
-                    }
                 }
 #pragma unroll
                 for (int i = 0; i < NL; ++i) {
