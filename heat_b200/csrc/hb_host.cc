@@ -269,6 +269,7 @@ inline bool is_pane(const SurfacePlan& P) {
     return P.n_nodes == 2 && P.cavities.empty() && P.nomass_chunks.size() == 2 && P.nomass_chunks[0] == 0 &&
            P.nomass_chunks[1] == 2;
 }
+constexpr int kBulkSubsteps = 56;   // below: tiles are scheduled for throughput, not for latency (hb_capi.cu S bins)
 constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE;   // tiles are uniform in these
 
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
@@ -406,6 +407,9 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // tiles of the face kernel (all-massive / no-mass ends) are as small as the model allows
         const bool face = (M.variant & (TILE_EXT | TILE_DIST)) == 0;
         M.walls = face ? walls_for_model(group_of_nodes(M.nmax), M.n_surfaces, M.n_zones) : Wmax;
+        // 16 lanes per wall, few sub-steps (throughput-bound bulk): 16 walls per tile fill the face warp's 32 lanes
+        // (the same walls per SM: 2 blocks of 256 threads instead of 4 of 128); long tiles keep the short node phase
+        if (face && group_of_nodes(M.nmax) == 16 && M.dt_subdivisions < kBulkSubsteps) M.walls = std::max(M.walls, 16);
     }
     B.model_order.resize(d->n_models);
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
