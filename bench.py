@@ -262,6 +262,14 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
+        traffic, traffic_src = None, None
+        try:   # DRAM bytes per step measured once with ncu for the default workload (profiles/r1p_traffic.json)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r1p_traffic.json")))
+            if tj.get("workload") == wname and world == 1:
+                traffic = int(tj["dram_bytes_read_per_step"]) + int(tj["dram_bytes_written_per_step"])
+                traffic_src = "profiles/r1p_traffic.json (ncu dram__bytes_read+write.sum, all launches of one step)"
+        except (OSError, ValueError, KeyError):
+            pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         hbm_src = "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (B200_PROFILING.md)"
         value = total_updates / t_step
@@ -277,7 +285,8 @@ def main():
                        "l2": "flushed between timed iterations (256 MiB write)",
                        "ms_per_step_by_rank": [round(x, 2) for x in by_rank], "ensemble_stats": reduced},
             "roofline": {"bound": "fp64", "achieved": fp64_achieved, "peak": fp64_peak, "unit": "TFLOP/s",
-                         "frac": fp64_achieved / fp64_peak if fp64_peak else None, "traffic": None,
+                         "frac": fp64_achieved / fp64_peak if fp64_peak else None, "traffic": traffic,
+                         "traffic_source": traffic_src,
                          "flop_per_update": FLOP_PER_UPDATE,
                          "peak_source": "DFMA probe kernel run in this process (hb_measure_fp64_peak)"},
             "roofline_hbm": {"bound": "hbm", "achieved": alg_bytes / t_step / 1e9, "peak": hbm_peak, "unit": "GB/s",
