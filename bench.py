@@ -119,7 +119,7 @@ def cpu_reference_rate(desc, weather, inputs, n_models: int, hours: int, threads
     return updates / dt, updates, dt
 
 
-CPU_SAMPLE_SECONDS = 20.0   # CPU work per bounded sample of the workload
+CPU_SAMPLE_SECONDS = float(os.environ.get("HEAT_B200_CPU_SAMPLE_S", "20"))   # CPU work per bounded sample of the workload
 
 
 def cpu_sample_size(desc, weather, inputs, hours: int, threads: int):
