@@ -215,6 +215,15 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
     HB_CUDA(cudaEventRecord(h->fork, h->stream));
     // HB_GROUP_TIMES=1 (diagnostic): run the launch groups one after the other and print each one's duration
     static const bool group_times = std::getenv("HB_GROUP_TIMES") != nullptr;
+    // HB_GROUP_TIMELINE=1 (diagnostic): start and end of every group relative to the fork, groups left concurrent
+    // (the timing events hold the hardware queues: use it with CUDA_DEVICE_MAX_CONNECTIONS=32)
+    static const bool timeline = std::getenv("HB_GROUP_TIMELINE") != nullptr;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> tl;
+    cudaEvent_t tl0 = nullptr;
+    if (timeline) {
+        HB_CUDA(cudaEventCreate(&tl0));
+        HB_CUDA(cudaEventRecord(tl0, h->stream));
+    }
     for (auto& gp : h->groups) {
         hb_handle::Group& g = *gp;
         HB_CUDA(cudaStreamWaitEvent(g.stream, h->fork, 0));
@@ -223,6 +232,13 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             HB_CUDA(cudaEventCreate(&t0));
             HB_CUDA(cudaEventCreate(&t1));
             HB_CUDA(cudaEventRecord(t0, g.stream));
+        }
+        if (timeline) {
+            cudaEvent_t a, b;
+            HB_CUDA(cudaEventCreate(&a));
+            HB_CUDA(cudaEventCreate(&b));
+            HB_CUDA(cudaEventRecord(a, g.stream));
+            tl.emplace_back(a, b);
         }
         cudaError_t e;
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
@@ -246,8 +262,23 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             cudaEventDestroy(t0);
             cudaEventDestroy(t1);
         }
+        if (timeline) HB_CUDA(cudaEventRecord(tl.back().second, g.stream));
         HB_CUDA(cudaEventRecord(g.done, g.stream));
         HB_CUDA(cudaStreamWaitEvent(h->stream, g.done, 0));
+    }
+    if (timeline) {
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        for (size_t i = 0; i < tl.size(); ++i) {
+            const hb_handle::Group& g = *h->groups[i];
+            float a = 0.f, b = 0.f;
+            cudaEventElapsedTime(&a, tl0, tl[i].first);
+            cudaEventElapsedTime(&b, tl0, tl[i].second);
+            std::fprintf(stderr, "[hb tl] G=%d W=%d var=%d tiles=%d smax=%d: %.2f -> %.2f ms\n", g.G, g.W, g.var, g.n_tiles,
+                         g.s_max, a, b);
+            cudaEventDestroy(tl[i].first);
+            cudaEventDestroy(tl[i].second);
+        }
+        cudaEventDestroy(tl0);
     }
 }
 
