@@ -76,6 +76,7 @@ struct hb_handle {
     // one launch per (lanes-per-wall, kernel variant); each on its own stream so that small groups overlap
     struct Group {
         int G, W, var;
+        int NL = hb::kNL;   // slots per lane of the group's tiles
         int n_tiles;
         int s_max = 1;   // most sub-steps of a tile of the group
         DevBuf<int32_t> ids;   // tile ids, heaviest first
@@ -163,13 +164,13 @@ void build_device(hb_handle* h) {
     // longest tile: tiles are binned by S and the bins with the most sub-steps are launched first, on streams of
     // higher priority, so that across ALL groups the long tiles start at once and the short ones fill in behind.
     auto s_class = [](int S) { return S >= 96 ? 0 : S >= 56 ? 1 : S >= 32 ? 2 : S >= 16 ? 3 : 4; };
-    std::map<std::tuple<int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -G, variant, W)
+    std::map<std::tuple<int, int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -NL, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
         const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5
                         : (t.flags & hb::TILE_END) ? ((t.flags & hb::TILE_SIMPLE) ? 7 : 3) : ((t.flags & hb::TILE_SIMPLE) ? 6 : 0);
         // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
-        by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.G, var, t.W}].push_back((int32_t)ti);
+        by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.NL, -t.G, var, t.W}].push_back((int32_t)ti);
     }
     int prio_lo = 0, prio_hi = 0;   // numerically lower = higher priority
     HB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
@@ -177,9 +178,10 @@ void build_device(hb_handle* h) {
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
         const int cls = std::get<0>(kv.first);
-        grp->G = -std::get<2>(kv.first);
-        grp->var = std::get<3>(kv.first);
-        grp->W = std::get<4>(kv.first);
+        grp->NL = -std::get<2>(kv.first);
+        grp->G = -std::get<3>(kv.first);
+        grp->var = std::get<4>(kv.first);
+        grp->W = std::get<5>(kv.first);
         std::stable_sort(kv.second.begin(), kv.second.end(),
                          [&](int32_t a, int32_t b) { return B.tiles[a].S > B.tiles[b].S; });
         grp->n_tiles = (int)kv.second.size();
@@ -197,7 +199,7 @@ void build_device(hb_handle* h) {
 namespace hb {
 // one translation unit per lanes-per-wall tier (hb_march_tier.cu compiled with -DHB_TIER=G) so they build in parallel
 #define HB_DECL_TIER(N) \
-    cudaError_t launch_march_##N(int var, int W, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+    cudaError_t launch_march_##N(int var, int W, int nl, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
 HB_DECL_TIER(1) HB_DECL_TIER(2) HB_DECL_TIER(4) HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(32)
 #undef HB_DECL_TIER
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
@@ -244,12 +246,12 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
         const int var = (g.var == 0 || g.var == 3 || g.var >= 5) && !P.single_site ? 4 : g.var;
         switch (g.G) {
-            case 1: e = hb::launch_march_1(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 2: e = hb::launch_march_2(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 4: e = hb::launch_march_4(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 8: e = hb::launch_march_8(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 16: e = hb::launch_march_16(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            default: e = hb::launch_march_32(var, g.W, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 1: e = hb::launch_march_1(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 2: e = hb::launch_march_2(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 4: e = hb::launch_march_4(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 8: e = hb::launch_march_8(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 16: e = hb::launch_march_16(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            default: e = hb::launch_march_32(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
         }
         HB_CUDA(e);
         h->launches += 1;
@@ -258,7 +260,7 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             HB_CUDA(cudaEventSynchronize(t1));
             float ms = 0.f;
             HB_CUDA(cudaEventElapsedTime(&ms, t0, t1));
-            std::fprintf(stderr, "[hb] group G=%d W=%d var=%d tiles=%d: %.3f ms\n", g.G, g.W, g.var, g.n_tiles, ms);
+            std::fprintf(stderr, "[hb] group G=%d NL=%d W=%d var=%d tiles=%d: %.3f ms\n", g.G, g.NL, g.W, g.var, g.n_tiles, ms);
             cudaEventDestroy(t0);
             cudaEventDestroy(t1);
         }
@@ -273,8 +275,8 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             float a = 0.f, b = 0.f;
             cudaEventElapsedTime(&a, tl0, tl[i].first);
             cudaEventElapsedTime(&b, tl0, tl[i].second);
-            std::fprintf(stderr, "[hb tl] G=%d W=%d var=%d tiles=%d smax=%d: %.2f -> %.2f ms\n", g.G, g.W, g.var, g.n_tiles,
-                         g.s_max, a, b);
+            std::fprintf(stderr, "[hb tl] G=%d NL=%d W=%d var=%d tiles=%d smax=%d: %.2f -> %.2f ms\n", g.G, g.NL, g.W, g.var,
+                         g.n_tiles, g.s_max, a, b);
             cudaEventDestroy(tl[i].first);
             cudaEventDestroy(tl[i].second);
         }

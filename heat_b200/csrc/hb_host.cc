@@ -351,7 +351,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     // runs one loop shape; models are sorted by (G, variant, S) and packed greedily.
     for (int m = 0; m < d->n_models; ++m) {
         ModelPlan& M = B.models[m];
-        if (M.nmax > kMaxNodes) fail("surface has more nodes than the supported maximum (254)");
+        if (M.nmax > kMaxNodesBig) fail("surface has more nodes than the supported maximum (1022)");
         M.variant = 0;
         // `rest`: variant of the model without its single panes; a model whose other walls suit the face kernel keeps
         // its panes there too (both faces of a wall in one warp: tiles of at most 16 walls, >= 2 lanes per wall)
@@ -407,6 +407,10 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // tiles of the face kernel (all-massive / no-mass ends) are as small as the model allows
         const bool face = (M.variant & (TILE_EXT | TILE_DIST)) == 0;
         M.walls = face ? walls_for_model(group_of_nodes(M.nmax), M.n_surfaces, M.n_zones) : Wmax;
+        M.NL = slots_of_nodes(M.nmax);
+        if (!face && M.NL != kNL)
+            fail("surface with no-mass layers between massive ones, cavities or inner solar absorption has more nodes "
+                 "than the supported maximum (254)");
         // 16 lanes per wall, few sub-steps (throughput-bound bulk): 16 walls per tile fill the face warp's 32 lanes
         // (the same walls per SM: 2 blocks of 256 threads instead of 4 of 128); long tiles keep the short node phase
         if (face && group_of_nodes(M.nmax) == 16 && M.dt_subdivisions < kBulkSubsteps) M.walls = std::max(M.walls, 16);
@@ -415,7 +419,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
     auto key = [&](int m) {
         const ModelPlan& M = B.models[m];
-        return std::make_tuple(group_of_nodes(M.nmax), M.variant & kTileKey, M.walls, M.dt_subdivisions);
+        return std::make_tuple(group_of_nodes(M.nmax), M.NL, M.variant & kTileKey, M.walls, M.dt_subdivisions);
     };
     if (d->n_models > 1)
         std::stable_sort(B.model_order.begin(), B.model_order.end(), [&](int a, int b) { return key(a) < key(b); });
@@ -432,7 +436,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     auto close_tile = [&]() {
         if (!open) return;
         cur.node_offset = node_off;
-        node_off += (int64_t)kNL * cur.G * cur.W;
+        node_off += (int64_t)cur.NL * cur.G * cur.W;
         cur.ext_offset = -1;
         if (cur.flags & TILE_EXT) {
             cur.ext_offset = ext_off;
@@ -449,7 +453,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         const int G = group_of_nodes(M.nmax);
         const int W = M.walls;
         const int variant = M.variant & kTileKey;
-        if (open && (cur.G != G || cur.W != W || (cur.flags & kTileKey) != variant || cur.S != M.dt_subdivisions ||
+        if (open && (cur.G != G || cur.NL != M.NL || cur.W != W || (cur.flags & kTileKey) != variant || cur.S != M.dt_subdivisions ||
                      cur.n_surfaces + M.n_surfaces > W || cur.n_zones + M.n_zones > W))
             close_tile();
         if (!open) {
@@ -457,6 +461,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             cur.surface_begin = surf_slots;
             cur.zone_begin = zone_slots;
             cur.G = G;
+            cur.NL = M.NL;
             cur.W = W;
             cur.S = M.dt_subdivisions;
             cur.dt = M.dt;

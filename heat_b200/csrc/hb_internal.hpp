@@ -16,7 +16,11 @@ namespace hb {
 // warp evaluates the per-wall scalar physics (film coefficients, no-mass chunks, zone update) of wall j.
 constexpr int kNL = 8;               // slots per lane
 constexpr int kMaxG = 32;            // lanes per wall: 1, 2, 4, 8, 16, 32
-constexpr int kMaxNodes = kMaxG * kNL - 2;  // 254
+constexpr int kMaxNodes = kMaxG * kNL - 2;  // 254: the largest wall of the regular tiers
+// Walls beyond 254 nodes (thick, low-diffusivity layers under a short sub-step another surface of the model imposes)
+// keep 32 lanes and take 16 or 32 slots per lane (hb_face_kernel only; spills to local memory, rare by construction).
+constexpr int kNLBig = 16, kNLHuge = 32;
+constexpr int kMaxNodesBig = kMaxG * kNLHuge - 2;  // 1022
 constexpr int kMaxWalls = 32;        // walls (and zones) per tile; == warp size (scalar role)
 constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
 constexpr int kMaxSubsteps = 128;    // shared weather table rows (S <= 120 for n >= 1 step/hour)
@@ -35,8 +39,11 @@ inline int walls_for_model(int G, int n_surfaces, int n_zones) {
 }
 inline int group_of_nodes(int n) {
     int G = 1;
-    while (G * kNL < n + 2) G *= 2;
+    while (G < kMaxG && G * kNL < n + 2) G *= 2;
     return G;
+}
+inline int slots_of_nodes(int n) {   // slots per lane of the tier that holds a wall of n nodes
+    return n + 2 <= kMaxG * kNL ? kNL : n + 2 <= kMaxG * kNLBig ? kNLBig : kNLHuge;
 }
 
 // Constants of the reference (kept in one place; cited where used)
@@ -83,6 +90,7 @@ struct ModelPlan {
     int32_t nmax = 0;
     int32_t variant = 0;             // TILE_* flags needed by its surfaces
     int32_t walls = 0;               // wall slots of the tiles this model goes into
+    int32_t NL = kNL;                // slots per lane of those tiles
 };
 
 enum : int32_t {
@@ -106,8 +114,8 @@ struct Tile {
     int32_t G;               // lanes per wall
     int32_t W;               // wall slots
     int32_t flags;           // TILE_*
-    int32_t pad_;
-    int64_t node_offset;     // offset (doubles) of the tile's [kNL][G*W] slabs (node T, coefficient A, coefficient B)
+    int32_t NL;              // slots per lane (kNL; kNLBig / kNLHuge for walls beyond kMaxNodes)
+    int64_t node_offset;     // offset (doubles) of the tile's [NL][G*W] slabs (node T, coefficient A, coefficient B)
     int64_t ext_offset;      // offset (doubles) of the tile's [nmax][W] wall-major arrays (TILE_EXT only, else -1)
     double dt;               // sub-step length [s] (uniform over the tile)
 };
@@ -144,7 +152,7 @@ struct BatchPlan {
         const Tile& t = tiles[surface_tile[gd]];
         const int wl = dev_surface_of[gd] - t.surface_begin;
         const int slot = node + 1;
-        return t.node_offset + (int64_t)(slot % kNL) * (t.G * t.W) + (int64_t)wl * t.G + slot / kNL;
+        return t.node_offset + (int64_t)(slot % t.NL) * (t.G * t.W) + (int64_t)wl * t.G + slot / t.NL;
     }
 };
 

@@ -442,15 +442,16 @@ __device__ __forceinline__ void node_rk4(double (&T)[NL], const double (&A)[NL],
 #ifndef HB_FACE_OCC
 #define HB_FACE_OCC 512   // resident threads per SM the face kernel is compiled for (512: 128 registers per thread)
 #endif
-template <int G, int W, int MODE, bool SIMPLE>
-__global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads(G, W))
+// NL: slots per lane — kNL for the regular tiers; kNLBig / kNLHuge (G = 32 only, one block per SM) for walls beyond 254 nodes
+template <int G, int W, int MODE, bool SIMPLE, int NL = kNL>
+__global__ void __launch_bounds__(face_threads(G, W), NL == kNL ? HB_FACE_OCC / face_threads(G, W) : 1)
     hb_face_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     constexpr bool END = MODE != kFaceLean;    // single-node no-mass chunks at the ends of walls are possible
     constexpr bool LEAN = MODE != kFaceGen;    // one weather table per tile, no film override, no AmbientTemperature back
     extern __shared__ double s_dyn[];
     constexpr int NT = G * W;                   // node lanes (the tile's slab stride)
     constexpr int TPB = face_threads(G, W);     // a tile of 32 node lanes gets a second warp for the back faces
-    constexpr int NL = kNL;
+    static_assert(NL == kNL || (G == kMaxG && (NL == kNLBig || NL == kNLHuge)), "slots per lane");
     constexpr int NWARP = TPB / 32;
     constexpr bool ONE = 2 * W <= 32;           // front faces on lanes [0, W), back faces on lanes [W, 2W) of ONE warp
     constexpr bool PANE = ONE && (MODE == kFaceGen || MODE == kFacePane);   // panes: both faces in one warp
@@ -495,14 +496,19 @@ __global__ void __launch_bounds__(face_threads(G, W), HB_FACE_OCC / face_threads
 #pragma unroll
         for (int i = 0; i < NL; ++i) T[i] = A[i] = B[i] = 0.;
     }
-    // value of the lane-local slot k (0 <= k < NL) as a 3-level mux: no divergent branches
+    // value of the lane-local slot k (0 <= k < NL) as a log2(NL)-level mux: no divergent branches
     auto slot = [&](int k) {
-        const double a0 = (k & 1) ? T[1] : T[0], a1 = (k & 1) ? T[3] : T[2], a2 = (k & 1) ? T[5] : T[4],
-                     a3 = (k & 1) ? T[7] : T[6];
-        const double b0 = (k & 2) ? a1 : a0, b1 = (k & 2) ? a3 : a2;
-        return (k & 4) ? b1 : b0;
+        double m[NL / 2];
+#pragma unroll
+        for (int i = 0; i < NL / 2; ++i) m[i] = (k & 1) ? T[2 * i + 1] : T[2 * i];
+#pragma unroll
+        for (int len = NL / 4, b = 2; len >= 1; len >>= 1, b <<= 1) {
+#pragma unroll
+            for (int i = 0; i < len; ++i) m[i] = (k & b) ? m[2 * i + 1] : m[2 * i];
+        }
+        return m[0];
     };
-    static_assert(NL == 8, "slot() is an 8-way mux");
+    static_assert((NL & (NL - 1)) == 0 && NL >= 8, "slot() is a power-of-two mux");
     const bool has_last = iN >= 0 && iN < NL, has_prev = END && iN - 1 >= 0 && iN - 1 < NL;
     const bool has_prev2 = END && iN - 2 >= 0 && iN - 2 < NL;
     double* const p_prev2 = &s_end[5][wl];
@@ -1004,8 +1010,8 @@ __global__ void __launch_bounds__(kReduceBlock) hb_reduce_kernel(DevView V, int 
         for (int th = t; th < TPB; th += kReduceBlock) {
             const int wl = th / tile.G, part = th % tile.G;
             const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
-            for (int i = 0; i < kNL; ++i) {
-                const int slot = part * kNL + i;
+            for (int i = 0; i < tile.NL; ++i) {
+                const int slot = part * tile.NL + i;
                 if (slot >= 1 && slot <= n) {
                     const double v = V.nodeT[tile.node_offset + (int64_t)i * TPB + th];
                     sn += v;

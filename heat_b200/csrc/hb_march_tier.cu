@@ -23,7 +23,7 @@ cudaError_t launch_variant(int n_tiles, cudaStream_t st, const DevView& V, const
     hb_march_kernel<G, W, VAR><<<n_tiles, G * W, dyn, st>>>(V, P, ids);
     return cudaGetLastError();
 }
-template <int G, int W, int END, bool SIMPLE>
+template <int G, int W, int END, bool SIMPLE, int NL = kNL>
 cudaError_t launch_face(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P,
                         const int32_t* ids) {
     const size_t dyn = (size_t)2 * s_max * sizeof(SubWeather);   // <= 8 KB: no opt-in needed
@@ -31,7 +31,7 @@ cudaError_t launch_face(int n_tiles, int s_max, cudaStream_t st, const DevView& 
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     cudaMemcpyToSymbol(hb_phase_clk, z, sizeof(z));
 #endif
-    hb_face_kernel<G, W, END, SIMPLE><<<n_tiles, face_threads(G, W), dyn, st>>>(V, P, ids);
+    hb_face_kernel<G, W, END, SIMPLE, NL><<<n_tiles, face_threads(G, W), dyn, st>>>(V, P, ids);
 #ifdef HB_PHASE_CLOCKS
     cudaStreamSynchronize(st);
     cudaMemcpyFromSymbol(o, hb_phase_clk, sizeof(o));
@@ -44,28 +44,35 @@ cudaError_t launch_face(int n_tiles, int s_max, cudaStream_t st, const DevView& 
 }
 
 template <int G, int END, bool SIMPLE>
-cudaError_t launch_face_w(int W, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P,
+cudaError_t launch_face_w(int W, int nl, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P,
                           const int32_t* ids) {
     constexpr int W0 = pref_walls_of_group(G), W1 = walls_of_group(G);
     static_assert(W1 == W0 || W1 == 2 * W0, "two tile widths per tier");
+    if constexpr (G == kMaxG) {   // walls beyond 254 nodes: 16 or 32 slots per lane
+        if (nl == kNLBig && W == W0) return launch_face<G, W0, END, SIMPLE, kNLBig>(n_tiles, s_max, st, V, P, ids);
+        if (nl == kNLBig && W == W1) return launch_face<G, W1, END, SIMPLE, kNLBig>(n_tiles, s_max, st, V, P, ids);
+        if (nl == kNLHuge && W == W0) return launch_face<G, W0, END, SIMPLE, kNLHuge>(n_tiles, s_max, st, V, P, ids);
+        if (nl == kNLHuge && W == W1) return launch_face<G, W1, END, SIMPLE, kNLHuge>(n_tiles, s_max, st, V, P, ids);
+    }
+    if (nl != kNL) return cudaErrorInvalidValue;
     if (W == W0) return launch_face<G, W0, END, SIMPLE>(n_tiles, s_max, st, V, P, ids);
     if (W == W1) return launch_face<G, W1, END, SIMPLE>(n_tiles, s_max, st, V, P, ids);
     return cudaErrorInvalidValue;
 }
 }  // namespace
 
-cudaError_t HB_CAT(launch_march_, HB_TIER)(int var, int W, int n_tiles, int s_max, cudaStream_t st,
+cudaError_t HB_CAT(launch_march_, HB_TIER)(int var, int W, int nl, int n_tiles, int s_max, cudaStream_t st,
                                            const DevView& V, const SeriesDev& P, const int32_t* ids) {
     constexpr int G = HB_TIER, WL = walls_of_group(HB_TIER);
     switch (var) {
-        case kVarPlain: return launch_face_w<G, kFaceLean, false>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarEnd: return launch_face_w<G, kFaceLeanEnd, false>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarGen: return launch_face_w<G, kFaceGen, false>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarPane: return launch_face_w<G, kFacePane, false>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarPlainSimple: return launch_face_w<G, kFaceLean, true>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarEndSimple: return launch_face_w<G, kFaceLeanEnd, true>(W, n_tiles, s_max, st, V, P, ids);
-        case kVarExt: return W == WL ? launch_variant<G, WL, kVarExt>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
-        default: return W == WL ? launch_variant<G, WL, kVarDist>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
+        case kVarPlain: return launch_face_w<G, kFaceLean, false>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarEnd: return launch_face_w<G, kFaceLeanEnd, false>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarGen: return launch_face_w<G, kFaceGen, false>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarPane: return launch_face_w<G, kFacePane, false>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarPlainSimple: return launch_face_w<G, kFaceLean, true>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarEndSimple: return launch_face_w<G, kFaceLeanEnd, true>(W, nl, n_tiles, s_max, st, V, P, ids);
+        case kVarExt: return W == WL && nl == kNL ? launch_variant<G, WL, kVarExt>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
+        default: return W == WL && nl == kNL ? launch_variant<G, WL, kVarDist>(n_tiles, st, V, P, ids) : cudaErrorInvalidValue;
     }
 }
 }  // namespace hb

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "hb_math.cuh"
@@ -282,7 +283,7 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
 
 // hb_face_kernel's data flow (all-massive tiles and tiles whose no-mass chunks are single end nodes): per-face lanes.
 void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, double* zone_rec_base) {
-    const int G = tile.G, W = tile.W, NT = G * W, NL = kNL;
+    const int G = tile.G, W = tile.W, NT = G * W, NL = tile.NL;
     const bool END = tile.flags & TILE_END;
     const int S = tile.S;
     const double dt = tile.dt;
@@ -464,19 +465,25 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                     right[tid] = part < G - 1 ? x[(tid + 1) * NL] : x[tid * NL];
                 }
             };
-            using Arr = double(&)[kNL];
-            halos(T);
-            for (int tid = 0; tid < NT; ++tid) {
-                sweep_first<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid], right[tid]);
-                for (int i = 0; i < NL; ++i) T[tid * NL + i] += Vv[tid * NL + i];
-            }
-            const double cs[3] = {1. / 2., 1. / 6., 1. / 24.};
-            for (int k = 0; k < 3; ++k) {
-                halos(Vv);
-                for (int tid = 0; tid < NT; ++tid)
-                    sweep_next<kNL>((Arr)T[tid * NL], (Arr)Vv[tid * NL], (Arr)A[tid * NL], (Arr)B[tid * NL], left[tid],
-                                    right[tid], cs[k]);
-            }
+            auto sweeps = [&](auto nl) {   // the four RK4 sweeps for lanes of nl slots
+                constexpr int N = decltype(nl)::value;
+                using Arr = double(&)[N];
+                halos(T);
+                for (int tid = 0; tid < NT; ++tid) {
+                    sweep_first<N>((Arr)T[tid * N], (Arr)Vv[tid * N], (Arr)A[tid * N], (Arr)B[tid * N], left[tid], right[tid]);
+                    for (int i = 0; i < N; ++i) T[tid * N + i] += Vv[tid * N + i];
+                }
+                const double cs[3] = {1. / 2., 1. / 6., 1. / 24.};
+                for (int k = 0; k < 3; ++k) {
+                    halos(Vv);
+                    for (int tid = 0; tid < NT; ++tid)
+                        sweep_next<N>((Arr)T[tid * N], (Arr)Vv[tid * N], (Arr)A[tid * N], (Arr)B[tid * N], left[tid],
+                                      right[tid], cs[k]);
+                }
+            };
+            if (NL == kNL) sweeps(std::integral_constant<int, kNL>{});
+            else if (NL == kNLBig) sweeps(std::integral_constant<int, kNLBig>{});
+            else sweeps(std::integral_constant<int, kNLHuge>{});
             publish_ends();
             for (int t = 0; t < W; ++t) {
                 if (!have[t]) continue;

@@ -257,3 +257,57 @@ def check_two_node_end_chunks(batch_cls, n_steps=48):
         assert np.abs(got[9:] - so[9:]).max() <= 1e-6, cons
         iters = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
         assert iters == om.nomass_iterations, cons
+
+
+def _dense_layer(th, eps=0.9, alpha=0.7):
+    """Low-diffusivity solid (k = 0.05, rho = 2500, cp = 2000): ~1200 nodes per metre under a 30 s sub-step."""
+    return D.solid_layer(th, conductivity=0.05, density=2500.0, specific_heat=2000.0, front_emissivity=eps,
+                         back_emissivity=eps, front_solar_abs=alpha, back_solar_abs=alpha)
+
+
+def check_walls_beyond_254_nodes(batch_cls, n_steps=3):
+    """Walls of more than 254 nodes (32 lanes x 8 slots): the 16- and 32-slot tiers of the face kernel.  Hourly steps;
+    a thin polyurethane skin (or the building's pane) imposes the 30.5 s sub-step under which the dense layers
+    discretize finely (discretization.rs:410-544).  (a) single walls with their own zone, (b) a shoebox with a pane."""
+    import oracle_py as O
+
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    normal = (0.0, -1.0, 0.0)
+    seen = []
+    for th in (0.40, 0.70):
+        layers = [cases.polyurethane(0.02, 0.9, 0.7), _dense_layer(th), cases.polyurethane(0.02, 0.9, 0.7)]
+        surf = [D.surface(0, 60.0, 46.0, normal, 1.5, front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0))]
+        d = D.single_model([layers], [600.0], surf, 1)
+        b = batch_cls(d)
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        got = b.get_state()
+        om = O.OracleModel(d, 0)
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        nn = om.n_nodes(0)
+        seen.append(nn)
+        assert len(got) == len(so)
+        assert np.abs(got - so).max() <= 1e-6, (th, nn, np.abs(got - so).max())
+    assert 254 < seen[0] <= 510 < seen[1] <= 1022, seen
+
+    # (b) two shoeboxes; the first one's opaque construction (two layers) becomes a polyurethane skin on a dense layer
+    d, gains = cases.shoebox_ensemble(2, seed=43)
+    lo = int(d.construction_offset[0])
+    assert int(d.construction_offset[1]) - lo == 2
+    d.layers[lo] = cases.polyurethane(0.02, 0.8, 0.5)
+    d.layers[lo + 1] = _dense_layer(0.36, 0.8, 0.5)
+    b = batch_cls(d)
+    b.set_zone_inputs(q_internal=gains)
+    b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+    got = b.get_state()
+    off = 0
+    big = 0
+    for m in range(d.n_models):
+        om = O.OracleModel(d, m)
+        om.set_zone_inputs(q_internal=gains[m:m + 1])
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        big = max(big, max(om.n_nodes(s) for s in range(om.n_surfaces)))
+        assert np.abs(got[off:off + len(so)] - so).max() <= 1e-6, (m, np.abs(got[off:off + len(so)] - so).max())
+        off += len(so)
+    assert big > 254, big

@@ -108,3 +108,7 @@ def test_emulated_two_zone_buildings():
 
 def test_emulated_two_node_end_chunks():
     pc.check_two_node_end_chunks(emu_py.EmuBatch)
+
+
+def test_emulated_walls_beyond_254_nodes():
+    pc.check_walls_beyond_254_nodes(emu_py.EmuBatch)

@@ -161,6 +161,12 @@ def test_two_node_end_chunks_match_oracle():
     pc.check_two_node_end_chunks(ThermalBatch)
 
 
+def test_walls_beyond_254_nodes_match_oracle():
+    from heat_b200.model import ThermalBatch
+
+    pc.check_walls_beyond_254_nodes(ThermalBatch, n_steps=6)
+
+
 def test_reduce_matches_state():
     from heat_b200 import cases
     from heat_b200.model import ThermalBatch
