@@ -226,9 +226,12 @@ def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layer
     return D.BatchDesc(layers, off.astype(np.int32), ar, ar, volume, surfaces, steps_per_hour)
 
 
-def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 1):
+def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 1, glazing=None):
     """`n_buildings` single-zone shoeboxes: 4 walls + roof (Outdoor ↔ Space), floor (AmbientTemperature front) and one
-    single-layer window, parametric sweep. Returns (BatchDesc, q_internal[n_buildings])."""
+    single-layer window, parametric sweep. Returns (BatchDesc, q_internal[n_buildings]).
+
+    `glazing`: list of layers of the window construction shared by all buildings (default: one 6 mm pane); e.g.
+    `double_glazing()` — panes + gas cavity, ISO 9050 optics (glazing.rs:180-286) and Cavity::u_value (cavity.rs:59-69)."""
     rng = SplitMix64(seed)
     n = n_buildings
     # one opaque construction per building (1-3 layers) + one glazing construction shared by all
@@ -236,13 +239,14 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     off = np.zeros(n + 2, np.int64)
     np.cumsum(n_lay, out=off[1:n + 1])
     total = int(off[n])
-    off[n + 1] = total + 1
+    glazing = [glass(0.006, 0.6, 0.84, 0.2)] if glazing is None else list(glazing)
+    off[n + 1] = total + len(glazing)
     k, rho, cp, th = _random_layers(rng, total)
     eps = rng.uniform(n, 0.7, 0.95)
     alpha = rng.uniform(n, 0.2, 0.9)
     volume = rng.uniform(n, 50.0, 600.0)
     gains = rng.uniform(n, 0.0, 500.0)
-    layers = np.zeros(total + 1, D.LAYER_DTYPE)
+    layers = np.zeros(total + len(glazing), D.LAYER_DTYPE)
     layers["kind"] = D.LAYER_SOLID
     layers["thickness"][:total], layers["conductivity"][:total] = th, k
     layers["density"][:total], layers["specific_heat"][:total] = rho, cp
@@ -250,7 +254,8 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     for f, v in (("front_emissivity", eps), ("back_emissivity", eps), ("front_solar_abs", alpha), ("back_solar_abs", alpha)):
         layers[f][:total] = v[b_of_layer]
     layers["solar_transmittance"] = D.NAN
-    layers[total] = glass(0.006, 0.6, 0.84, 0.2)
+    for i, g in enumerate(glazing):
+        layers[total + i] = g
 
     height = 3.0
     side = np.sqrt(volume / height)
@@ -286,6 +291,11 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     return D.BatchDesc(layers, off.astype(np.int32), zo, so, volume, surfaces.reshape(-1), steps_per_hour), gains
 
 
+def double_glazing(gas=D.GAS_ARGON, gap=0.012):
+    """6 mm pane | gas cavity | 4 mm low-absorption pane (the pattern of tests/test_host_planning.py)."""
+    return [glass(0.006, 0.7, 0.84, 0.1), D.gas_layer(gap, gas), glass(0.004, 0.8, 0.84, 0.05)]
+
+
 def two_zone_ensemble(n_buildings: int, seed: int = 44, *, steps_per_hour: int = 2):
     """`n_buildings` two-zone buildings: zones 0 and 1 with four outdoor walls each and one partition whose front face
     looks at zone 0 and whose back face looks at zone 1 (a surface between two spaces, model.rs:79-96), plus a
@@ -296,9 +306,10 @@ def two_zone_ensemble(n_buildings: int, seed: int = 44, *, steps_per_hour: int =
     off = np.zeros(n + 2, np.int64)
     np.cumsum(n_lay, out=off[1:n + 1])
     total = int(off[n])
-    off[n + 1] = total + 1
+    glazing = [glass(0.006, 0.6, 0.84, 0.2)] if glazing is None else list(glazing)
+    off[n + 1] = total + len(glazing)
     k, rho, cp, th = _random_layers(rng, total)
-    layers = np.zeros(total + 1, D.LAYER_DTYPE)
+    layers = np.zeros(total + len(glazing), D.LAYER_DTYPE)
     layers["kind"] = D.LAYER_SOLID
     layers["thickness"][:total], layers["conductivity"][:total] = th, k
     layers["density"][:total], layers["specific_heat"][:total] = rho, cp

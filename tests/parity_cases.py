@@ -182,6 +182,40 @@ def check_general_mode_buildings(batch_cls, n=8):
         off += len(so)
 
 
+def check_double_glazed_buildings(batch_cls, n=6, n_steps=6):
+    """Shoeboxes whose window is pane | gas | pane: ISO 9050 absorptances per pane (glazing.rs:180-286), the cavity's
+    temperature-dependent U (cavity.rs:59-69, gas.rs:82-315) and the no-mass solve of a 4-node window, next to the zone
+    coupling.  One ensemble per gas / gap so that both Nusselt regimes of a vertical cavity are met."""
+    import oracle_py as O
+
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    worst = 0.0
+    for gas, gap in ((D.GAS_ARGON, 0.012), (D.GAS_AIR, 0.03)):
+        d, gains = cases.shoebox_ensemble(n, seed=17, steps_per_hour=2, glazing=cases.double_glazing(gas, gap))
+        b = batch_cls(d)
+        b.set_zone_inputs(q_internal=gains)
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        got = b.get_state()
+        off = 0
+        for m in range(d.n_models):
+            om = O.OracleModel(d, m)
+            om.set_zone_inputs(q_internal=gains[m:m + 1])
+            so = om.initial_state()
+            om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+            mine = got[off:off + len(so)]
+            assert om.n_nodes(6) == 4, om.n_nodes(6)
+            assert abs(mine[0] - so[0]) <= 1e-6, (gas, m, mine[0], so[0])
+            for s in range(7):
+                o = om.state_offset(s)
+                nn = om.n_nodes(s)
+                err = np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max()
+                worst = max(worst, err)
+                assert err <= 1e-6, (gas, m, s, err)
+            off += len(so)
+        assert off == len(got)
+    return worst
+
+
 def check_multi_site_walls(batch_cls, n=48):
     """Walls (massive and with no-mass layers) under per-model weather sites: general face mode / general kernel."""
     import oracle_py as O

@@ -98,6 +98,10 @@ def test_emulated_general_face_mode_buildings():
     pc.check_general_mode_buildings(emu_py.EmuBatch)
 
 
+def test_emulated_double_glazed_buildings():
+    pc.check_double_glazed_buildings(emu_py.EmuBatch)
+
+
 def test_emulated_multi_site_walls():
     pc.check_multi_site_walls(emu_py.EmuBatch)
 

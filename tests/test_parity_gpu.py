@@ -143,6 +143,13 @@ def test_general_face_mode_buildings_match_oracle():
     pc.check_general_mode_buildings(ThermalBatch, n=20)
 
 
+def test_double_glazed_buildings_match_oracle():
+    """pane | gas | pane windows in shoeboxes: multi-pane optics + cavity U-value + zone coupling."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_double_glazed_buildings(ThermalBatch, n=24, n_steps=12)
+
+
 def test_multi_site_walls_match_oracle():
     from heat_b200.model import ThermalBatch
 
