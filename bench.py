@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — wall node-substep updates/s of the wall-conduction time-stepping path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload walls|buildings|mixed]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload walls|buildings|mixed|buildings2g]
 
 A "step" is one pass of the hot path over one batch of synthetic input: the whole ensemble marched over the whole
 horizon (default: BASELINE.json configs[2] — 10^5 independent massive walls with randomised layer stacks, each with
@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="walls", choices=["walls", "buildings", "mixed"])
+    ap.add_argument("--workload", default="walls", choices=["walls", "buildings", "mixed", "buildings2g"])
     ap.add_argument("--units", type=int, default=0, help="walls / buildings per GPU (0 = the config's size)")
     ap.add_argument("--hours", type=int, default=8760, help="main steps per bench step (n = 1/h)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -57,6 +57,10 @@ def make_workload(kind: str, units: int, rank: int):
         n = units or 1_250_000
         return (cases.wall_ensemble(n, seed=44 + 1000 * rank, mixed_fraction=0.5), None,
                 f"{n} walls 50% massive / 50% poly-X-poly (configs[4] shard), seed 44")
+    if kind == "buildings2g":  # probe: configs[3] topology with pane | argon | pane windows (general kernel)
+        n = units or 20_000
+        d, gains = cases.shoebox_ensemble(n, seed=43 + 1000 * rank, glazing=cases.double_glazing())
+        return d, gains, f"{n} shoebox buildings, 6 surfaces + double-glazed window (probe), seed 43"
     n = units or 125_000      # configs[3] per-GPU shard of 10^6 buildings / 8
     d, gains = cases.shoebox_ensemble(n, seed=43 + 1000 * rank)
     return d, gains, f"{n} shoebox buildings, 6 surfaces + window (configs[3] shard), seed 43"

@@ -54,7 +54,7 @@ class SeriesC(C.Structure):
         ("n_steps", C.c_int32), ("weather_mode", C.c_int32), ("n_sites", C.c_int32), ("model_site", C.c_void_p),
         ("weather", C.c_void_p), ("weather_rows", C.c_int64), ("input_mode", C.c_int32), ("ir_mode", C.c_int32),
         ("inputs", C.c_void_p), ("record_every", C.c_int32), ("zone_t_record", C.c_void_p),
-        ("state_record", C.c_void_p),
+        ("state_record", C.c_void_p), ("zone_gain", C.c_void_p),
     ]
 
 

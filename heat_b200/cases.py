@@ -306,10 +306,9 @@ def two_zone_ensemble(n_buildings: int, seed: int = 44, *, steps_per_hour: int =
     off = np.zeros(n + 2, np.int64)
     np.cumsum(n_lay, out=off[1:n + 1])
     total = int(off[n])
-    glazing = [glass(0.006, 0.6, 0.84, 0.2)] if glazing is None else list(glazing)
-    off[n + 1] = total + len(glazing)
+    off[n + 1] = total + 1
     k, rho, cp, th = _random_layers(rng, total)
-    layers = np.zeros(total + len(glazing), D.LAYER_DTYPE)
+    layers = np.zeros(total + 1, D.LAYER_DTYPE)
     layers["kind"] = D.LAYER_SOLID
     layers["thickness"][:total], layers["conductivity"][:total] = th, k
     layers["density"][:total], layers["specific_heat"][:total] = rho, cp

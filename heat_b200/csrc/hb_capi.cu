@@ -519,6 +519,21 @@ hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const doubl
     });
 }
 
+// hb_series.zone_gain (host, [n_steps][zones of the description]) -> device table in device zone order.
+static void upload_zone_gain(hb_handle* h, const hb_series* s, DevBuf<double>& d_gain, hb::SeriesDev& P) {
+    const hb::BatchPlan& B = h->plan;
+    P.n_dev_zones = B.n_dev_zones;
+    if (!s->zone_gain || s->n_steps <= 0) return;
+    const int64_t nz = (int64_t)B.dev_zone_of.size();
+    std::vector<double> v((size_t)s->n_steps * B.n_dev_zones, 0.);
+    for (int64_t t = 0; t < s->n_steps; ++t)
+        for (int64_t z = 0; z < nz; ++z) v[(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = s->zone_gain[t * nz + z];
+    d_gain.alloc(v.size());
+    HB_CUDA(cudaMemcpyAsync(d_gain.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    HB_CUDA(cudaStreamSynchronize(h->stream));   // `v` goes out of scope
+    P.zone_gain = d_gain.p;
+}
+
 hb_status hb_march_series(hb_handle* h, const hb_series* s) {
     hb_status rc = guarded([&] {
         need_device(h);
@@ -526,7 +541,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         if (s->n_steps == 0) return;
         update_sites(h, s);
         const hb::BatchPlan& B = h->plan;
-        DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec;
+        DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec, d_gain;
         const int64_t wcount = (int64_t)s->n_sites * s->weather_rows * 3;
         d_weather.alloc(wcount);
         HB_CUDA(cudaMemcpyAsync(d_weather.p, s->weather, wcount * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -547,6 +562,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         P.n_desc_surfaces = (int64_t)B.surfaces.size();
         P.record_every = n_rec > 0 && (s->zone_t_record || s->state_record) ? s->record_every : 0;
         P.slab_len = B.node_slab_len;
+        upload_zone_gain(h, s, d_gain, P);
         if (P.record_every) {
             d_zone_rec.alloc((size_t)n_rec * B.n_dev_zones);
             P.zone_rec = d_zone_rec.p;
@@ -629,6 +645,8 @@ hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_m
         P.n_desc_surfaces = (int64_t)h->plan.surfaces.size();
         P.record_every = 0;
         P.slab_len = h->plan.node_slab_len;
+        DevBuf<double> d_gain;
+        upload_zone_gain(h, s, d_gain, P);
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (elapsed_ms) {
             HB_CUDA(cudaEventCreate(&e0));

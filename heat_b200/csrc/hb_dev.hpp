@@ -112,6 +112,8 @@ struct SeriesDev {
     double* node_rec;        // [rec][slab_len]
     double* sc_rec;          // [rec][8][n_dev_surfaces]
     int64_t slab_len;
+    const double* zone_gain; // [n_steps][n_dev_zones] (device zone order) or nullptr: q of the zones during main step t
+    int64_t n_dev_zones;
 };
 
 enum { ST_NAN_H = 1, ST_NAN_ERR = 2, ST_NAN_ZONE = 4, ST_ITER_CAP = 8, ST_BAD_GAMMA = 16 };

@@ -138,6 +138,11 @@ __global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
         // ---- main-step prologue: weather table, per-step inputs (what the caller writes into SimulationState) ----
+        if (P.zone_gain != nullptr) {   // scheduled gains of this main step (read by the zone lanes after the syncs below)
+            __syncthreads();
+            if (tid < tile.n_zones) s_zc[tid].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + tid];
+            __syncthreads();
+        }
         if (P.single_site) {
             const double* w0 = P.weather + (int64_t)step * 3;
             if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) w0 = P.weather + (int64_t)step * S * 3;
@@ -770,6 +775,11 @@ __global__ void __launch_bounds__(face_threads(G, W), NL == kNL ? HB_FACE_OCC / 
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
         if (step + 1 < P.n_steps) fill_weather(step + 1);   // read from the next main step's first pre() on
+        if (P.zone_gain != nullptr && szone) {   // scheduled gains: this main step's q, sources re-summed in the reference's order
+            ZoneC zc = s_zc[j];
+            zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + sgz];
+            zone_sources(zc, za0, zb0);
+        }
         for (int s = 0; s < S; ++s) {
 #ifdef HB_PHASE_CLOCKS
             tlast = clock64();

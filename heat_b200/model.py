@@ -223,10 +223,18 @@ class ThermalBatch:
 
     def march_series(self, n_steps: int, weather, *, weather_mode=_lib.WEATHER_STEP_CONSTANT, inputs=None,
                      input_mode=_lib.INPUT_STATE, ir_mode=_lib.IR_IRRADIANCE, model_site=None, record_every: int = 0,
-                     record_state: bool = False):
-        """Advance every model `n_steps` main steps. Returns (zone_T[rec][zones], state[rec][state_len]) or None."""
+                     record_state: bool = False, zone_gain=None):
+        """Advance every model `n_steps` main steps. Returns (zone_T[rec][zones], state[rec][state_len]) or None.
+
+        `zone_gain` [n_steps][zones]: schedule of the zones' HVAC + luminaire power [W] (model.rs:502-516); row t
+        replaces `q_internal` of `set_zone_inputs` during main step t."""
         keep: list = []
         s = self._series(n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, keep)
+        if zone_gain is not None:
+            zone_gain = _lib.f8(zone_gain)
+            assert zone_gain.size == n_steps * self.n_zones, f"zone_gain has {zone_gain.size} values"
+            s.zone_gain = _lib.ptr(zone_gain)
+            keep.append(zone_gain)
         zone_rec = state_rec = None
         if record_every > 0:
             n_rec = n_steps // record_every

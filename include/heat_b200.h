@@ -198,6 +198,11 @@ typedef struct {
     int32_t record_every;         /* 0: no recording; k: record after every k-th main step */
     double* zone_t_record;        /* [n_steps/record_every][total zones] or NULL */
     double* state_record;         /* [n_steps/record_every][state_len_total] or NULL (small batches only) */
+    const double* zone_gain;      /* schedule of the zones' HVAC + luminaire power (model.rs:502-516): HOST table
+                                     [n_steps][total zones] [W], row t replaces q_internal of hb_set_zone_inputs during
+                                     main step t (the reference reads these state elements once per sub-step and the
+                                     caller rewrites them between march calls); NULL = the constants stay.  Host
+                                     memory in hb_march_series AND hb_march_series_dev. */
 } hb_series;
 
 /* Advance every model by series->n_steps main steps (each = dt_subdivisions substeps, model.rs:369-424).

@@ -115,6 +115,8 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
     int rec = 0;
     std::vector<double> left(TPB), right(TPB);
     for (int step = 0; step < P.n_steps; ++step) {
+        if (P.zone_gain)   // scheduled gains of this main step
+            for (int t = 0; t < tile.n_zones; ++t) zc[t].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + t];
         if (P.single_site)
             for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
         for (int t = 0; t < W; ++t) {
@@ -367,6 +369,8 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
     int rec = 0;
     std::vector<double> left(NT), right(NT);
     for (int step = 0; step < P.n_steps; ++step) {
+        if (P.zone_gain)   // scheduled gains of this main step
+            for (int t = 0; t < tile.n_zones; ++t) zc[t].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + t];
         if (P.single_site)
             for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
         for (int t = 0; t < W; ++t) {
@@ -577,6 +581,15 @@ int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, con
         P.n_desc_surfaces = (int64_t)B.surfaces.size();
         P.single_site = single ? 1 : 0;
         P.slab_len = B.node_slab_len;
+        P.n_dev_zones = B.n_dev_zones;
+        std::vector<double> gain_dev;
+        if (s->zone_gain && s->n_steps > 0) {
+            const int64_t nz = (int64_t)B.dev_zone_of.size();
+            gain_dev.assign((size_t)s->n_steps * B.n_dev_zones, 0.);
+            for (int64_t t = 0; t < s->n_steps; ++t)
+                for (int64_t z = 0; z < nz; ++z) gain_dev[(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = s->zone_gain[t * nz + z];
+            P.zone_gain = gain_dev.data();
+        }
         const int n_rec = s->record_every > 0 ? s->n_steps / s->record_every : 0;
         std::vector<double> zr, nr, sr;
         P.record_every = n_rec > 0 && (s->zone_t_record || s->state_record) ? s->record_every : 0;

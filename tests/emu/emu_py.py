@@ -76,7 +76,8 @@ class EmuBatch:
                              (q_internal, infiltration_volume, infiltration_temperature, ventilation_volume,
                               ventilation_temperature)]
 
-    def _run(self, n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, record_every, record_state):
+    def _run(self, n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, record_every, record_state,
+             zone_gain=None):
         s = _lib.SeriesC()
         weather = _lib.f8(weather)
         if weather.ndim == 2:
@@ -90,6 +91,10 @@ class EmuBatch:
         if inputs is not None:
             inputs = _lib.f8(inputs)
             s.inputs = _lib.ptr(inputs)
+        if zone_gain is not None:
+            zone_gain = _lib.f8(zone_gain)
+            assert zone_gain.size == n_steps * self.n_zones
+            s.zone_gain = _lib.ptr(zone_gain)
         zone_rec = state_rec = None
         if record_every > 0:
             n_rec = n_steps // record_every
@@ -112,9 +117,9 @@ class EmuBatch:
         return zone_rec, state_rec
 
     def march_series(self, n_steps, weather, *, weather_mode=0, inputs=None, input_mode=0, ir_mode=0, model_site=None,
-                     record_every=0, record_state=False):
+                     record_every=0, record_state=False, zone_gain=None):
         return self._run(n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, record_every,
-                         record_state)
+                         record_state, zone_gain)
 
 
 def run_emu(name, max_steps=None, record_state=False):

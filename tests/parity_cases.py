@@ -216,6 +216,51 @@ def check_double_glazed_buildings(batch_cls, n=6, n_steps=6):
     return worst
 
 
+def check_scheduled_zone_gains(batch_cls, n=10, n_steps=8):
+    """HVAC / luminaire power as a per-main-step schedule (model.rs:502-516: the reference reads the state elements the
+    caller rewrites before each march): one series call with `zone_gain` against the oracle marched step by step with
+    the gains reset in between.  Shoeboxes (face kernel, zone scan), two-zone models (general zone sums) and
+    double-glazed shoeboxes (general kernel)."""
+    import oracle_py as O
+
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    builders = (lambda: cases.shoebox_ensemble(n, seed=23, steps_per_hour=2),
+                lambda: cases.two_zone_ensemble(max(2, n // 2), seed=29, steps_per_hour=2),
+                lambda: cases.shoebox_ensemble(max(2, n // 2), seed=31, steps_per_hour=2, glazing=cases.double_glazing()))
+    for build in builders:
+        d, gains = build()
+        nz = len(gains)
+        rng = cases.SplitMix64(1234)
+        sched = rng.uniform(n_steps * nz, -800.0, 1500.0).reshape(n_steps, nz)   # heating and cooling
+        sched[1] = 0.0
+        b = batch_cls(d)
+        b.set_zone_inputs(q_internal=gains)   # overridden by the schedule while it runs
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1, zone_gain=sched)
+        got = b.get_state()
+        off = 0
+        zoff = d.model_zone_offset
+        for m in range(d.n_models):
+            z0, z1 = int(zoff[m]), int(zoff[m + 1])
+            om = O.OracleModel(d, m)
+            so = om.initial_state()
+            for t in range(n_steps):
+                om.set_zone_inputs(q_internal=sched[t, z0:z1])
+                om.march_series(so, 1, weather[t:t + 2], weather_mode=1, inputs=inputs[t:t + 1], input_mode=1)
+            mine = got[off:off + len(so)]
+            nzm = z1 - z0
+            assert np.abs(mine[:nzm] - so[:nzm]).max() <= 1e-6, (m, mine[:nzm], so[:nzm])
+            for s in range(om.n_surfaces):
+                o = om.state_offset(s)
+                nn = om.n_nodes(s)
+                assert np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max() <= 1e-6, (m, s)
+            off += len(so)
+        # the schedule must matter: the same run with constant gains ends elsewhere
+        b2 = batch_cls(d)
+        b2.set_zone_inputs(q_internal=gains)
+        b2.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        assert np.abs(b2.get_state() - got).max() > 1e-3
+
+
 def check_multi_site_walls(batch_cls, n=48):
     """Walls (massive and with no-mass layers) under per-model weather sites: general face mode / general kernel."""
     import oracle_py as O

@@ -102,6 +102,10 @@ def test_emulated_double_glazed_buildings():
     pc.check_double_glazed_buildings(emu_py.EmuBatch)
 
 
+def test_emulated_scheduled_zone_gains():
+    pc.check_scheduled_zone_gains(emu_py.EmuBatch)
+
+
 def test_emulated_multi_site_walls():
     pc.check_multi_site_walls(emu_py.EmuBatch)
 

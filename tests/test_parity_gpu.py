@@ -150,6 +150,13 @@ def test_double_glazed_buildings_match_oracle():
     pc.check_double_glazed_buildings(ThermalBatch, n=24, n_steps=12)
 
 
+def test_scheduled_zone_gains_match_oracle():
+    """hb_series.zone_gain: per-main-step HVAC / luminaire power, face kernel and general kernel."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_scheduled_zone_gains(ThermalBatch, n=24, n_steps=12)
+
+
 def test_multi_site_walls_match_oracle():
     from heat_b200.model import ThermalBatch
 
