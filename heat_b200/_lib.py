@@ -96,6 +96,7 @@ SYMBOLS = {
     "hb_reset_energy": (C.c_int32, [_P]),
     "hb_measure_fp64_peak": (C.c_int32, [C.c_int32, C.POINTER(C.c_double)]),
     "hb_flush_l2": (C.c_int32, [_P, C.c_int64]),
+    "hb_read_epw": (C.c_int32, [C.c_char_p, _P, _P, C.c_int64, C.POINTER(C.c_int64)]),
 }
 
 _lib = None

@@ -611,6 +611,13 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
     return HB_OK;
 }
 
+hb_status hb_read_epw(const char* path, double* weather, double* inputs, int64_t capacity, int64_t* n_rows) {
+    return guarded([&] {
+        if (!path || !n_rows || capacity < 0) throw std::invalid_argument("hb_read_epw: path, n_rows and capacity >= 0 are required");
+        *n_rows = hb::read_epw(path, weather, inputs, capacity);
+    });
+}
+
 hb_status hb_upload(hb_handle* h, const double* host, int64_t count, double** dev_out) {
     return guarded([&] {
         need_device(h);

@@ -96,6 +96,7 @@ void pack_arrays(const BatchPlan& B, HostArrays& H);
 // scatter / gather between the reference-layout state vector and the packed buffers
 void scatter_state(const BatchPlan& B, const double* state, double* nodeT, double* sc, double* zoneT);
 void gather_state(const BatchPlan& B, const double* nodeT, const double* sc, const double* zoneT, double* state);
+int64_t read_epw(const char* path, double* weather, double* inputs, int64_t capacity);
 
 struct SeriesDev {
     int32_t n_steps;

@@ -10,6 +10,9 @@
 // that feed them keep the reference's operation order; this file is compiled with -ffp-contract=off.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <numeric>
 #include <stdexcept>
 #include <tuple>
@@ -657,6 +660,57 @@ void gather_state(const BatchPlan& B, const double* nodeT, const double* sc, con
         for (int k = 0; k < 8; ++k) p[k] = sc[k * NS + g];
         for (int i = 0; i < B.plans[gd].n_nodes; ++i) p[8 + i] = nodeT[B.slab_index((int64_t)gd, i)];
     }
+}
+
+// EPW ingestion.  The reference takes weather through the un-vendored `weather` crate
+// (`weather.get_weather_data(date)`, model.rs:372); what it reads of a record is dry bulb, wind direction, wind speed
+// (+ horizontal infrared for the sky temperature).  An EPW file is 8 header lines, then one comma-separated record per
+// hour; 1-based fields: 7 dry bulb [C], 13 horizontal infrared [W/m2], 14 global horizontal [Wh/m2], 21 wind
+// direction [deg], 22 wind speed [m/s] (mapping onto the march inputs: BASELINE.md §3, builder-defined).
+// Rows come out in the layouts hb_series consumes: weather [row][3], inputs [row][4] = (GHI, 0, IR, 0).
+int64_t read_epw(const char* path, double* weather, double* inputs, int64_t capacity) {
+    std::FILE* f = std::fopen(path, "rb");
+    if (!f) fail(std::string("EPW: cannot open '") + path + "'");
+    std::string line;
+    int64_t n = 0, lineno = 0;
+    int ch;
+    bool eof = false;
+    while (!eof) {
+        line.clear();
+        while ((ch = std::fgetc(f)) != EOF && ch != '\n') line.push_back((char)ch);
+        if (ch == EOF) eof = true;
+        ++lineno;
+        while (!line.empty() && (line.back() == '\r' || line.back() == ' ')) line.pop_back();
+        if (lineno <= 8 || line.empty()) continue;   // LOCATION … DATA PERIODS
+        double field[22];
+        int k = 0;
+        const char* p = line.c_str();
+        while (k < 22) {
+            const char* e = std::strchr(p, ',');
+            if (k == 6 || k == 12 || k == 13 || k == 20 || k == 21) {
+                char* end = nullptr;
+                field[k] = std::strtod(p, &end);
+                if (end == p) {
+                    std::fclose(f);
+                    fail("EPW: line " + std::to_string(lineno) + ": field " + std::to_string(k + 1) + " is not a number");
+                }
+            }
+            ++k;
+            if (!e) break;
+            p = e + 1;
+        }
+        if (k < 22) {
+            std::fclose(f);
+            fail("EPW: line " + std::to_string(lineno) + " has " + std::to_string(k) + " fields, expected at least 22");
+        }
+        if (n < capacity) {
+            if (weather) { weather[3 * n] = field[6]; weather[3 * n + 1] = field[20]; weather[3 * n + 2] = field[21]; }
+            if (inputs) { inputs[4 * n] = field[13]; inputs[4 * n + 1] = 0.; inputs[4 * n + 2] = field[12]; inputs[4 * n + 3] = 0.; }
+        }
+        ++n;
+    }
+    std::fclose(f);
+    return n;
 }
 
 }  // namespace hb

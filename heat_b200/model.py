@@ -13,6 +13,7 @@ from __future__ import annotations
 import ctypes as C
 import dataclasses
 import math
+import os
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -287,6 +288,20 @@ class ThermalBatch:
     @property
     def launch_count(self) -> int:
         return self._lib.hb_launch_count(self._h)
+
+
+def read_epw(path: str, periodic: bool = True):
+    """Hourly records of an EPW file → (weather[rows(+1)][3], inputs[rows][4]) as `march_series` takes them
+    (`weather_mode=WEATHER_LINEAR, input_mode=INPUT_SITE`); `periodic` appends the first record after the last."""
+    lib = _lib.load()
+    n = C.c_int64()
+    _lib.check(lib.hb_read_epw(os.fsencode(path), None, None, 0, C.byref(n)))
+    weather = np.zeros((n.value + (1 if periodic else 0), 3))
+    inputs = np.zeros((n.value, 4))
+    _lib.check(lib.hb_read_epw(os.fsencode(path), _lib.ptr(weather), _lib.ptr(inputs), n.value, C.byref(n)))
+    if periodic and n.value:
+        weather[-1] = weather[0]
+    return weather, inputs
 
 
 def measure_fp64_peak(device: int = 0) -> float:

@@ -232,6 +232,15 @@ typedef struct {
 hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out);
 hb_status hb_reset_energy(hb_handle* h);
 
+/* ---- EPW ingestion (host only; the reference reads weather through the `weather` crate, model.rs:372) ----
+ * Hourly records of an EnergyPlus weather file in the layouts hb_series consumes:
+ * weather [row][3] = dry bulb [C] (EPW field 7), wind direction [deg] (21), wind speed [m/s] (22);
+ * inputs  [row][4] = global horizontal [W/m2] (14) as front solar, 0, horizontal infrared [W/m2] (13) as front IR, 0
+ * (HB_INPUT_SITE + HB_IR_IRRADIANCE).  Either array may be NULL; at most `capacity` rows are written, `*n_rows`
+ * receives the number of records in the file (call with capacity 0 to size the buffers).  For a periodic year with
+ * HB_WEATHER_LINEAR append row 0 after the last one. */
+hb_status hb_read_epw(const char* path, double* weather, double* inputs, int64_t capacity, int64_t* n_rows);
+
 /* ---- device probes used by bench.py ---- */
 /* Dependent-free DFMA micro-benchmark: returns measured FP64 TFLOP/s (FMA = 2 FLOP) on `device`. */
 hb_status hb_measure_fp64_peak(int32_t device, double* tflops);

@@ -2,6 +2,7 @@
 0 mismatches allowed in tstep_subdivision, n_elements, node counts, chunk ranges and state offsets
 (BASELINE.json north_star); masses / conductances / alphas bit-exact."""
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -118,3 +119,65 @@ def test_no_cpu_fallback():
     assert e.value.status == 2  # HB_ERR_CUDA
     with pytest.raises(HeatB200Error):
         b.get_state()
+
+
+# ---- EPW ingestion (hb_read_epw) ------------------------------------------------------------------------------
+_EPW_HEADER = ["LOCATION,TESTVILLE,-,XXX,Synthetic,000000,-33.38,-70.78,-4.0,476.0", "DESIGN CONDITIONS,0",
+               "TYPICAL/EXTREME PERIODS,0", "GROUND TEMPERATURES,0", "HOLIDAYS/DAYLIGHT SAVINGS,No,0,0,0",
+               'COMMENTS 1,"a, quoted, comment"', "COMMENTS 2,none", "DATA PERIODS,1,1,Data,Sunday, 1/ 1,12/31"]
+
+
+def _epw_record(hour, t, ir, ghi, wdir, wspd):
+    f = ["1987", "1", "1", str(hour), "60", "C9C9*0?9", f"{t}", "9.6", "63", "95600", "0", "1415", f"{ir}", f"{ghi}",
+         "0", "0", "0", "0", "0", "0", f"{wdir}", f"{wspd}", "0", "0", "9.9", "77777", "9", "999999999", "0", "0.2680",
+         "0", "88", "0.000", "0.0", "0"]
+    return ",".join(f)
+
+
+def test_read_epw_synthetic_file(tmp_path):
+    from heat_b200.model import read_epw
+
+    rng = np.random.default_rng(3)
+    vals = np.round(rng.uniform(-5, 400, (30, 5)), 1)
+    p = tmp_path / "synthetic.epw"
+    body = [_epw_record(i % 24 + 1, *vals[i]) for i in range(30)]
+    p.write_text("\r\n".join(_EPW_HEADER + body) + "\r\n")      # CRLF like the files in the wild, trailing newline
+    weather, inputs = read_epw(str(p))
+    assert weather.shape == (31, 3) and inputs.shape == (30, 4)
+    assert np.array_equal(weather[:30], vals[:, [0, 3, 4]])       # dry bulb, wind direction, wind speed
+    assert np.array_equal(weather[30], weather[0])                # periodic closure for HB_WEATHER_LINEAR
+    assert np.array_equal(inputs[:, 0], vals[:, 2]) and np.array_equal(inputs[:, 2], vals[:, 1])
+    assert not inputs[:, [1, 3]].any()
+    w2, _ = read_epw(str(p), periodic=False)
+    assert w2.shape == (30, 3)
+
+
+def test_read_epw_errors(tmp_path):
+    from heat_b200.model import read_epw
+
+    with pytest.raises(Exception) as e:
+        read_epw(str(tmp_path / "missing.epw"))
+    assert "cannot open" in str(e.value)
+    p = tmp_path / "short.epw"
+    p.write_text("\n".join(_EPW_HEADER + ["1987,1,1,1,60,flags,16.7,9.6"]) + "\n")
+    with pytest.raises(Exception) as e:
+        read_epw(str(p))
+    assert "fields" in str(e.value)
+    p = tmp_path / "nan.epw"
+    p.write_text("\n".join(_EPW_HEADER + [_epw_record(1, "abc", 1, 2, 3, 4)]) + "\n")
+    with pytest.raises(Exception) as e:
+        read_epw(str(p))
+    assert "not a number" in str(e.value)
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/tests/epw/CHL_Santiago.855740_IWEC.epw"),
+                    reason="reference tree only exists in the build container")
+def test_read_epw_reference_file_matches_fixture():
+    """The reference's own EPW through hb_read_epw == tests/golden/epw_santiago.npz (parsed by make_fixtures.py)."""
+    from heat_b200.model import read_epw
+
+    weather, inputs = read_epw("/root/reference/tests/epw/CHL_Santiago.855740_IWEC.epw")
+    h = np.load(os.path.join(os.path.dirname(__file__), "golden", "epw_santiago.npz"))["hourly"]
+    assert weather.shape == (8761, 3)
+    assert np.array_equal(weather[:8760], h[:, [0, 3, 4]])
+    assert np.array_equal(inputs[:, 0], h[:, 2]) and np.array_equal(inputs[:, 2], h[:, 1])
