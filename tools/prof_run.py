@@ -11,6 +11,8 @@ kind = sys.argv[3] if len(sys.argv) > 3 else "walls"
 if kind == "walls":
     d = cases.wall_ensemble(units, seed=42)
     gains = None
+elif kind == "buildings2g":
+    d, gains = cases.shoebox_ensemble(units, seed=43, glazing=cases.double_glazing())
 else:
     d, gains = cases.shoebox_ensemble(units, seed=43)
 weather, inputs = cases.synthetic_weather(hours + 1)
