@@ -182,6 +182,39 @@ def check_general_mode_buildings(batch_cls, n=8):
         off += len(so)
 
 
+def write_epw_from_fixture(path, hours=8760):
+    """EPW text file (8 header lines + hourly records, CRLF) holding the Santiago fixture's five columns — the reference's
+    own file does not travel to the GPU box.  `repr` of a double round-trips through strtod exactly."""
+    h = _npz("epw_santiago.npz")["hourly"][:hours]
+    head = ["LOCATION,SANTIAGO,-,CHL,IWEC Data,855740,-33.38,-70.78,-4.0,476.0", "DESIGN CONDITIONS,0",
+            "TYPICAL/EXTREME PERIODS,0", "GROUND TEMPERATURES,0", "HOLIDAYS/DAYLIGHT SAVINGS,No,0,0,0", "COMMENTS 1,fixture",
+            "COMMENTS 2,fixture", "DATA PERIODS,1,1,Data,Sunday, 1/ 1,12/31"]
+    with open(path, "w", newline="") as f:
+        f.write("\r\n".join(head) + "\r\n")
+        for i, (t, ir, ghi, wd, ws) in enumerate(h):
+            rec = ["1987", str(1 + i // 730), str(1 + (i // 24) % 30), str(1 + i % 24), "60", "?9?9", repr(float(t)), "9.6",
+                   "63", "95600", "0", "1415", repr(float(ir)), repr(float(ghi)), "0", "0", "0", "0", "0", "0",
+                   repr(float(wd)), repr(float(ws)), "0", "0", "9.9", "77777", "9", "999999999", "0", "0.2680", "0", "88",
+                   "0.000", "0.0", "0"]
+            f.write(",".join(rec) + "\r\n")
+
+
+def check_epw_file_year(batch_cls, path, case="massive_full"):
+    """EPW file → hb_read_epw → one series call over the whole year (n = 1/h, linear weather between records) against
+    the committed oracle output of the same case (north_star: full-year hourly EPW run within 1e-6 °C)."""
+    from heat_b200.model import read_epw
+
+    write_epw_from_fixture(path)
+    weather, inputs = read_epw(path)
+    c = make_case(f"epw/{case}")
+    assert np.array_equal(weather, c.weather) and np.array_equal(inputs, c.inputs)
+    b = batch_cls(cases.validation_case(case, 1))
+    zone, _ = b.march_series(len(inputs), weather, weather_mode=1, inputs=inputs, input_mode=1, ir_mode=0, record_every=1)
+    zone_g, final_g = golden(f"epw/{case}")
+    assert np.abs(zone[:, 0] - np.asarray(zone_g).reshape(len(inputs), -1)[:, 0]).max() <= 1e-6
+    assert np.abs(b.get_state() - final_g).max() <= 1e-5
+
+
 def check_double_glazed_buildings(batch_cls, n=6, n_steps=6):
     """Shoeboxes whose window is pane | gas | pane: ISO 9050 absorptances per pane (glazing.rs:180-286), the cavity's
     temperature-dependent U (cavity.rs:59-69, gas.rs:82-315) and the no-mass solve of a 4-node window, next to the zone

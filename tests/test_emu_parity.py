@@ -102,6 +102,10 @@ def test_emulated_double_glazed_buildings():
     pc.check_double_glazed_buildings(emu_py.EmuBatch)
 
 
+def test_emulated_epw_file_year(tmp_path):
+    pc.check_epw_file_year(emu_py.EmuBatch, str(tmp_path / "santiago.epw"))
+
+
 def test_emulated_scheduled_zone_gains():
     pc.check_scheduled_zone_gains(emu_py.EmuBatch)
 

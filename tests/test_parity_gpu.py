@@ -150,6 +150,14 @@ def test_double_glazed_buildings_match_oracle():
     pc.check_double_glazed_buildings(ThermalBatch, n=24, n_steps=12)
 
 
+@pytest.mark.parametrize("case", ["massive_full", "mixed_full"])
+def test_epw_file_year_matches_golden(tmp_path, case):
+    """EPW text file through hb_read_epw, then the whole year in one series call, against the committed oracle output."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_epw_file_year(ThermalBatch, str(tmp_path / "santiago.epw"), case)
+
+
 def test_scheduled_zone_gains_match_oracle():
     """hb_series.zone_gain: per-main-step HVAC / luminaire power, face kernel and general kernel."""
     from heat_b200.model import ThermalBatch
