@@ -31,8 +31,14 @@ constexpr int kVarPlain = 0, kVarExt = 1, kVarDist = 2, kVarEnd = 3, kVarGen = 4
 // no-mass end nodes and single panes
 constexpr int kFaceLean = 0, kFaceLeanEnd = 1, kFaceGen = 2, kFacePane = 3;
 
+#ifndef HB_MARCH_OCC
+// resident threads per SM the general kernel is compiled for.  384 (168 registers per thread, spills halved) measured
+// 5.5 % faster than 512 (128 registers) on double-glazed buildings, 256 (no spills) the same as 384, 768 (80
+// registers) 14 % slower (profiles/r1x_occ_ab.log, r1x_occ_ab2.log): the scalar lane's chain sets the time, not occupancy
+#define HB_MARCH_OCC 384
+#endif
 template <int G, int W, int VAR>
-__global__ void __launch_bounds__(G* W, 512 / (G * W)) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+__global__ void __launch_bounds__(G* W, HB_MARCH_OCC / (G * W) > 0 ? HB_MARCH_OCC / (G * W) : 1) hb_march_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
     constexpr int TPB = G * W;
     constexpr int NL = kNL;
     constexpr bool EXT = VAR >= kVarExt, DIST = VAR == kVarDist;
