@@ -82,12 +82,36 @@ struct hb_handle {
         DevBuf<int32_t> ids;   // tile ids, heaviest first
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;
+        Group() = default;
+        Group(const Group&) = delete;
+        Group& operator=(const Group&) = delete;
+        ~Group() {   // a create that throws half-way (cudaMalloc OOM on a large shard) must not leak streams / events
+            if (stream) {
+                cudaStreamSynchronize(stream);
+                cudaStreamDestroy(stream);
+            }
+            if (done) cudaEventDestroy(done);
+        }
     };
     std::vector<std::unique_ptr<Group>> groups;
     cudaEvent_t fork = nullptr;
     std::vector<int32_t> host_site;  // per device surface slot (rebuilt when model_site changes)
     std::vector<int32_t> model_site_cache;
     bool single_site = true;
+
+    hb_handle() = default;
+    hb_handle(const hb_handle&) = delete;
+    hb_handle& operator=(const hb_handle&) = delete;
+    ~hb_handle() {
+        if (device < 0) return;
+        cudaSetDevice(device);
+        groups.clear();   // joins and destroys the group streams / events
+        if (fork) cudaEventDestroy(fork);
+        if (stream) {
+            cudaStreamSynchronize(stream);
+            cudaStreamDestroy(stream);
+        }
+    }
 
     hb::DevView view() {
         hb::DevView V{};
@@ -337,8 +361,13 @@ int64_t input_count(const hb_handle* h, const hb_series* s) {
     return 0;
 }
 
+void clear_status(hb_handle* h) {
+    if (h->status.n) HB_CUDA(cudaMemsetAsync(h->status.p, 0, h->status.n * sizeof(int32_t), h->stream));
+}
+
 void check_status(hb_handle* h) {
-    // a non-zero per-surface status word is the reference's panic!
+    // a non-zero per-surface status word is the reference's panic! — of THIS call: the words are cleared at the start of
+    // every march (clear_status), so a handle stays usable after a reported failure (hb_set_state + march again)
     std::vector<int32_t> st(h->plan.n_dev_surfaces);
     HB_CUDA(cudaMemcpyAsync(st.data(), h->status.p, st.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     HB_CUDA(cudaStreamSynchronize(h->stream));
@@ -352,6 +381,19 @@ void check_status(hb_handle* h) {
         if (st[g] & hb::ST_BAD_GAMMA) what += " cavity tilt out of range;";
         throw std::domain_error("physics failure on device surface slot " + std::to_string(g) + ":" + what);
     }
+}
+
+hb_status physics_status(hb_handle* h) {
+    try {
+        check_status(h);
+    } catch (const CudaError& e) {
+        g_err = e.what();
+        return HB_ERR_CUDA;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return HB_ERR_PHYSICS;
+    }
+    return HB_OK;
 }
 
 }  // namespace
@@ -386,27 +428,7 @@ hb_status hb_create(const hb_batch_desc* desc, int32_t device, hb_handle** out) 
     return rc;
 }
 
-void hb_destroy(hb_handle* h) {
-    if (!h) return;
-    if (h->device < 0) {
-        delete h;
-        return;
-    }
-    cudaSetDevice(h->device);
-    for (auto& g : h->groups) {
-        if (g->stream) {
-            cudaStreamSynchronize(g->stream);
-            cudaStreamDestroy(g->stream);
-        }
-        if (g->done) cudaEventDestroy(g->done);
-    }
-    if (h->fork) cudaEventDestroy(h->fork);
-    if (h->stream) {
-        cudaStreamSynchronize(h->stream);
-        cudaStreamDestroy(h->stream);
-    }
-    delete h;
-}
+void hb_destroy(hb_handle* h) { delete h; }   // ~hb_handle releases streams, events and device buffers
 
 int32_t hb_n_models(const hb_handle* h) { return (int32_t)h->plan.models.size(); }
 int64_t hb_n_surfaces_total(const hb_handle* h) { return (int64_t)h->plan.surfaces.size(); }
@@ -470,12 +492,13 @@ hb_status hb_set_state(hb_handle* h, const double* state) {
     return guarded([&] {
         need_device(h);
         const hb::BatchPlan& B = h->plan;
-        // ghost / padding slots keep whatever they hold: start from the device image
+        // ghost / padding slots are rewritten by the kernels before they are read: a zero-filled slab is fine
         std::vector<double> nodeT(B.node_slab_len, 0.), sc(8 * B.n_dev_surfaces, 0.), zoneT(B.n_dev_zones, 0.);
         hb::scatter_state(B, state, nodeT.data(), sc.data(), zoneT.data());
         HB_CUDA(cudaMemcpyAsync(h->nodeT.p, nodeT.data(), nodeT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         HB_CUDA(cudaMemcpyAsync(h->sc.p, sc.data(), sc.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
         HB_CUDA(cudaMemcpyAsync(h->zoneT.p, zoneT.data(), zoneT.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        clear_status(h);   // a new state starts with a clean record (the reference's error belongs to one march call)
         HB_CUDA(cudaStreamSynchronize(h->stream));
     });
 }
@@ -540,6 +563,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         validate_series(h, s);
         if (s->n_steps == 0) return;
         update_sites(h, s);
+        clear_status(h);
         const hb::BatchPlan& B = h->plan;
         DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec, d_gain;
         const int64_t wcount = (int64_t)s->n_sites * s->weather_rows * 3;
@@ -599,16 +623,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         HB_CUDA(cudaGetLastError());
     });
     if (rc != HB_OK) return rc;
-    try {
-        check_status(h);
-    } catch (const CudaError& e) {
-        g_err = e.what();
-        return HB_ERR_CUDA;
-    } catch (const std::exception& e) {
-        g_err = e.what();
-        return HB_ERR_PHYSICS;
-    }
-    return HB_OK;
+    return physics_status(h);
 }
 
 hb_status hb_read_epw(const char* path, double* weather, double* inputs, int64_t capacity, int64_t* n_rows) {
@@ -637,10 +652,11 @@ hb_status hb_free_dev(hb_handle* h, double* dev) {
 }
 
 hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_ms) {
-    return guarded([&] {
+    hb_status rc = guarded([&] {
         need_device(h);
         validate_series(h, s);
         update_sites(h, s);
+        clear_status(h);
         hb::SeriesDev P{};
         P.n_steps = s->n_steps;
         P.weather_mode = s->weather_mode;
@@ -672,6 +688,8 @@ hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_m
         }
         HB_CUDA(cudaGetLastError());
     });
+    if (rc != HB_OK) return rc;
+    return physics_status(h);   // after the timed events: a poisoned run must not return HB_OK
 }
 
 hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out) {

@@ -654,14 +654,12 @@ __global__ void __launch_bounds__(face_threads(G, W), NL == kNL ? HB_FACE_OCC / 
     };
     // what the caller writes into SimulationState before a main step + the per-step derived quantities
     auto main_step_inputs = [&](int step) {
-        double sol_front = back ? V.sc[4 * NS + sg] : w.sol;
         if (P.input_mode != HB_INPUT_STATE) {
             const double* in = P.input_mode == HB_INPUT_SITE
                                    ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
                                    : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
             w.sol = in[kf];
             w.ir = in[2 + kf];
-            sol_front = in[0];
             if (!back && P.ir_mode == HB_IR_NET_GAIN) {
                 // validate_wall_heat_transfer.rs:689-699 (front face only, as in the reference driver)
                 if (c.eps > 1e-3) {
@@ -673,7 +671,7 @@ __global__ void __launch_bounds__(face_threads(G, W), NL == kNL ? HB_FACE_OCC / 
                 }
             }
         }
-        face_begin_main_step(c, w, sol_front);
+        face_begin_main_step(c, w);
     };
     // A pane's two faces (lanes j and W + j of this warp) exchange their border conditions and both solve the wall's
     // 2x2 no-mass system (solve_pane) with identical inputs; each keeps its own node.

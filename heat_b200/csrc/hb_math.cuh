@@ -490,7 +490,8 @@ HB_HD void begin_main_step(const WallC& c, WallS& w) {
     double solar_front = w.sol_f;
     if (solar_front != solar_front || solar_front < 0.0) solar_front = 0.0;  // surface.rs:916-919
     double solar_back = w.sol_b;
-    if (solar_back != solar_back || w.sol_f < 0.0) solar_back = 0.0;          // surface.rs:920-923 (tests solar_front)
+    // surface.rs:920-923 tests `solar_front < 0.0` AFTER the front clamp above made it >= 0: only a NaN zeroes it
+    if (solar_back != solar_back || solar_front < 0.0) solar_back = 0.0;
     w.solar_front = solar_front;
     w.solar_back = solar_back;
     w.trad_out_f = sqrt(sqrt(w.ir_f / kSigma)) - 273.15;
@@ -732,12 +733,12 @@ struct FaceS {
     unsigned long long nm_iters;
     int32_t status;
 };
-// surface.rs:916-931,647,692 for one face. `sol_front` is the FRONT irradiance slot: the reference's back clamp
-// tests it (surface.rs:921).
-HB_HD void face_begin_main_step(const FaceC& c, FaceS& w, double sol_front) {
+// surface.rs:916-931,647,692 for one face.  The reference's back clamp tests `solar_front < 0.0` (surface.rs:921) after
+// the front clamp has already made solar_front >= 0, so the back irradiance is zeroed by a NaN only.
+HB_HD void face_begin_main_step(const FaceC& c, FaceS& w) {
     double s = w.sol;
     if (c.fl & FC_BACK) {
-        if (s != s || sol_front < 0.0) s = 0.0;
+        if (s != s) s = 0.0;
     } else {
         if (s != s || s < 0.0) s = 0.0;
     }

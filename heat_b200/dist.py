@@ -49,6 +49,9 @@ class EnsembleStats:
         return self.sum_node_t / self.n_nodes
 
 
+STATUS_BITS = 8   # ST_NAN_H, ST_NAN_ERR, ST_NAN_ZONE, ST_ITER_CAP, ST_BAD_GAMMA (hb_dev.hpp) + spare
+
+
 def combine_stats(local: EnsembleStats, device: Optional[str] = None, group=None) -> EnsembleStats:
     """All-reduce the per-rank statistics over `torch.distributed` (sum / min / max / bitwise-or of the status words).
 
@@ -65,14 +68,16 @@ def combine_stats(local: EnsembleStats, device: Optional[str] = None, group=None
                          float(local.n_zones), float(local.n_nodes), float(local.nomass_iterations)],
                         dtype=torch.float64, device=dev)
     mins = torch.tensor([local.min_zone_t, local.min_node_t], dtype=torch.float64, device=dev)
-    maxs = torch.tensor([local.max_zone_t, local.max_node_t, float(local.status_flags != 0)], dtype=torch.float64,
-                        device=dev)
+    # the status words are OR-ed bit by bit: NCCL has no bitwise-or reduction, a MAX per bit is the same thing
+    bits = [float((int(local.status_flags) >> k) & 1) for k in range(STATUS_BITS)]
+    maxs = torch.tensor([local.max_zone_t, local.max_node_t] + bits, dtype=torch.float64, device=dev)
     dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=group)
     dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
     s, mn, mx = sums.tolist(), mins.tolist(), maxs.tolist()
+    flags = sum(1 << k for k in range(STATUS_BITS) if mx[2 + k] > 0.5)
     return EnsembleStats(s[0], mn[0], mx[0], s[1], mn[1], mx[1], s[2], s[3], int(round(s[4])), int(round(s[5])),
-                         int(round(s[6])), local.status_flags if mx[2] == 0 else (local.status_flags or 1))
+                         int(round(s[6])), flags)
 
 
 def max_over_ranks(values, device: Optional[str] = None, group=None):

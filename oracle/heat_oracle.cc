@@ -1502,11 +1502,24 @@ int32_t ho_glazing_alphas(const double* tau, const double* rho_front, const doub
         -1);
 }
 
+int64_t ho_run_ensemble_q(ho_model* const* models, int32_t n_models, int32_t n_steps, const double* weather,
+                          const double* surf_inputs, int32_t weather_linear, int32_t threads,
+                          double* final_state_concat, const double* q_internal_concat);
+
 int64_t ho_run_ensemble(ho_model* const* models, int32_t n_models, int32_t n_steps, const double* weather,
                         const double* surf_inputs, int32_t weather_linear, int32_t threads,
                         double* final_state_concat) {
-    std::vector<size_t> offsets(n_models + 1, 0);
+    return ho_run_ensemble_q(models, n_models, n_steps, weather, surf_inputs, weather_linear, threads,
+                             final_state_concat, nullptr);
+}
+
+// Same, with the zones' HVAC + luminaire power (model.rs:502-516) given per zone, models concatenated (or NULL).
+int64_t ho_run_ensemble_q(ho_model* const* models, int32_t n_models, int32_t n_steps, const double* weather,
+                          const double* surf_inputs, int32_t weather_linear, int32_t threads,
+                          double* final_state_concat, const double* q_internal_concat) {
+    std::vector<size_t> offsets(n_models + 1, 0), zoffsets(n_models + 1, 0);
     for (int i = 0; i < n_models; ++i) offsets[i + 1] = offsets[i] + models[i]->state_len;
+    for (int i = 0; i < n_models; ++i) zoffsets[i + 1] = zoffsets[i] + models[i]->zone_volume.size();
     std::atomic<int> next{0};
     std::atomic<int64_t> updates{0};
     std::atomic<int> failed{0};
@@ -1544,7 +1557,9 @@ int64_t ho_run_ensemble(ho_model* const* models, int32_t n_models, int32_t n_ste
                             state[s.state_offset + SLOT_BACK_IR] = in[3];
                         }
                     }
-                    m->march(state.data(), wrow.data(), nullptr);
+                    ho_zone_inputs zin{};
+                    if (q_internal_concat) zin.q_internal = q_internal_concat + zoffsets[i];
+                    m->march(state.data(), wrow.data(), q_internal_concat ? &zin : nullptr);
                     local += nodes * (int64_t)S;
                 }
             } catch (const std::exception&) {

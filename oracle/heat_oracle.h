@@ -176,6 +176,10 @@ int32_t ho_glazing_alphas(const double* tau, const double* rho_front, const doub
 int64_t ho_run_ensemble(ho_model* const* models, int32_t n_models, int32_t n_steps, const double* weather,
                         const double* surf_inputs, int32_t weather_linear, int32_t threads,
                         double* final_state_concat);
+/* … with the zones' HVAC + luminaire power [W] per zone, models concatenated (NULL = none) */
+int64_t ho_run_ensemble_q(ho_model* const* models, int32_t n_models, int32_t n_steps, const double* weather,
+                          const double* surf_inputs, int32_t weather_linear, int32_t threads,
+                          double* final_state_concat, const double* q_internal_concat);
 
 #ifdef __cplusplus
 }

@@ -110,6 +110,8 @@ def load() -> C.CDLL:
         lib.ho_glazing_alphas.argtypes = [_P, _P, _P, C.c_int32, _P]
         lib.ho_run_ensemble.restype = C.c_int64
         lib.ho_run_ensemble.argtypes = [_P, C.c_int32, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P]
+        lib.ho_run_ensemble_q.restype = C.c_int64
+        lib.ho_run_ensemble_q.argtypes = [_P, C.c_int32, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P]
         _lib = lib
     return _lib
 
@@ -379,16 +381,20 @@ def glazing_alphas(tau, rho_front, rho_back):
     return out[:n]
 
 
-def run_ensemble(models, n_steps, weather, surf_inputs=None, weather_linear=False, threads=1, want_state=False):
-    """Time-able CPU baseline: each model marched on one of `threads` host threads. Returns (updates, states)."""
+def run_ensemble(models, n_steps, weather, surf_inputs=None, weather_linear=False, threads=1, want_state=False,
+                 q_internal=None):
+    """Time-able CPU baseline: each model marched on one of `threads` host threads. Returns (updates, states).
+    `q_internal`: HVAC + luminaire power per zone, models concatenated."""
     lib = load()
     arr = (C.c_void_p * len(models))(*[m.handle for m in models])
     weather = _f8(weather)
     si = None if surf_inputs is None else _f8(surf_inputs)
     total = sum(m.state_len for m in models)
     out = np.zeros(total) if want_state else None
-    n = lib.ho_run_ensemble(arr, len(models), n_steps, weather.ctypes.data, None if si is None else si.ctypes.data,
-                            int(weather_linear), threads, None if out is None else out.ctypes.data)
+    q = None if q_internal is None else _f8(q_internal)
+    n = lib.ho_run_ensemble_q(arr, len(models), n_steps, weather.ctypes.data, None if si is None else si.ctypes.data,
+                              int(weather_linear), threads, None if out is None else out.ctypes.data,
+                              None if q is None else q.ctypes.data)
     if n < 0:
         raise OracleError(lib.ho_last_error().decode())
     return n, out

@@ -375,7 +375,6 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
         for (int t = 0; t < W; ++t) {
             if (!have[t]) continue;
-            double sol_front = fs[2 * t].sol;
             for (int k = 0; k < 2; ++k) {
                 const FaceC& c = fc[2 * t + k];
                 FaceS& w = fs[2 * t + k];
@@ -384,7 +383,6 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                                            ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
                                            : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
                     w.sol = in[k]; w.ir = in[2 + k];
-                    sol_front = in[0];
                     if (k == 0 && P.ir_mode == HB_IR_NET_GAIN) {
                         if (c.eps > 1e-3) {
                             const double tk = w.ts + 273.15;
@@ -395,7 +393,7 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                         }
                     }
                 }
-                face_begin_main_step(c, w, sol_front);
+                face_begin_main_step(c, w);
             }
         }
         for (int s = 0; s < S; ++s) {

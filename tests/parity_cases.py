@@ -5,6 +5,7 @@ CPU oracle and `run_gpu` the CUDA path through the C ABI with the SAME arrays.
 """
 from __future__ import annotations
 
+import math
 import os
 import sys
 
@@ -423,3 +424,257 @@ def check_walls_beyond_254_nodes(batch_cls, n_steps=3):
         assert np.abs(got[off:off + len(so)] - so).max() <= 1e-6, (m, np.abs(got[off:off + len(so)] - so).max())
         off += len(so)
     assert big > 254, big
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Round 2: the benchmarked ensembles over the full horizon, and the device branches round 1 never reached
+# ------------------------------------------------------------------------------------------------------------------
+def ensemble_of(kind: str, n: int):
+    """The generators bench.py runs (configs[2], [3], [4]) with their seeds, at `n` units."""
+    if kind == "walls":
+        return cases.wall_ensemble(n, seed=42), None
+    if kind == "mixed":
+        return cases.wall_ensemble(n, seed=44, mixed_fraction=0.5), None
+    if kind == "buildings":
+        return cases.shoebox_ensemble(n, seed=43)
+    raise KeyError(kind)
+
+
+def check_full_horizon_ensemble(batch_cls, kind: str, n: int, hours: int = 8760, threads: int | None = None,
+                                tol: float = 1e-6):
+    """A seeded sample of a benchmarked ensemble marched over the whole horizon in ONE series call (as bench.py does)
+    against the live oracle: every node and zone temperature of every model at the end of the horizon, the zone
+    temperatures at every 24th main step, and equal no-mass iteration counts (branch parity).  north_star: "within
+    1e-6 °C absolute over a full-year hourly EPW run"."""
+    import oracle_py as O
+
+    d, gains = ensemble_of(kind, n)
+    weather, inputs = cases.synthetic_weather(hours + 1)
+    inputs = np.ascontiguousarray(inputs[:hours])
+    b = batch_cls(d)
+    if gains is not None:
+        b.set_zone_inputs(q_internal=gains)
+    b.march_series(hours, weather, weather_mode=1, inputs=inputs, input_mode=1)
+    got = b.get_state()
+    models = [O.OracleModel(d, m) for m in range(d.n_models)]
+    threads = threads or os.cpu_count() or 1
+    _, ref = O.run_ensemble(models, hours, weather, inputs, weather_linear=True, threads=threads, want_state=True,
+                            q_internal=gains)
+    assert ref.shape == got.shape
+    off = 0
+    worst_node = worst_zone = 0.0
+    for om in models:
+        nz = om.n_zones
+        worst_zone = max(worst_zone, float(np.abs(got[off:off + nz] - ref[off:off + nz]).max()))
+        for s in range(om.n_surfaces):
+            o = off + om.state_offset(s)
+            nn = om.n_nodes(s)
+            worst_node = max(worst_node, float(np.abs(got[o + 8:o + 8 + nn] - ref[o + 8:o + 8 + nn]).max()))
+            # film coefficients and convective flows of the last sub-step
+            assert np.abs(got[o:o + 4] - ref[o:o + 4]).max() <= 1e-5 * max(1.0, np.abs(ref[o:o + 4]).max())
+        off += om.state_len
+    assert off == got.size
+    assert worst_node <= tol and worst_zone <= tol, (kind, worst_node, worst_zone)
+    iters = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
+    assert iters == sum(om.nomass_iterations for om in models), (kind, iters)
+    return worst_node, worst_zone
+
+
+def _march_and_compare(batch_cls, d, n_steps, weather, *, weather_mode=1, inputs=None, input_mode=1, zone_inputs=None,
+                       tol=1e-6, label=""):
+    """Batch against one oracle per model on the same arrays: all zones, all nodes, h and flows, iteration counts."""
+    import oracle_py as O
+
+    b = batch_cls(d)
+    if zone_inputs:
+        b.set_zone_inputs(**zone_inputs)
+    b.march_series(n_steps, weather, weather_mode=weather_mode, inputs=inputs, input_mode=input_mode)
+    got = b.get_state()
+    off = 0
+    iters = 0
+    n_surf_total = int(d.model_surface_offset[-1])
+    for m in range(d.n_models):
+        om = O.OracleModel(d, m)
+        z0, z1 = int(d.model_zone_offset[m]), int(d.model_zone_offset[m + 1])
+        if zone_inputs:
+            om.set_zone_inputs(**{k: np.asarray(v, float)[z0:z1] for k, v in zone_inputs.items()})
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=weather_mode, inputs=inputs, input_mode=input_mode,
+                        surface_base=int(d.model_surface_offset[m]), n_surfaces_total=n_surf_total)
+        mine = got[off:off + len(so)]
+        nz = z1 - z0
+        assert np.abs(mine[:nz] - so[:nz]).max() <= tol, (label, m, "zone", mine[:nz], so[:nz])
+        for s in range(om.n_surfaces):
+            o = om.state_offset(s)
+            nn = om.n_nodes(s)
+            err = np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max()
+            assert err <= tol, (label, m, s, "nodes", err)
+            assert np.abs(mine[o:o + 4] - so[o:o + 4]).max() <= 1e-5 * max(1.0, np.abs(so[o:o + 4]).max()), (label, m, s)
+        iters += om.nomass_iterations
+        off += len(so)
+    assert off == got.size
+    mine_it = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
+    assert mine_it == iters, (label, mine_it, iters)
+    return got
+
+
+def check_negative_front_solar(batch_cls, n=24, n_steps=12):
+    """surface.rs:916-923: the back clamp tests `solar_front < 0.0` AFTER solar_front was clamped to >= 0, so a negative
+    front irradiance zeroes the front only.  Massive walls (lean face path), mixed walls (no-mass ends) and a Trombe
+    wall (general kernel), front = -5, back = 200 W/m2 on some steps."""
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    inputs = inputs[:n_steps].copy()
+    inputs[:, 0] = np.where(np.arange(n_steps) % 3 == 0, -5.0, inputs[:, 0])
+    inputs[:, 1] = 200.0
+    d = cases.wall_ensemble(n, seed=5, mixed_fraction=0.5)
+    _march_and_compare(batch_cls, d, n_steps, weather, inputs=inputs, label="neg-solar walls")
+    _march_and_compare(batch_cls, cases.validation_case("trombe_wall_full", 2), n_steps, weather, inputs=inputs,
+                       label="neg-solar trombe")
+
+
+def back_ambient_models(n=12, seed=61):
+    """Models whose walls have an AmbientTemperature BACK boundary — the arm the reference builds from FRONT values
+    (surface.rs:672-685): (a) Outdoor | wall | Ambient next to an ordinary wall of the same zone, (b) a floor whose
+    front looks at the zone and whose back is the ground at a fixed temperature."""
+    rng = cases.SplitMix64(seed)
+    k, rho, cp, th = cases._random_layers(rng, n)
+    layers = np.zeros(n, D.LAYER_DTYPE)
+    layers["kind"] = D.LAYER_SOLID
+    layers["thickness"], layers["conductivity"], layers["density"], layers["specific_heat"] = th, k, rho, cp
+    for f, v in (("front_emissivity", 0.9), ("back_emissivity", 0.8), ("front_solar_abs", 0.6), ("back_solar_abs", 0.5)):
+        layers[f] = v
+    layers["solar_transmittance"] = D.NAN
+    surfaces = np.zeros((n, 3), D.SURFACE_DTYPE)
+    surfaces["construction"] = np.arange(n)[:, None]
+    surfaces["area"], surfaces["perimeter"], surfaces["centroid_z"] = 12.0, 14.0, 1.5
+    surfaces["normal"][:, 0] = (0.0, -1.0, 0.0)
+    surfaces["normal"][:, 1] = (1.0, 0.0, 0.0)
+    surfaces["normal"][:, 2] = (0.0, 0.0, 1.0)       # floor seen from the zone
+    surfaces["front_zone"], surfaces["back_zone"] = -1, -1
+    # 0: ordinary exterior wall
+    surfaces["front_kind"][:, 0], surfaces["back_kind"][:, 0], surfaces["back_zone"][:, 0] = D.BOUNDARY_OUTDOOR, D.BOUNDARY_SPACE, 0
+    # 1: Outdoor front, AmbientTemperature back
+    surfaces["front_kind"][:, 1], surfaces["back_kind"][:, 1] = D.BOUNDARY_OUTDOOR, D.BOUNDARY_AMBIENT
+    surfaces["back_ambient_t"][:, 1] = 18.0
+    # 2: zone in front, ground (AmbientTemperature) behind
+    surfaces["front_kind"][:, 2], surfaces["front_zone"][:, 2] = D.BOUNDARY_SPACE, 0
+    surfaces["back_kind"][:, 2] = D.BOUNDARY_AMBIENT
+    surfaces["back_ambient_t"][:, 2] = 12.0
+    for f in ("front_hs_override", "back_hs_override", "front_emissivity_override", "back_emissivity_override"):
+        surfaces[f] = D.NAN
+    volume = rng.uniform(n, 50.0, 300.0)
+    return D.BatchDesc(layers, np.arange(n + 1, dtype=np.int32), np.arange(n + 1, dtype=np.int32),
+                       (np.arange(n + 1) * 3).astype(np.int32), volume, surfaces.reshape(-1), 2)
+
+
+def check_back_ambient(batch_cls, n=12, n_steps=12):
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    _march_and_compare(batch_cls, back_ambient_models(n), n_steps, weather, inputs=inputs[:n_steps], label="back-ambient")
+
+
+def check_infiltration_and_ventilation(batch_cls, n=16, n_steps=12):
+    """model.rs:524-544: infiltration AND ventilation together (ρ·V̇·cp at each stream's own temperature), on shoeboxes
+    (shared zone sums), walls with their own zone (register zone) and double-glazed shoeboxes (general kernel)."""
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    rng = cases.SplitMix64(77)
+    for label, (d, gains) in (("inf+vent shoebox", cases.shoebox_ensemble(n, seed=71, steps_per_hour=2)),
+                              ("inf+vent walls", (cases.wall_ensemble(n, seed=72, mixed_fraction=0.3), None)),
+                              ("inf+vent 2g", cases.shoebox_ensemble(max(2, n // 4), seed=73, steps_per_hour=2,
+                                                                     glazing=cases.double_glazing()))):
+        nz = int(d.model_zone_offset[-1])
+        zin = dict(q_internal=np.zeros(nz) if gains is None else gains,
+                   infiltration_volume=rng.uniform(nz, 0.0, 0.08), infiltration_temperature=rng.uniform(nz, -5.0, 30.0),
+                   ventilation_volume=rng.uniform(nz, 0.0, 0.2), ventilation_temperature=rng.uniform(nz, 14.0, 26.0))
+        zin["ventilation_temperature"][::5] = np.nan      # element absent on some zones
+        zin["infiltration_temperature"][1::7] = np.nan
+        _march_and_compare(batch_cls, d, n_steps, weather, inputs=inputs[:n_steps], zone_inputs=zin, label=label)
+
+
+def check_per_surface_inputs(batch_cls, n=10, n_steps=10):
+    """HB_INPUT_PER_SURFACE: rows [t][surface][4] — each surface of each building gets its own irradiances."""
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    for label, (d, gains) in (("per-surface shoebox", cases.shoebox_ensemble(n, seed=81, steps_per_hour=2)),
+                              ("per-surface walls", (cases.wall_ensemble(3 * n, seed=82, mixed_fraction=0.4), None))):
+        ns = int(d.model_surface_offset[-1])
+        rng = cases.SplitMix64(83)
+        scale = rng.uniform(n_steps * ns, 0.2, 1.3).reshape(n_steps, ns)
+        per = np.zeros((n_steps, ns, 4))
+        per[:, :, 0] = inputs[:n_steps, 0][:, None] * scale
+        per[:, :, 1] = 30.0 * scale
+        per[:, :, 2] = inputs[:n_steps, 2][:, None] * (0.9 + 0.1 * scale)
+        per[:, :, 3] = inputs[:n_steps, 3][:, None]
+        zin = None if gains is None else dict(q_internal=gains)
+        _march_and_compare(batch_cls, d, n_steps, weather, inputs=per, input_mode=2, zone_inputs=zin, label=label)
+
+
+def check_terrain_classes(batch_cls, n_steps=12):
+    """surface.rs:135-166: every TerrainClass (and 'details without terrain') changes the wind-speed modifier of the
+    forced-convection term; one wall + zone per class, same wall otherwise."""
+    base = cases.validation_case("massive_full", 2)
+    terr = [D.TERRAIN_NONE, D.TERRAIN_COUNTRY, D.TERRAIN_SUBURBS, D.TERRAIN_CITY, D.TERRAIN_OCEAN, D.TERRAIN_URBAN]
+    n = len(terr)
+    surfaces = np.repeat(base.surfaces, n)
+    d = D.BatchDesc(base.layers, base.construction_offset, np.arange(n + 1), np.arange(n + 1),
+                    np.repeat(base.zone_volume, n), surfaces, 2, np.array(terr, np.int32))
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    weather[:, 2] += 2.0   # keep some wind
+    got = _march_and_compare(batch_cls, d, n_steps, weather, inputs=inputs[:n_steps], label="terrain")
+    per = got.reshape(n, -1)
+    # NONE == URBAN == SUBURBS (0.22, 370); the others differ
+    assert np.array_equal(per[0], per[5]) and np.array_equal(per[0], per[2])
+    for k in (1, 3, 4):
+        assert np.abs(per[k] - per[0]).max() > 1e-4, k
+
+
+def tilted_glazing_models(steps_per_hour=2):
+    """Double-glazed fenestrations at tilts 0° (roof), 45°, 60°, 75°, 90° and 135° next to an opaque wall, one model per
+    tilt: with the tilt complement taken when t_front > t_back (gas.rs:137) every regime of `nusselt`
+    (gas.rs:197-221: 0-60°, 60°, 60-90°, 90°, 90-180°) runs on the device."""
+    tilts = [0.0, 45.0, 60.0, 75.0, 90.0, 135.0]
+    n = len(tilts)
+    glazing = cases.double_glazing(D.GAS_AIR, 0.02)
+    layers = [cases.concrete(0.15, 0.9, 0.6)] + glazing
+    surfaces = []
+    for k, t in enumerate(tilts):
+        a = math.radians(t)
+        normal = (0.0, -math.sin(a), math.cos(a))
+        surfaces.append(D.surface(0, 10.0, 13.0, (0.0, -1.0, 0.0), 1.5, front=(D.BOUNDARY_OUTDOOR, 0),
+                                  back=(D.BOUNDARY_SPACE, 0)))
+        surfaces.append(D.surface(1, 4.0, 8.0, normal, 2.0, front=(D.BOUNDARY_OUTDOOR, 0), back=(D.BOUNDARY_SPACE, 0),
+                                  is_fenestration=True))
+    return D.BatchDesc(np.array(layers, D.LAYER_DTYPE), [0, 1, 4], np.arange(n + 1), np.arange(n + 1) * 2,
+                       np.full(n, 60.0), np.array(surfaces, D.SURFACE_DTYPE), steps_per_hour)
+
+
+def check_tilted_glazing(batch_cls, n_steps=24):
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    d = tilted_glazing_models()
+    nz = d.n_models
+    # heat some zones above and cool others below the outdoor temperature: both signs of (t_front - t_back)
+    q = np.where(np.arange(nz) % 2 == 0, 1500.0, -1500.0)
+    _march_and_compare(batch_cls, d, n_steps, weather, inputs=inputs[:n_steps], zone_inputs=dict(q_internal=q),
+                       label="tilted glazing")
+    q2 = -q
+    _march_and_compare(batch_cls, d, n_steps, weather, inputs=inputs[:n_steps], zone_inputs=dict(q_internal=q2),
+                       label="tilted glazing (signs swapped)")
+
+
+def check_marches_again_after_failure(batch_cls):
+    """The reference's Err / panic belongs to ONE march call: after a reported physics failure, set_state with a sane
+    state and march again must succeed (status words are per call)."""
+    from heat_b200 import HeatB200Error
+
+    b = batch_cls(cases.validation_case("massive_full"))
+    s0 = b.get_state()
+    try:
+        b.march_series(1, np.array([[float("nan"), 0.0, 1.0]]))
+        raise AssertionError("NaN weather must be reported")
+    except HeatB200Error as e:
+        assert e.status == 3
+    b.set_state(s0)
+    b.march_series(3, np.array([[10.0, 90.0, 2.0]] * 3))
+    s1 = b.get_state()
+    assert np.all(np.isfinite(s1)) and b.reduce().status_flags == 0
+    b2 = batch_cls(cases.validation_case("massive_full"))
+    b2.march_series(3, np.array([[10.0, 90.0, 2.0]] * 3))
+    assert np.array_equal(b2.get_state(), s1)

@@ -54,6 +54,7 @@ def _worker(rank, world, port, q):
         shard = full.slice_models(m0, m1)
         state = _march(shard)
         local = D.stats_from_state(state, _layout(shard))
+        local.status_flags = 1 if rank == 0 else 8   # different status bits per rank: every rank must end with the OR
         total = D.combine_stats(local)
         t = D.max_over_ranks([float(rank + 1)])
         u = D.sum_over_ranks([float(m1 - m0)])
@@ -98,3 +99,4 @@ def test_two_rank_gloo_equals_single_process():
         assert abs(total.sum_node_t - ref.sum_node_t) <= 1e-9 * abs(ref.sum_node_t)
         assert abs(total.sum_zone_t - ref.sum_zone_t) <= 1e-9 * abs(ref.sum_zone_t)
         assert tmax == 2.0 and usum == float(N_WALLS)
+        assert total.status_flags == 9

@@ -124,3 +124,34 @@ def test_emulated_two_node_end_chunks():
 
 def test_emulated_walls_beyond_254_nodes():
     pc.check_walls_beyond_254_nodes(emu_py.EmuBatch)
+
+
+# ---- round 2 cases (the same checks the GPU tests run) ----
+@pytest.mark.parametrize("kind,n", [("walls", 48), ("mixed", 48), ("buildings", 8)])
+def test_emulated_benchmarked_ensembles_prefix(kind, n):
+    """The benchmarked generators over 5 days (the GPU test runs the whole year)."""
+    pc.check_full_horizon_ensemble(emu_py.EmuBatch, kind, n, hours=120)
+
+
+def test_emulated_negative_front_solar():
+    pc.check_negative_front_solar(emu_py.EmuBatch)
+
+
+def test_emulated_back_ambient():
+    pc.check_back_ambient(emu_py.EmuBatch)
+
+
+def test_emulated_infiltration_and_ventilation():
+    pc.check_infiltration_and_ventilation(emu_py.EmuBatch)
+
+
+def test_emulated_per_surface_inputs():
+    pc.check_per_surface_inputs(emu_py.EmuBatch)
+
+
+def test_emulated_terrain_classes():
+    pc.check_terrain_classes(emu_py.EmuBatch)
+
+
+def test_emulated_tilted_glazing():
+    pc.check_tilted_glazing(emu_py.EmuBatch)
