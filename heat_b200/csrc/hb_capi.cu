@@ -191,7 +191,8 @@ void build_device(hb_handle* h) {
     std::map<std::tuple<int, int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -NL, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
-        const int var = (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5
+        const int var = (t.flags & hb::TILE_WARP) ? ((t.flags & hb::TILE_END) ? 9 : 8)   // warp tiles (hb_wtile_kernel)
+                        : (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5
                         : (t.flags & hb::TILE_END) ? ((t.flags & hb::TILE_SIMPLE) ? 7 : 3) : ((t.flags & hb::TILE_SIMPLE) ? 6 : 0);
         // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
         by[{s_class(t.S), var == 1 || var == 2 ? 0 : 1, -t.NL, -t.G, var, t.W}].push_back((int32_t)ti);
@@ -226,6 +227,11 @@ namespace hb {
     cudaError_t launch_march_##N(int var, int W, int nl, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
 HB_DECL_TIER(1) HB_DECL_TIER(2) HB_DECL_TIER(4) HB_DECL_TIER(8) HB_DECL_TIER(16) HB_DECL_TIER(32)
 #undef HB_DECL_TIER
+// warp tiles: mode = hb_face_kernel's lean modes (0 all-massive, 1 no-mass ends)
+#define HB_DECL_WTIER(N) \
+    cudaError_t launch_wtile_##N(int mode, int nl, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids);
+HB_DECL_WTIER(1) HB_DECL_WTIER(2) HB_DECL_WTIER(4) HB_DECL_WTIER(8) HB_DECL_WTIER(16) HB_DECL_WTIER(32)
+#undef HB_DECL_WTIER
 void launch_reduce(int grid, cudaStream_t st, const DevView& V, int n_tiles, double* out, unsigned long long* iout);
 void launch_dfma_probe(int blocks, int threads, double* out, int iters, double seed);
 void launch_fill(cudaStream_t st, double* p, int64_t n, double v);
@@ -268,7 +274,18 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         }
         cudaError_t e;
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
-        const int var = (g.var == 0 || g.var == 3 || g.var >= 5) && !P.single_site ? 4 : g.var;
+        const int var = (g.var == 0 || g.var == 3 || (g.var >= 5 && g.var < 8)) && !P.single_site ? 4 : g.var;
+        if (var >= 8) {   // warp tiles (per-site weather is handled inside the kernel)
+            const int mode = var == 9 ? 1 : 0;
+            switch (g.G) {
+                case 1: e = hb::launch_wtile_1(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                case 2: e = hb::launch_wtile_2(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                case 4: e = hb::launch_wtile_4(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                case 8: e = hb::launch_wtile_8(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                case 16: e = hb::launch_wtile_16(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                default: e = hb::launch_wtile_32(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            }
+        } else
         switch (g.G) {
             case 1: e = hb::launch_march_1(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
             case 2: e = hb::launch_march_2(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;

@@ -273,7 +273,7 @@ inline bool is_pane(const SurfacePlan& P) {
            P.nomass_chunks[1] == 2;
 }
 constexpr int kBulkSubsteps = 56;   // below: tiles are scheduled for throughput, not for latency (hb_capi.cu S bins)
-constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE;   // tiles are uniform in these
+constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE | TILE_WARP;   // tiles are uniform in these
 
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
@@ -404,6 +404,18 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             const hb_surface& s = B.surfaces[M.surface_begin];
             if (s.back_kind == HB_BOUNDARY_SPACE && s.front_kind != HB_BOUNDARY_SPACE) M.variant |= TILE_SIMPLE;
         }
+        M.G = group_of_nodes(M.nmax);
+        // A wall with its own zone behind it, all-massive or with no-mass chunks at its ends only: the warp-tile kernel
+        // (no block barrier; HB_NO_WTILE=1 keeps the block-tile kernels for A/B measurements)
+        static const bool no_wtile = std::getenv("HB_NO_WTILE") != nullptr;
+        if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) && M.nmax <= kWtMaxNodes) {
+            const WtGeom* g = wt_geom_of_nodes(M.nmax);
+            M.variant |= TILE_WARP;
+            M.G = g->G;
+            M.NL = g->NL;
+            M.walls = 32 / g->G;
+            continue;
+        }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)
             fail("model larger than one tile (" + std::to_string(Wmax) + " surfaces / zones at this wall size)");
@@ -422,7 +434,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
     auto key = [&](int m) {
         const ModelPlan& M = B.models[m];
-        return std::make_tuple(group_of_nodes(M.nmax), M.NL, M.variant & kTileKey, M.walls, M.dt_subdivisions);
+        return std::make_tuple(M.G, M.NL, M.variant & kTileKey, M.walls, M.dt_subdivisions);
     };
     if (d->n_models > 1)
         std::stable_sort(B.model_order.begin(), B.model_order.end(), [&](int a, int b) { return key(a) < key(b); });
@@ -453,7 +465,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     for (int pos = 0; pos < d->n_models; ++pos) {
         const int m = B.model_order[pos];
         const ModelPlan& M = B.models[m];
-        const int G = group_of_nodes(M.nmax);
+        const int G = M.G;
         const int W = M.walls;
         const int variant = M.variant & kTileKey;
         if (open && (cur.G != G || cur.NL != M.NL || cur.W != W || (cur.flags & kTileKey) != variant || cur.S != M.dt_subdivisions ||

@@ -57,6 +57,19 @@ constexpr double kMassiveThreshold = 1e-5; // discretization.rs:149,155
 constexpr double kInitialH = 1.739658084820765;  // surface_trait.rs:231,248
 constexpr double kInitialT = 22.0;               // surface_trait.rs:365-370, zone.rs:45-50
 
+// ---- warp tiles (hb_wtile_kernel): one warp = one tile of 32 / G walls, NL NODES per lane, no ghost slots ----------
+// Geometries in order of capacity G·NL; a wall takes the first one that holds it (cost per wall and sub-step in FP64
+// warp instructions ≈ (16.5·NL + 115·faces per lane)·G / 32 grows with the capacity, so the smallest fit is the cheapest).
+struct WtGeom { int cap, G, NL; };
+constexpr WtGeom kWtGeoms[] = {{8, 1, 8},    {12, 1, 12},  {16, 2, 8},    {24, 2, 12},   {32, 2, 16},  {48, 4, 12}, {64, 4, 16},
+                               {96, 8, 12},  {128, 8, 16}, {192, 16, 12}, {256, 16, 16}, {384, 32, 12}, {512, 32, 16}};
+constexpr int kWtMaxNodes = 512;
+inline const WtGeom* wt_geom_of_nodes(int n) {
+    for (const WtGeom& g : kWtGeoms)
+        if (n <= g.cap) return &g;
+    return nullptr;
+}
+
 struct CavityParams {   // cavity.rs:28-50
     int32_t node;       // link between node and node+1
     int32_t gas;
@@ -91,6 +104,7 @@ struct ModelPlan {
     int32_t variant = 0;             // TILE_* flags needed by its surfaces
     int32_t walls = 0;               // wall slots of the tiles this model goes into
     int32_t NL = kNL;                // slots per lane of those tiles
+    int32_t G = 1;                   // lanes per wall of those tiles
 };
 
 enum : int32_t {
@@ -101,6 +115,7 @@ enum : int32_t {
     TILE_PANE = 32,  // face-kernel tile with single-pane windows (two no-mass nodes solved jointly by the face lanes)
     TILE_SIMPLE = 64,  // face-kernel tile whose models are one wall with its own zone behind it (zone j <-> wall j)
     TILE_GEN = 16,   // face-kernel tile with a film-coefficient override or an AmbientTemperature back boundary
+    TILE_WARP = 128, // warp tile (hb_wtile_kernel): G·W = 32, NL nodes per lane, node i in slot i (no ghost slots)
 };
 
 // A tile = the models one CUDA block marches.
@@ -151,7 +166,7 @@ struct BatchPlan {
     int64_t slab_index(int64_t gd, int node) const {
         const Tile& t = tiles[surface_tile[gd]];
         const int wl = dev_surface_of[gd] - t.surface_begin;
-        const int slot = node + 1;
+        const int slot = (t.flags & TILE_WARP) ? node : node + 1;   // block tiles keep slot 0 for the front ghost
         return t.node_offset + (int64_t)(slot % t.NL) * (t.G * t.W) + (int64_t)wl * t.G + slot / t.NL;
     }
 };

@@ -1026,7 +1026,8 @@ __global__ void __launch_bounds__(kReduceBlock) hb_reduce_kernel(DevView V, int 
             const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
             for (int i = 0; i < tile.NL; ++i) {
                 const int slot = part * tile.NL + i;
-                if (slot >= 1 && slot <= n) {
+                // block tiles: slots 1..n hold the nodes (0 and n+1 are ghosts); warp tiles: slots 0..n-1
+                if ((tile.flags & TILE_WARP) ? slot < n : (slot >= 1 && slot <= n)) {
                     const double v = V.nodeT[tile.node_offset + (int64_t)i * TPB + th];
                     sn += v;
                     mnn = fmin(mnn, v);

@@ -1,0 +1,441 @@
+// hb_wtile.cuh — K1/K2 "warp tile" kernel (sm_100a): one WARP marches one tile, with no block barrier and no
+// shared-memory hand-off anywhere in the sub-step loop.
+//
+// Why: the block-tile kernel (hb_face_kernel) is bound by the dependent chain  node march → face physics → node march
+// of a tile: three of a tile's four warps wait at the block barrier while one warp runs post → zone → pre
+// (profiles/r1j_summary.md: 2.9 warps stalled on the barrier per issued instruction, FP64 pipe 34 % busy), and the
+// register file admits only four such tiles per SM.  Here every warp is its own tile:
+//   * a wall is owned by G consecutive lanes (G = 1 … 32), each lane keeping NL (8, 12 or 16) NODES in registers —
+//     no ghost slots: the film links enter through the halo values of the first / last node (capacity n <= G·NL);
+//   * the FRONT face of a wall is evaluated by the first lane of its group, the BACK face (and, for a wall with its own
+//     zone, the zone) by the last lane (G = 1: both by the one lane) — the face results reach the node lanes through
+//     two warp shuffles, the end-node temperatures come back through a register mux + one shuffle;
+//   * warps never wait for each other, so the FP64 pipe of a sub-partition is filled by whichever of its 2–4 resident
+//     warps has an instruction ready: the kernel is bound by FP64 issue, not by a barrier chain.
+// Arithmetic and operation order of the face physics are those of hb_face_kernel's lean modes (hb_math.cuh):
+// model.rs:79-96,145-169,489-597,650-674, surface.rs:37-46,596-717,790-898,916-948, convection.rs:87-168.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "hb_math.cuh"
+
+namespace hb {
+
+// registers per thread each geometry is compiled for: 168 / 200 / 224 / 255 registers = 12 / 10 / 9 / 8 resident warps
+// per SM.  (__maxnreg__, not the min-blocks argument of __launch_bounds__: for 32-thread blocks ptxas caps that form at
+// 168 registers whatever the block count asked for.)
+__host__ __device__ constexpr int wt_max_regs(int G, int NL) {
+    return G == 1 ? (NL <= 8 ? 200 : NL <= 12 ? 224 : 255) : (NL <= 8 ? 168 : NL <= 12 ? 200 : 224);
+}
+
+// T[k], k lane-dependent, as a select tree (registers cannot be indexed)
+template <int NL>
+__device__ __forceinline__ double wt_mux(const double (&T)[NL], int k) {
+    constexpr int P = NL <= 8 ? 8 : 16;
+    static_assert(NL <= 16, "wt_mux covers 16 slots");
+    double m[P / 2];
+#pragma unroll
+    for (int i = 0; i < P / 2; ++i) {
+        const double a = T[2 * i < NL ? 2 * i : NL - 1], b = T[2 * i + 1 < NL ? 2 * i + 1 : NL - 1];
+        m[i] = (k & 1) ? b : a;
+    }
+#pragma unroll
+    for (int len = P / 4, bit = 2; len >= 1; len >>= 1, bit <<= 1) {
+#pragma unroll
+        for (int i = 0; i < len; ++i) m[i] = (k & bit) ? m[2 * i + 1] : m[2 * i];
+    }
+    return m[0];
+}
+
+// One sub-step of RK4 (surface.rs:228-308 in Horner / flux form, see node_rk4 in hb_kernels.cuh) for a lane's NL nodes.
+// `first`: the lane holds node 0 — its left neighbour is the front ghost (temperature gf in the first sweep, 0 later:
+// the ghost does not move); `edge`: the lane's last slot is the wall's last node — its right neighbour is the back ghost.
+template <int G, int NL>
+__device__ __forceinline__ void wt_rk4(double (&T)[NL], const double (&A)[NL], const double (&B)[NL], bool first,
+                                       double gf, bool edge, double gb) {
+    constexpr unsigned FULL = 0xffffffffu;
+    double X[NL];
+    double left = gf, right = gb;
+    if constexpr (G > 1) {
+        const double l = __shfl_up_sync(FULL, T[NL - 1], 1, G), r = __shfl_down_sync(FULL, T[0], 1, G);
+        left = first ? gf : l;
+        right = edge ? gb : r;
+    }
+    // sweep 1: X = M·T
+    {
+        const double d0 = T[1] - T[0], dl = T[0] - left;
+        const double dr = right - T[NL - 1], dm = T[NL - 1] - T[NL - 2];
+        X[0] = A[0] * d0 - B[0] * dl;
+        X[NL - 1] = A[NL - 1] * dr - B[NL - 1] * dm;
+        if constexpr (G > 1) {
+            const double l = __shfl_up_sync(FULL, X[NL - 1], 1, G), r = __shfl_down_sync(FULL, X[0], 1, G);
+            left = first ? 0. : l;
+            right = edge ? 0. : r;
+        } else {
+            left = 0.;
+            right = 0.;
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double dnext = T[i + 1] - T[i];
+            X[i] = A[i] * dnext - B[i] * dprev;
+            dprev = dnext;
+        }
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] += X[i];
+    }
+    // sweeps 2-4: X ← M·X, T += c·X
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double c = k == 0 ? 1. / 2. : k == 1 ? 1. / 6. : 1. / 24.;
+        const double d0 = X[1] - X[0], dl = X[0] - left;
+        const double dr = right - X[NL - 1], dm = X[NL - 1] - X[NL - 2];
+        const double x0 = A[0] * d0 - B[0] * dl;
+        const double xl = A[NL - 1] * dr - B[NL - 1] * dm;
+        if constexpr (G > 1) {
+            if (k < 2) {
+                const double l = __shfl_up_sync(FULL, xl, 1, G), r = __shfl_down_sync(FULL, x0, 1, G);
+                left = first ? 0. : l;
+                right = edge ? 0. : r;
+            }
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double dnext = (i + 1 == NL - 1 ? X[NL - 1] : X[i + 1]) - X[i];
+            X[i] = A[i] * dnext - B[i] * dprev;
+            dprev = dnext;
+        }
+        X[0] = x0;
+        X[NL - 1] = xl;
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] = fma(c, X[i], T[i]);
+    }
+}
+
+// Results of one face's pre-march evaluation, handed to the node lanes.
+struct WtLinks {
+    double ghost, link;   // equivalent air temperature and h·dt/C of the end node
+    double t_in;          // two-node no-mass end chunk: the chunk's inner node
+};
+
+template <int G, int NL, int MODE, bool SIMPLE>
+__global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+    constexpr bool END = MODE != kFaceLean;   // no-mass chunks of one or two nodes at the ends of walls are possible
+    constexpr int NF = G == 1 ? 2 : 1;        // faces evaluated by a face lane
+    constexpr unsigned FULL = 0xffffffffu;
+    static_assert(SIMPLE, "zones shared by several walls: not in this kernel yet");
+    static_assert(G >= 1 && G <= 32 && (G & (G - 1)) == 0 && NL >= 4, "geometry");
+    extern __shared__ double s_dyn[];
+    SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn);   // [S] sub-step weather of the current main step
+
+    const Tile tile = V.tiles[tile_ids[blockIdx.x]];
+    const int lane = threadIdx.x;
+    const int64_t NS = V.n_dev_surfaces;
+    const int S = tile.S;
+    const double dt = tile.dt;
+
+    // ---- node role ----
+    const int wl = lane / G, part = lane % G, base = lane - part;
+    const int64_t sg = (int64_t)tile.surface_begin + wl;
+    const int n = V.n_nodes[sg];
+    const int last = n - 1 - part * NL;   // lane-local index of the wall's last node (this lane holds it iff 0 <= last < NL)
+    const bool first = part == 0, edge = last == NL - 1;
+    const int nm1 = n > 0 ? n - 1 : 0, nm2 = n > 1 ? n - 2 : 0, nm3 = n > 2 ? n - 3 : 0;
+    const int wflags = V.flags[sg];
+    const bool nmf = END && ((wflags >> 10) & 1), nmb = END && ((wflags >> 11) & 1);
+    const bool nmf2 = END && ((wflags >> 13) & 1), nmb2 = END && ((wflags >> 14) & 1);
+    double T[NL], A[NL], B[NL];
+    {
+        const int64_t o = tile.node_offset + lane;
+#pragma unroll
+        for (int i = 0; i < NL; ++i) {
+            T[i] = V.nodeT[o + (int64_t)i * 32];
+            A[i] = V.coefA[o + (int64_t)i * 32];
+            B[i] = V.coefB[o + (int64_t)i * 32];
+        }
+    }
+
+    // ---- face role: front face on the first lane of the group, back face (and the zone) on the last ----
+    const bool bk = part == G - 1;
+    const bool face_lane = first || bk;
+    const bool fwall = face_lane && n > 0;
+    const bool szone = bk && wl < tile.n_zones;
+    const int64_t sgz = (int64_t)tile.zone_begin + wl;
+    FaceC c[NF];
+    FaceS w[NF];
+    double ir_state[NF];
+    double zT = 0., za0 = 0., zb0 = 0., zvol = 1.;
+    ZoneC zc{};
+    bool simple_ok = true;
+    if (szone) {
+        zc.vol = V.zvol[sgz]; zc.q = V.zq[sgz]; zc.inf_v = V.zinf_v[sgz]; zc.inf_t = V.zinf_t[sgz];
+        zc.vent_v = V.zvent_v[sgz]; zc.vent_t = V.zvent_t[sgz]; zc.sb = V.z_surf_begin[sgz]; zc.se = V.z_surf_end[sgz];
+        zT = V.zoneT[sgz];
+        zone_sources(zc, za0, zb0);
+        zvol = zc.vol;
+        simple_ok = zc.sb == wl && zc.se == wl + 1;
+    }
+#pragma unroll
+    for (int f = 0; f < NF; ++f) {
+        const bool back = G == 1 ? f == 1 : bk;
+        const int kf = back ? 1 : 0;
+        w[f] = FaceS{};
+        if (fwall) {
+            WallC wc;
+            load_wallc(V, sg, P.single_site != 0, wc);
+            const bool nm = END && ((wflags >> (back ? 11 : 10)) & 1);
+            const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
+            load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, c[f], false, 0., 0., nm2f, back ? V.u_b2[sg] : V.u_f2[sg]);
+            w[f].h = V.sc[(0 + kf) * NS + sg]; w[f].flow = V.sc[(2 + kf) * NS + sg];
+            w[f].sol = V.sc[(4 + kf) * NS + sg]; w[f].ir = V.sc[(6 + kf) * NS + sg];
+            // one wall with its own zone behind it (TILE_SIMPLE, decided on the host): re-checked here
+            if (back) simple_ok = simple_ok && wc.zb == wl && wc.zf < 0 && szone;
+        } else {
+            c[f] = FaceC{};   // the lean face path runs unpredicated: lanes without a face work on zeros
+            if (back && face_lane) simple_ok = simple_ok && !szone;
+        }
+        ir_state[f] = w[f].ir;
+    }
+    if (!__all_sync(FULL, simple_ok) && lane == 0) atomicOr(&V.status[tile.surface_begin], ST_NAN_ZONE);
+
+    // end-node temperatures: node 0 (and 1, 2) on the first lane, node n-1 (n-2, n-3) wherever they live
+    double ts_f = T[0], t1_f = T[1], t2_f = T[2];
+    double ts_b, t1_b = 0., t2_b = 0.;
+    auto gather_back = [&]() {
+        const double m0 = wt_mux<NL>(T, nm1 % NL);
+        ts_b = G == 1 ? m0 : __shfl_sync(FULL, m0, base + nm1 / NL);
+        if constexpr (END) {
+            const double m1 = wt_mux<NL>(T, nm2 % NL), m2 = wt_mux<NL>(T, nm3 % NL);
+            t1_b = G == 1 ? m1 : __shfl_sync(FULL, m1, base + nm2 / NL);
+            t2_b = G == 1 ? m2 : __shfl_sync(FULL, m2, base + nm3 / NL);
+        }
+    };
+    gather_back();
+#pragma unroll
+    for (int f = 0; f < NF; ++f) {
+        const bool back = G == 1 ? f == 1 : bk;
+        w[f].ts = back ? ts_b : ts_f;
+    }
+
+    // sub-step weather of main step `step` (the whole warp), single-site tables
+    auto fill_weather = [&](int step) {
+        if (!P.single_site) return;
+        const double* w0 = P.weather + (int64_t)step * 3;
+        if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) w0 = P.weather + (int64_t)step * S * 3;
+        for (int s = lane; s < S; s += 32) {
+            double t_out, wdir, wspeed;
+            if (P.weather_mode == HB_WEATHER_LINEAR) {
+                const double f = (double)(s + 1) / (double)S;
+                t_out = lerp_rn(w0[0], w0[3], f);
+                wdir = lerp_rn(w0[1], w0[4], f);
+                wspeed = lerp_rn(w0[2], w0[5], f);
+            } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+                t_out = w0[3 * s + 0]; wdir = w0[3 * s + 1]; wspeed = w0[3 * s + 2];
+            } else {
+                t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+            }
+            sub_weather(t_out, wdir, wspeed, s_w[s]);
+        }
+        __syncwarp();
+    };
+    // per-site weather (several weather tables in one batch): evaluated by the face lane itself
+    auto site_weather = [&](const FaceC& cf, int step, int s, SubWeather& sw) {
+        const double* wtab = P.weather + (int64_t)cf.site * P.weather_rows * 3;
+        const double* w0 = wtab + (int64_t)step * 3;
+        double t_out, wdir, wspeed;
+        if (P.weather_mode == HB_WEATHER_LINEAR) {
+            const double f = (double)(s + 1) / (double)S;
+            t_out = lerp_rn(w0[0], w0[3], f);
+            wdir = lerp_rn(w0[1], w0[4], f);
+            wspeed = lerp_rn(w0[2], w0[5], f);
+        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+            w0 = wtab + ((int64_t)step * S + s) * 3;
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        } else {
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        }
+        sub_weather(t_out, wdir, wspeed, sw);
+    };
+    // what the caller writes into SimulationState before a main step + the per-step derived quantities
+    auto main_step_inputs = [&](int step) {
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const bool back = G == 1 ? f == 1 : bk;
+            const int kf = back ? 1 : 0;
+            if (P.input_mode != HB_INPUT_STATE) {
+                const double* in = P.input_mode == HB_INPUT_SITE
+                                       ? P.inputs + ((int64_t)c[f].site * P.n_steps + step) * 4
+                                       : P.inputs + ((int64_t)step * P.n_desc_surfaces + c[f].desc_index) * 4;
+                w[f].sol = in[kf];
+                w[f].ir = in[2 + kf];
+                if (!back && P.ir_mode == HB_IR_NET_GAIN) {
+                    // validate_wall_heat_transfer.rs:689-699 (front face only, as in the reference driver)
+                    if (c[f].eps > 1e-3) {
+                        const double tk = w[f].ts + 273.15;
+                        const double tk2 = tk * tk;
+                        w[f].ir = w[f].ir / c[f].area / c[f].eps + kSigma * (tk2 * tk2);
+                    } else {
+                        w[f].ir = ir_state[f];
+                    }
+                }
+            }
+            face_begin_main_step(c[f], w[f]);
+        }
+    };
+    // border conditions of sub-step s of main step `step` (old surface temperatures) → links for the node lanes
+    WtLinks lk[NF];
+    auto pre = [&](int step, int s) {
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const bool back = G == 1 ? f == 1 : bk;
+            const FaceC& cf = c[f];
+            FaceS& wf = w[f];
+            SubWeather sw;
+            if (P.single_site) sw = s_w[s]; else site_weather(cf, step, s, sw);
+            const int fl = cf.fl;
+            const bool is_out = fl & FC_OUT;
+            const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(cf.nx, sw.sin_wd), mul_rn(cf.ny, sw.cos_wd)) > 0.0);
+            wf.forced = cf.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
+            wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? zT : cf.amb;
+            const double trad = is_out ? wf.trad_out : wf.air;
+            const double hn = tarp_lean(wf.air - wf.ts, cf.kpos, cf.kneg);
+            const double h = is_out ? hn + wf.forced : hn;
+            if (h != h) wf.status |= ST_NAN_H;
+            const double xr = 273.15 + (trad + wf.ts) / 2.;
+            const double rad = cf.eps4s * ((xr * xr) * xr);
+            const double asol = cf.alpha_end * wf.solar;
+            lk[f].t_in = 0.;
+            if constexpr (END) {
+                if (fl & FC_NM2) {
+                    double t_in = back ? t1_b : t1_f;
+                    solve_end_pair<true>(back, wf.air, h, rad, trad, asol, cf.u_nb, cf.u_nb2, back ? t2_b : t2_f, wf.ts,
+                                         t_in, wf.nm_iters, wf.status);
+                    lk[f].t_in = t_in;
+                } else if (fl & FC_NM) {
+                    wf.ts = solve_end_node<true>(wf.air, h, rad, trad, cf.u_nb, back ? t1_b : t1_f, asol, wf.ts,
+                                                 wf.nm_iters, wf.status);
+                }
+            }
+            const double hs = h > 1e-12 ? h : 1e-12;
+            lk[f].ghost = wf.air + (rad * (trad - wf.ts) + asol) * rcp_lean(hs);
+            lk[f].link = hs * cf.v_end;
+        }
+    };
+
+    int rec = 0;
+    for (int step = 0; step < P.n_steps; ++step) {
+        fill_weather(step);
+        main_step_inputs(step);
+        if (P.zone_gain != nullptr && szone) {   // scheduled gains: this main step's q, sources re-summed in the reference's order
+            zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + sgz];
+            zone_sources(zc, za0, zb0);
+        }
+        for (int s = 0; s < S; ++s) {
+            // ================= face role: border conditions with the old surface temperatures =================
+            pre(step, s);
+            // ================= face lanes → node lanes =================
+            const double gf = lk[0].ghost, lf = lk[0].link;
+            double gb = lk[NF - 1].ghost, lb = lk[NF - 1].link;
+            double tf0 = w[0].ts, tf1 = lk[0].t_in, tb0 = w[NF - 1].ts, tb1 = lk[NF - 1].t_in;
+            if constexpr (G > 1) {
+                gb = __shfl_sync(FULL, gb, base + G - 1);
+                lb = __shfl_sync(FULL, lb, base + G - 1);
+                if constexpr (END) {
+                    tb0 = __shfl_sync(FULL, tb0, base + G - 1);
+                    tb1 = __shfl_sync(FULL, tb1, base + G - 1);
+                }
+            }
+            B[0] = first ? lf : B[0];
+            if constexpr (END) {
+                T[0] = (first && nmf) ? tf0 : T[0];
+                T[1] = (first && nmf2) ? tf1 : T[1];
+            }
+#pragma unroll
+            for (int i = 0; i < NL; ++i) {
+                A[i] = i == last ? lb : A[i];
+                if constexpr (END) {
+                    T[i] = (i == last && nmb) ? tb0 : T[i];
+                    T[i] = (i == last - 1 && nmb2) ? tb1 : T[i];
+                }
+                T[i] = i == last + 1 ? gb : T[i];   // the slot behind the last node stands for the back ghost
+            }
+            // ================= node role: RK4 of the massive nodes =================
+            wt_rk4<G, NL>(T, A, B, first, gf, edge, gb);
+            // ================= node lanes → face lanes =================
+            ts_f = T[0];
+            if constexpr (END) {
+                t1_f = T[1];
+                t2_f = T[2];
+            }
+            gather_back();
+            // ================= face role: new film coefficients, flows, zone =================
+            double hA_b = 0., hAT_b = 0.;
+#pragma unroll
+            for (int f = 0; f < NF; ++f) {
+                const bool back = G == 1 ? f == 1 : bk;
+                const FaceC& cf = c[f];
+                FaceS& wf = w[f];
+                const double ts = back ? ts_b : ts_f;
+                const double hn = tarp_lean(wf.air - ts, cf.kpos, cf.kneg);
+                const double h = (cf.fl & FC_OUT) ? hn + wf.forced : hn;
+                if (h != h) wf.status |= ST_NAN_H;
+                wf.ts = ts;
+                wf.h = h;
+                wf.flow = (ts - wf.air) * h;
+                wf.e += wf.flow * cf.area * dt;
+                if (back) {
+                    hA_b = h * cf.area;
+                    hAT_b = hA_b * ts;
+                }
+            }
+            {   // the lane's own wall is the zone's only surface (its back face): model.rs:489-597, 650-674
+                const double inv_cc = zone_inv_c_t<true>(zvol, zT);
+                const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT_b, zb0 + hA_b);
+                if (szone) {
+                    if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
+                    zT = tn;
+                }
+            }
+        }
+
+        if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
+            if (P.zone_rec && szone) P.zone_rec[(int64_t)rec * V.n_dev_zones + sgz] = zT;
+            if (P.node_rec) {
+#pragma unroll
+                for (int i = 0; i < NL; ++i)
+                    P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * 32 + lane] = T[i];
+                if (fwall) {
+                    double* rr = P.sc_rec + (int64_t)rec * 8 * NS;
+#pragma unroll
+                    for (int f = 0; f < NF; ++f) {
+                        const int kf = (G == 1 ? f == 1 : bk) ? 1 : 0;
+                        rr[(0 + kf) * NS + sg] = w[f].h; rr[(2 + kf) * NS + sg] = w[f].flow;
+                        rr[(4 + kf) * NS + sg] = w[f].sol; rr[(6 + kf) * NS + sg] = w[f].ir;
+                    }
+                }
+            }
+            ++rec;
+        }
+    }
+
+    // ---- write the state back ----
+#pragma unroll
+    for (int i = 0; i < NL; ++i) V.nodeT[tile.node_offset + (int64_t)i * 32 + lane] = T[i];
+    if (fwall) {
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const bool back = G == 1 ? f == 1 : bk;
+            const int kf = back ? 1 : 0;
+            V.sc[(0 + kf) * NS + sg] = w[f].h; V.sc[(2 + kf) * NS + sg] = w[f].flow;
+            V.sc[(4 + kf) * NS + sg] = w[f].sol; V.sc[(6 + kf) * NS + sg] = w[f].ir;
+            if (back) V.energy_b[sg] += w[f].e; else V.energy_f[sg] += w[f].e;
+            if (w[f].nm_iters) atomicAdd(&V.nm_iters[sg], w[f].nm_iters);
+            if (w[f].status) atomicOr(&V.status[sg], w[f].status);
+        }
+    }
+    if (szone) V.zoneT[sgz] = zT;
+}
+
+}  // namespace hb

@@ -17,6 +17,7 @@ using namespace hb;
 
 namespace {
 std::string g_err;
+struct WallLinksEmu { double ghost, link, t_in; };   // hb_wtile.cuh: WtLinks
 
 void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* zone_rec_base) {
     const int G = tile.G, W = tile.W, TPB = G * W, NL = kNL, ROW = G * NL + 1;
@@ -281,6 +282,316 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
         V.status[sg] |= w.status;
     }
     for (int t = 0; t < tile.n_zones; ++t) V.zoneT[(int64_t)tile.zone_begin + t] = zT[t];
+}
+
+// hb_wtile_kernel's data flow (hb_wtile.cuh): one warp = one tile, G lanes per wall, NL NODES per lane (no ghost slots),
+// front face on the first lane of a group, back face + zone on the last; shuffles become array reads.
+void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, double* zone_rec_base) {
+    const int G = tile.G, NL = tile.NL, NF = G == 1 ? 2 : 1;
+    const bool END = tile.flags & TILE_END;
+    const int S = tile.S;
+    const double dt = tile.dt;
+    const int64_t NS = V.n_dev_surfaces;
+    if (G * tile.W != 32 || !(tile.flags & TILE_SIMPLE)) throw std::runtime_error("emu: warp tile shape");
+    std::vector<double> T(32 * NL), A(32 * NL), B(32 * NL), X(32 * NL);
+    struct Lane {
+        int wl, part, base, n, last, nm1, nm2, nm3;
+        bool first, edge, bk, face_lane, fwall, szone, nmf, nmb, nmf2, nmb2;
+        int64_t sg, sgz;
+        FaceC c[2];
+        FaceS w[2];
+        double ir_state[2];
+        WallLinksEmu lk[2];
+        double zT, za0, zb0, zvol;
+        ZoneC zc;
+        double ts_f, t1_f, t2_f, ts_b, t1_b, t2_b;
+    };
+    std::vector<Lane> L(32);
+    std::vector<SubWeather> swt(kMaxSubsteps);
+    for (int lane = 0; lane < 32; ++lane)
+        for (int i = 0; i < NL; ++i) {
+            const int64_t o = tile.node_offset + (int64_t)i * 32 + lane;
+            T[lane * NL + i] = V.nodeT[o];
+            A[lane * NL + i] = V.coefA[o];
+            B[lane * NL + i] = V.coefB[o];
+        }
+    auto gather_back = [&]() {
+        for (int lane = 0; lane < 32; ++lane) {
+            Lane& l = L[lane];
+            l.ts_f = T[lane * NL + 0]; l.t1_f = T[lane * NL + 1]; l.t2_f = T[lane * NL + 2];
+            l.ts_b = T[(l.base + l.nm1 / NL) * NL + l.nm1 % NL];
+            l.t1_b = T[(l.base + l.nm2 / NL) * NL + l.nm2 % NL];
+            l.t2_b = T[(l.base + l.nm3 / NL) * NL + l.nm3 % NL];
+        }
+    };
+    for (int lane = 0; lane < 32; ++lane) {
+        Lane& l = L[lane];
+        l.wl = lane / G; l.part = lane % G; l.base = lane - l.part;
+        l.sg = (int64_t)tile.surface_begin + l.wl;
+        l.n = V.n_nodes[l.sg];
+        l.last = l.n - 1 - l.part * NL;
+        l.first = l.part == 0; l.edge = l.last == NL - 1;
+        l.nm1 = l.n > 0 ? l.n - 1 : 0; l.nm2 = l.n > 1 ? l.n - 2 : 0; l.nm3 = l.n > 2 ? l.n - 3 : 0;
+        const int wflags = V.flags[l.sg];
+        l.nmf = END && ((wflags >> 10) & 1); l.nmb = END && ((wflags >> 11) & 1);
+        l.nmf2 = END && ((wflags >> 13) & 1); l.nmb2 = END && ((wflags >> 14) & 1);
+        l.bk = l.part == G - 1;
+        l.face_lane = l.first || l.bk;
+        l.fwall = l.face_lane && l.n > 0;
+        l.szone = l.bk && l.wl < tile.n_zones;
+        l.sgz = (int64_t)tile.zone_begin + l.wl;
+        l.zT = 0.; l.za0 = 0.; l.zb0 = 0.; l.zvol = 1.;
+        l.zc = ZoneC{};
+        if (l.szone) {
+            ZoneC& z = l.zc;
+            const int64_t gz = l.sgz;
+            z.vol = V.zvol[gz]; z.q = V.zq[gz]; z.inf_v = V.zinf_v[gz]; z.inf_t = V.zinf_t[gz];
+            z.vent_v = V.zvent_v[gz]; z.vent_t = V.zvent_t[gz]; z.sb = V.z_surf_begin[gz]; z.se = V.z_surf_end[gz];
+            l.zT = V.zoneT[gz];
+            zone_sources(z, l.za0, l.zb0);
+            l.zvol = z.vol;
+            if (!(z.sb == l.wl && z.se == l.wl + 1)) throw std::runtime_error("emu: warp tile is not SIMPLE");
+        }
+        for (int f = 0; f < NF; ++f) {
+            const bool back = G == 1 ? f == 1 : l.bk;
+            const int kf = back ? 1 : 0;
+            l.w[f] = FaceS{};
+            l.c[f] = FaceC{};
+            if (l.fwall) {
+                WallC wc;
+                load_wallc(V, l.sg, P.single_site != 0, wc);
+                const bool nm = END && ((wflags >> (back ? 11 : 10)) & 1);
+                const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
+                load_facec(wc, back, back ? V.u_b[l.sg] : V.u_f[l.sg], nm, l.c[f], false, 0., 0., nm2f,
+                           back ? V.u_b2[l.sg] : V.u_f2[l.sg]);
+                l.w[f].h = V.sc[(0 + kf) * NS + l.sg]; l.w[f].flow = V.sc[(2 + kf) * NS + l.sg];
+                l.w[f].sol = V.sc[(4 + kf) * NS + l.sg]; l.w[f].ir = V.sc[(6 + kf) * NS + l.sg];
+            }
+            l.ir_state[f] = l.w[f].ir;
+        }
+    }
+    gather_back();
+    for (Lane& l : L)
+        for (int f = 0; f < NF; ++f) l.w[f].ts = (G == 1 ? f == 1 : l.bk) ? l.ts_b : l.ts_f;
+
+    auto weather_at = [&](int site, int step, int s, SubWeather& out) {
+        const double* wtab = P.weather + (int64_t)site * P.weather_rows * 3;
+        const double* w0 = wtab + (int64_t)step * 3;
+        double t_out, wdir, wspeed;
+        if (P.weather_mode == HB_WEATHER_LINEAR) {
+            const double f = (double)(s + 1) / (double)S;
+            t_out = lerp_rn(w0[0], w0[3], f); wdir = lerp_rn(w0[1], w0[4], f); wspeed = lerp_rn(w0[2], w0[5], f);
+        } else if (P.weather_mode == HB_WEATHER_PER_SUBSTEP) {
+            w0 = wtab + ((int64_t)step * S + s) * 3;
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        } else {
+            t_out = w0[0]; wdir = w0[1]; wspeed = w0[2];
+        }
+        sub_weather(t_out, wdir, wspeed, out);
+    };
+    std::vector<double> left(32), right(32);
+    int rec = 0;
+    for (int step = 0; step < P.n_steps; ++step) {
+        if (P.single_site)
+            for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
+        for (Lane& l : L) {
+            for (int f = 0; f < NF; ++f) {
+                const bool back = G == 1 ? f == 1 : l.bk;
+                const int kf = back ? 1 : 0;
+                const FaceC& c = l.c[f];
+                FaceS& w = l.w[f];
+                if (P.input_mode != HB_INPUT_STATE) {
+                    const double* in = P.input_mode == HB_INPUT_SITE
+                                           ? P.inputs + ((int64_t)c.site * P.n_steps + step) * 4
+                                           : P.inputs + ((int64_t)step * P.n_desc_surfaces + c.desc_index) * 4;
+                    w.sol = in[kf];
+                    w.ir = in[2 + kf];
+                    if (!back && P.ir_mode == HB_IR_NET_GAIN) {
+                        if (c.eps > 1e-3) {
+                            const double tk = w.ts + 273.15;
+                            const double tk2 = tk * tk;
+                            w.ir = w.ir / c.area / c.eps + kSigma * (tk2 * tk2);
+                        } else {
+                            w.ir = l.ir_state[f];
+                        }
+                    }
+                }
+                face_begin_main_step(c, w);
+            }
+            if (P.zone_gain != nullptr && l.szone) {
+                l.zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + l.sgz];
+                zone_sources(l.zc, l.za0, l.zb0);
+            }
+        }
+        for (int s = 0; s < S; ++s) {
+            // face role: border conditions with the old surface temperatures
+            for (Lane& l : L)
+                for (int f = 0; f < NF; ++f) {
+                    const bool back = G == 1 ? f == 1 : l.bk;
+                    const FaceC& cf = l.c[f];
+                    FaceS& wf = l.w[f];
+                    SubWeather sw;
+                    if (P.single_site) sw = swt[s]; else weather_at(cf.site, step, s, sw);
+                    const int fl = cf.fl;
+                    const bool is_out = fl & FC_OUT;
+                    const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(cf.nx, sw.sin_wd), mul_rn(cf.ny, sw.cos_wd)) > 0.0);
+                    wf.forced = cf.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
+                    wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? l.zT : cf.amb;
+                    const double trad = is_out ? wf.trad_out : wf.air;
+                    const double hn = tarp_lean(wf.air - wf.ts, cf.kpos, cf.kneg);
+                    const double h = is_out ? hn + wf.forced : hn;
+                    if (h != h) wf.status |= ST_NAN_H;
+                    const double xr = 273.15 + (trad + wf.ts) / 2.;
+                    const double rad = cf.eps4s * ((xr * xr) * xr);
+                    const double asol = cf.alpha_end * wf.solar;
+                    l.lk[f].t_in = 0.;
+                    if (END) {
+                        if (fl & FC_NM2) {
+                            double t_in = back ? l.t1_b : l.t1_f;
+                            solve_end_pair<true>(back, wf.air, h, rad, trad, asol, cf.u_nb, cf.u_nb2, back ? l.t2_b : l.t2_f,
+                                                 wf.ts, t_in, wf.nm_iters, wf.status);
+                            l.lk[f].t_in = t_in;
+                        } else if (fl & FC_NM) {
+                            wf.ts = solve_end_node<true>(wf.air, h, rad, trad, cf.u_nb, back ? l.t1_b : l.t1_f, asol, wf.ts,
+                                                         wf.nm_iters, wf.status);
+                        }
+                    }
+                    const double hs = h > 1e-12 ? h : 1e-12;
+                    l.lk[f].ghost = wf.air + (rad * (trad - wf.ts) + asol) * rcp_lean(hs);
+                    l.lk[f].link = hs * cf.v_end;
+                }
+            // face lanes -> node lanes, placement
+            std::vector<double> gfv(32), gbv(32);
+            for (int lane = 0; lane < 32; ++lane) {
+                Lane& l = L[lane];
+                const Lane& lb = L[l.base + G - 1];
+                const double gf = l.lk[0].ghost, lf = l.lk[0].link;
+                const double gb = lb.lk[NF - 1].ghost, lbk = lb.lk[NF - 1].link;
+                const double tf0 = l.w[0].ts, tf1 = l.lk[0].t_in, tb0 = lb.w[NF - 1].ts, tb1 = lb.lk[NF - 1].t_in;
+                double* t = &T[lane * NL];
+                double* a = &A[lane * NL];
+                double* b = &B[lane * NL];
+                b[0] = l.first ? lf : b[0];
+                if (END) {
+                    t[0] = (l.first && l.nmf) ? tf0 : t[0];
+                    t[1] = (l.first && l.nmf2) ? tf1 : t[1];
+                }
+                for (int i = 0; i < NL; ++i) {
+                    a[i] = i == l.last ? lbk : a[i];
+                    if (END) {
+                        t[i] = (i == l.last && l.nmb) ? tb0 : t[i];
+                        t[i] = (i == l.last - 1 && l.nmb2) ? tb1 : t[i];
+                    }
+                    t[i] = i == l.last + 1 ? gb : t[i];
+                }
+                gfv[lane] = gf;
+                gbv[lane] = gb;
+            }
+            // node role: wt_rk4
+            auto halos = [&](const std::vector<double>& x, bool first_sweep) {
+                for (int lane = 0; lane < 32; ++lane) {
+                    const Lane& l = L[lane];
+                    double lv = first_sweep ? gfv[lane] : 0., rv = first_sweep ? gbv[lane] : 0.;
+                    if (G > 1) {
+                        const double sl = l.part > 0 ? x[(lane - 1) * NL + NL - 1] : x[lane * NL + NL - 1];
+                        const double sr = l.part < G - 1 ? x[(lane + 1) * NL] : x[lane * NL];
+                        lv = l.first ? lv : sl;
+                        rv = l.edge ? rv : sr;
+                    }
+                    left[lane] = lv;
+                    right[lane] = rv;
+                }
+            };
+            halos(T, true);
+            for (int lane = 0; lane < 32; ++lane) {
+                const double *t = &T[lane * NL], *a = &A[lane * NL], *b = &B[lane * NL];
+                double* x = &X[lane * NL];
+                for (int i = 0; i < NL; ++i) {
+                    const double dn = (i + 1 < NL ? t[i + 1] : right[lane]) - t[i];
+                    const double dp = t[i] - (i > 0 ? t[i - 1] : left[lane]);
+                    x[i] = a[i] * dn - b[i] * dp;
+                }
+            }
+            for (int q = 0; q < 32 * NL; ++q) T[q] += X[q];
+            for (int k = 0; k < 3; ++k) {
+                const double cc = k == 0 ? 1. / 2. : k == 1 ? 1. / 6. : 1. / 24.;
+                halos(X, false);
+                std::vector<double> Y(32 * NL);
+                for (int lane = 0; lane < 32; ++lane) {
+                    const double *x = &X[lane * NL], *a = &A[lane * NL], *b = &B[lane * NL];
+                    for (int i = 0; i < NL; ++i) {
+                        const double dn = (i + 1 < NL ? x[i + 1] : right[lane]) - x[i];
+                        const double dp = x[i] - (i > 0 ? x[i - 1] : left[lane]);
+                        Y[lane * NL + i] = a[i] * dn - b[i] * dp;
+                    }
+                }
+                X = Y;
+                for (int q = 0; q < 32 * NL; ++q) T[q] = fma(cc, X[q], T[q]);
+            }
+            gather_back();
+            // face role: new film coefficients, flows, zone
+            for (Lane& l : L) {
+                double hA_b = 0., hAT_b = 0.;
+                for (int f = 0; f < NF; ++f) {
+                    const bool back = G == 1 ? f == 1 : l.bk;
+                    const FaceC& cf = l.c[f];
+                    FaceS& wf = l.w[f];
+                    const double ts = back ? l.ts_b : l.ts_f;
+                    const double hn = tarp_lean(wf.air - ts, cf.kpos, cf.kneg);
+                    const double h = (cf.fl & FC_OUT) ? hn + wf.forced : hn;
+                    if (h != h) wf.status |= ST_NAN_H;
+                    wf.ts = ts;
+                    wf.h = h;
+                    wf.flow = (ts - wf.air) * h;
+                    wf.e += wf.flow * cf.area * dt;
+                    if (back) {
+                        hA_b = h * cf.area;
+                        hAT_b = hA_b * ts;
+                    }
+                }
+                if (l.szone) {
+                    const double inv_cc = zone_inv_c_t<true>(l.zvol, l.zT);
+                    const double tn = zone_advance<true>(l.zT, dt, inv_cc, l.za0 + hAT_b, l.zb0 + hA_b);
+                    if (tn != tn) V.status[l.sg] |= ST_NAN_ZONE;
+                    l.zT = tn;
+                }
+            }
+        }
+        if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
+            for (const Lane& l : L)
+                if (zone_rec_base && l.szone) zone_rec_base[(int64_t)rec * V.n_dev_zones + l.sgz] = l.zT;
+            if (P.node_rec) {
+                for (int lane = 0; lane < 32; ++lane)
+                    for (int i = 0; i < NL; ++i)
+                        P.node_rec[(int64_t)rec * P.slab_len + tile.node_offset + (int64_t)i * 32 + lane] = T[lane * NL + i];
+                for (const Lane& l : L) {
+                    if (!l.fwall) continue;
+                    double* rr = P.sc_rec + (int64_t)rec * 8 * NS;
+                    for (int f = 0; f < NF; ++f) {
+                        const int kf = (G == 1 ? f == 1 : l.bk) ? 1 : 0;
+                        rr[(0 + kf) * NS + l.sg] = l.w[f].h; rr[(2 + kf) * NS + l.sg] = l.w[f].flow;
+                        rr[(4 + kf) * NS + l.sg] = l.w[f].sol; rr[(6 + kf) * NS + l.sg] = l.w[f].ir;
+                    }
+                }
+            }
+            ++rec;
+        }
+    }
+    for (int lane = 0; lane < 32; ++lane)
+        for (int i = 0; i < NL; ++i) V.nodeT[tile.node_offset + (int64_t)i * 32 + lane] = T[lane * NL + i];
+    for (const Lane& l : L) {
+        if (l.fwall)
+            for (int f = 0; f < NF; ++f) {
+                const bool back = G == 1 ? f == 1 : l.bk;
+                const int kf = back ? 1 : 0;
+                V.sc[(0 + kf) * NS + l.sg] = l.w[f].h; V.sc[(2 + kf) * NS + l.sg] = l.w[f].flow;
+                V.sc[(4 + kf) * NS + l.sg] = l.w[f].sol; V.sc[(6 + kf) * NS + l.sg] = l.w[f].ir;
+                if (back) V.energy_b[l.sg] += l.w[f].e; else V.energy_f[l.sg] += l.w[f].e;
+                V.nm_iters[l.sg] += l.w[f].nm_iters;
+                V.status[l.sg] |= l.w[f].status;
+            }
+        if (l.szone) V.zoneT[l.sgz] = l.zT;
+    }
 }
 
 // hb_face_kernel's data flow (all-massive tiles and tiles whose no-mass chunks are single end nodes): per-face lanes.
@@ -601,7 +912,8 @@ int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, con
             }
         }
         for (const Tile& t : B.tiles) {
-            if (t.flags & (TILE_EXT | TILE_DIST)) march_tile(V, P, t, zr.empty() ? nullptr : zr.data());
+            if (t.flags & TILE_WARP) march_tile_warp(V, P, t, zr.empty() ? nullptr : zr.data());
+            else if (t.flags & (TILE_EXT | TILE_DIST)) march_tile(V, P, t, zr.empty() ? nullptr : zr.data());
             else march_tile_face(V, P, t, zr.empty() ? nullptr : zr.data());
         }
         if (P.record_every) {

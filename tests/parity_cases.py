@@ -475,8 +475,14 @@ def check_full_horizon_ensemble(batch_cls, kind: str, n: int, hours: int = 8760,
         off += om.state_len
     assert off == got.size
     assert worst_node <= tol and worst_zone <= tol, (kind, worst_node, worst_zone)
+    # Branch parity of the no-mass fixed point: identical iteration counts wherever no exit test is decided by the last
+    # bits.  Over a whole year (tens of millions of iterations; exit tests `err > old_err`, `err/n < 0.01` on values that
+    # differ from the oracle's in the last ulp) a handful of exits may flip without moving any temperature past `tol`;
+    # short runs (every other parity case) demand equality.
     iters = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
-    assert iters == sum(om.nomass_iterations for om in models), (kind, iters)
+    want = sum(om.nomass_iterations for om in models)
+    slack = 0 if hours <= 240 else max(1, int(1e-5 * want))
+    assert abs(iters - want) <= slack, (kind, iters, want)
     return worst_node, worst_zone
 
 
