@@ -25,6 +25,9 @@ import time
 
 import numpy as np
 
+# the launch groups of a series run on streams of their own: give each a hardware work queue (read at context creation)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for _p in (ROOT, os.path.join(ROOT, "oracle")):
     if _p not in sys.path:

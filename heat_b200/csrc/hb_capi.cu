@@ -19,6 +19,13 @@ namespace {
 
 thread_local std::string g_err;
 
+// The launch groups of a series run concurrently on streams of their own; with the default of 8 hardware work queues
+// streams share queues and groups queue up behind each other.  Takes effect when the library is loaded before the
+// process creates its CUDA context (never overrides a value the user set).
+struct EnvInit {
+    EnvInit() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+} g_env_init;
+
 struct CudaError : std::runtime_error {
     using std::runtime_error::runtime_error;
 };
@@ -187,7 +194,9 @@ void build_device(hb_handle* h) {
     // A tile's run time is proportional to its sub-step count S (2 … 118), and a series is only as short as its
     // longest tile: tiles are binned by S and the bins with the most sub-steps are launched first, on streams of
     // higher priority, so that across ALL groups the long tiles start at once and the short ones fill in behind.
-    auto s_class = [](int S) { return S >= 96 ? 0 : S >= 56 ? 1 : S >= 32 ? 2 : S >= 16 ? 3 : 4; };
+    // (three bins: with more than 32 launch groups — the number of hardware work queues, CUDA_DEVICE_MAX_CONNECTIONS —
+    // late groups queue up behind the longest ones they share a queue with)
+    auto s_class = [](int S) { return S >= 56 ? 0 : S >= 20 ? 1 : 2; };
     std::map<std::tuple<int, int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -NL, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
@@ -202,7 +211,6 @@ void build_device(hb_handle* h) {
     HB_CUDA(cudaEventCreateWithFlags(&h->fork, cudaEventDisableTiming));
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
-        const int cls = std::get<0>(kv.first);
         grp->NL = -std::get<2>(kv.first);
         grp->G = -std::get<3>(kv.first);
         grp->var = std::get<4>(kv.first);
@@ -212,9 +220,20 @@ void build_device(hb_handle* h) {
         grp->n_tiles = (int)kv.second.size();
         grp->s_max = B.tiles[kv.second.front()].S;
         grp->ids.upload(kv.second, st);
+        h->groups.push_back(std::move(grp));
+    }
+    // launch order = longest chains first (the block scheduler serves kernels in launch order), on streams of
+    // decreasing priority
+    // (first of all the few no-mass-end tiles that ask for an SM of their own, hb_wtile_tier.cu: they need empty SMs)
+    auto rank = [](const hb_handle::Group& g) { return g.var == 9 && g.s_max >= 96 && g.n_tiles <= 64 ? 1 : 0; };
+    std::stable_sort(h->groups.begin(), h->groups.end(),
+                     [&](const std::unique_ptr<hb_handle::Group>& a, const std::unique_ptr<hb_handle::Group>& b) {
+                         return rank(*a) != rank(*b) ? rank(*a) > rank(*b) : a->s_max > b->s_max;
+                     });
+    for (auto& grp : h->groups) {
+        const int cls = s_class(grp->s_max);
         HB_CUDA(cudaStreamCreateWithPriority(&grp->stream, cudaStreamNonBlocking, std::max(prio_hi, std::min(prio_lo, prio_hi + cls))));
         HB_CUDA(cudaEventCreateWithFlags(&grp->done, cudaEventDisableTiming));
-        h->groups.push_back(std::move(grp));
     }
     HB_CUDA(cudaStreamSynchronize(st));
 }

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <numeric>
 #include <stdexcept>
 #include <tuple>
@@ -275,6 +276,78 @@ inline bool is_pane(const SurfacePlan& P) {
 constexpr int kBulkSubsteps = 56;   // below: tiles are scheduled for throughput, not for latency (hb_capi.cu S bins)
 constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE | TILE_WARP;   // tiles are uniform in these
 
+const std::vector<int>& wt_nodes_per_lane() {
+    static const std::vector<int> nls = [] {
+    std::vector<int> v;
+    if (const char* e = std::getenv("HB_WT_NLS"))
+        for (const char* p = e; *p;) {
+            v.push_back(std::atoi(p));
+            while (*p && *p != ',') ++p;
+            if (*p == ',') ++p;
+        }
+    if (v.empty()) v = {8, 12, 16};
+    std::sort(v.begin(), v.end());
+    return v;
+}();
+    return nls;
+}
+
+// Warp tiles cost S sub-steps of a whole warp however many of their wall slots are filled.  Within a bucket of equal
+// kernel variant and sub-step count, the walls left over after the last FULL tile of a geometry move up to the next
+// larger geometry (a wall fits any geometry of at least its size) when they would fill at most 3/4 of a tile there:
+// 8.5 % fewer FP64 warp instructions on the 10^5-wall ensemble of BASELINE.json configs[2].
+void wt_merge_leftovers(BatchPlan& B) {
+    std::vector<WtGeom> geoms;
+    for (int G = 1; G <= 32; G *= 2)
+        for (int NL : wt_nodes_per_lane())
+            if (G * NL <= kWtMaxNodes) geoms.push_back(WtGeom{G * NL, G, NL});
+    std::sort(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap != b.cap ? a.cap < b.cap : a.NL > b.NL; });
+    geoms.erase(std::unique(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap == b.cap; }), geoms.end());
+    auto index_of = [&](const ModelPlan& M) {
+        for (size_t k = 0; k < geoms.size(); ++k)
+            if (geoms[k].G == M.G && geoms[k].NL == M.NL) return (int)k;
+        return -1;
+    };
+    std::map<std::pair<int, int>, std::vector<std::vector<int>>> buckets;   // (variant, S) -> geometry -> models
+    for (size_t m = 0; m < B.models.size(); ++m) {
+        const ModelPlan& M = B.models[m];
+        if (!(M.variant & TILE_WARP)) continue;
+        const int k = index_of(M);
+        if (k < 0) continue;
+        auto& v = buckets[{M.variant & kTileKey, M.dt_subdivisions}];
+        if (v.empty()) v.resize(geoms.size());
+        v[k].push_back((int)m);
+    }
+    for (auto& kv : buckets) {
+        const bool end = (kv.first.first & TILE_END) != 0;
+        if (end && kv.first.second >= kBulkSubsteps) continue;   // latency-bound tiles keep their 8-node geometry
+        auto& per = kv.second;
+        auto usable = [&](size_t k) { return !(end && geoms[k].G < 2); };
+        std::vector<int> carry;
+        for (size_t k = 0; k < geoms.size(); ++k) {
+            if (!usable(k)) continue;
+            std::vector<int> here = per[k];
+            for (int m : carry) {
+                ModelPlan& M = B.models[m];
+                M.G = geoms[k].G;
+                M.NL = geoms[k].NL;
+                M.walls = 32 / geoms[k].G;
+                here.push_back(m);
+            }
+            carry.clear();
+            per[k] = here;
+            const int W = 32 / geoms[k].G;
+            const int r = (int)here.size() % W;
+            bool later = false;
+            for (size_t q = k + 1; q < geoms.size(); ++q) later = later || (usable(q) && !per[q].empty());
+            if (r > 0 && later && 4 * r <= 3 * W) {
+                carry.assign(here.end() - r, here.end());
+                per[k].resize(here.size() - r);
+            }
+        }
+    }
+}
+
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
     if (d->steps_per_hour <= 0) fail("steps_per_hour must be positive");
@@ -408,12 +481,22 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // A wall with its own zone behind it, all-massive or with no-mass chunks at its ends only: the warp-tile kernel
         // (no block barrier; HB_NO_WTILE=1 keeps the block-tile kernels for A/B measurements)
         static const bool no_wtile = std::getenv("HB_NO_WTILE") != nullptr;
-        if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) && M.nmax <= kWtMaxNodes) {
-            const WtGeom* g = wt_geom_of_nodes(M.nmax);
+        // HB_WT_NLS="8,12,16" (diagnostic): nodes-per-lane values the planner may use (compiled: 8, 10, 12, 16)
+        static const std::vector<int>& wt_nls = wt_nodes_per_lane();
+        // Walls with no-mass ends never put both faces (two fixed-point loops in sequence) on one lane, and — they are
+        // the walls with the most sub-steps, the longest dependent chains of a series — those with many sub-steps take
+        // 8 nodes per lane (measured alone, S = 118: 2550 cycles per sub-step against 3100-3700 with 12 or 16).
+        // All-massive walls take the cheapest geometry whatever their sub-step count: 8 nodes per lane does not
+        // shorten their sub-step (1690 vs 1700 cycles) and costs 10 % more warp-sub-steps.
+        static const std::vector<int> wt_nls_long = {8};
+        const bool end_long = (M.variant & TILE_END) && M.dt_subdivisions >= kBulkSubsteps;
+        WtGeom wg{};
+        if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) &&
+            wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : wt_nls, wg, (M.variant & TILE_END) ? 2 : 1)) {
             M.variant |= TILE_WARP;
-            M.G = g->G;
-            M.NL = g->NL;
-            M.walls = 32 / g->G;
+            M.G = wg.G;
+            M.NL = wg.NL;
+            M.walls = 32 / wg.G;
             continue;
         }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
@@ -430,6 +513,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // (the same walls per SM: 2 blocks of 256 threads instead of 4 of 128); long tiles keep the short node phase
         if (face && group_of_nodes(M.nmax) == 16 && M.dt_subdivisions < kBulkSubsteps) M.walls = std::max(M.walls, 16);
     }
+    wt_merge_leftovers(B);
     B.model_order.resize(d->n_models);
     std::iota(B.model_order.begin(), B.model_order.end(), 0);
     auto key = [&](int m) {

@@ -61,13 +61,19 @@ constexpr double kInitialT = 22.0;               // surface_trait.rs:365-370, zo
 // Geometries in order of capacity G·NL; a wall takes the first one that holds it (cost per wall and sub-step in FP64
 // warp instructions ≈ (16.5·NL + 115·faces per lane)·G / 32 grows with the capacity, so the smallest fit is the cheapest).
 struct WtGeom { int cap, G, NL; };
-constexpr WtGeom kWtGeoms[] = {{8, 1, 8},    {12, 1, 12},  {16, 2, 8},    {24, 2, 12},   {32, 2, 16},  {48, 4, 12}, {64, 4, 16},
-                               {96, 8, 12},  {128, 8, 16}, {192, 16, 12}, {256, 16, 16}, {384, 32, 12}, {512, 32, 16}};
 constexpr int kWtMaxNodes = 512;
-inline const WtGeom* wt_geom_of_nodes(int n) {
-    for (const WtGeom& g : kWtGeoms)
-        if (n <= g.cap) return &g;
-    return nullptr;
+// Smallest-capacity geometry (G lanes x NL nodes) that holds a wall of n nodes, NL taken from `nls` (ascending);
+// ties go to the larger NL (fewer lanes per wall: the face work is shared by more walls).
+inline bool wt_geom_of_nodes(int n, const std::vector<int>& nls, WtGeom& out, int min_G = 1) {
+    bool found = false;
+    for (int G = min_G; G <= 32; G *= 2)
+        for (int NL : nls) {
+            const int cap = G * NL;
+            if (n > cap || cap > kWtMaxNodes) continue;
+            if (!found || cap < out.cap || (cap == out.cap && NL > out.NL)) out = WtGeom{cap, G, NL};
+            found = true;
+        }
+    return found;
 }
 
 struct CavityParams {   // cavity.rs:28-50

@@ -21,12 +21,13 @@
 
 namespace hb {
 
-// registers per thread each geometry is compiled for: 168 / 200 / 224 / 255 registers = 12 / 10 / 9 / 8 resident warps
-// per SM.  (__maxnreg__, not the min-blocks argument of __launch_bounds__: for 32-thread blocks ptxas caps that form at
-// 168 registers whatever the block count asked for.)
-__host__ __device__ constexpr int wt_max_regs(int G, int NL) {
-    return G == 1 ? (NL <= 8 ? 200 : NL <= 12 ? 224 : 255) : (NL <= 8 ? 168 : NL <= 12 ? 200 : 224);
-}
+// Registers per thread each geometry is compiled for.  Every warp of a block sits on one of the SM's four
+// sub-partitions, whose register file (16 384 registers) holds 3 warps of <= 168 registers or 2 of <= 255: there is
+// nothing in between.  (__maxnreg__, not the min-blocks argument of __launch_bounds__: for 32-thread blocks ptxas caps
+// that form at 168 registers whatever the block count asked for.)
+// Tiles with no-mass ends (MODE != lean) carry two fixed-point solvers and are, in the ensembles of BASELINE.json, the
+// walls with the most sub-steps — the longest dependent chains of a series: they get all the registers there are.
+__host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) { return NL <= 12 && MODE == kFaceLean ? 168 : 255; }
 
 // T[k], k lane-dependent, as a select tree (registers cannot be indexed)
 template <int NL>
@@ -114,24 +115,39 @@ __device__ __forceinline__ void wt_rk4(double (&T)[NL], const double (&A)[NL], c
     }
 }
 
+#ifdef HB_PHASE_CLOCKS
+__device__ unsigned long long hb_wt_clk[8];   // pre, place, rk4, gather, post, zone, -, sub-steps
+#define HB_WCLK(k) { const long long _t = clock64(); wclk[k] += _t - wlast; wlast = _t; }
+#else
+#define HB_WCLK(k)
+#endif
+
 // Results of one face's pre-march evaluation, handed to the node lanes.
 struct WtLinks {
     double ghost, link;   // equivalent air temperature and h·dt/C of the end node
     double t_in;          // two-node no-mass end chunk: the chunk's inner node
 };
 
+// Warps per block: the warps of a block are spread over the SM's four sub-partitions (one register file and one FP64
+// pipe each); every warp is an independent tile and never synchronises with the others.
+constexpr int kWtWarps = 4;
+
 template <int G, int NL, int MODE, bool SIMPLE>
-__global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids) {
+__global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, MODE))
+    hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids, int n_tiles, int s_rows) {
     constexpr bool END = MODE != kFaceLean;   // no-mass chunks of one or two nodes at the ends of walls are possible
     constexpr int NF = G == 1 ? 2 : 1;        // faces evaluated by a face lane
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(SIMPLE, "zones shared by several walls: not in this kernel yet");
     static_assert(G >= 1 && G <= 32 && (G & (G - 1)) == 0 && NL >= 4, "geometry");
     extern __shared__ double s_dyn[];
-    SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn);   // [S] sub-step weather of the current main step
+    const int tile_slot = blockIdx.x * kWtWarps + (threadIdx.x >> 5);
+    if (tile_slot >= n_tiles) return;   // whole warp
+    // [S] sub-step weather of the current main step, one table per warp
+    SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn) + (size_t)(threadIdx.x >> 5) * s_rows;
 
-    const Tile tile = V.tiles[tile_ids[blockIdx.x]];
-    const int lane = threadIdx.x;
+    const Tile tile = V.tiles[tile_ids[tile_slot]];
+    const int lane = threadIdx.x & 31;
     const int64_t NS = V.n_dev_surfaces;
     const int S = tile.S;
     const double dt = tile.dt;
@@ -318,12 +334,16 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
                                                  wf.nm_iters, wf.status);
                 }
             }
+            // a no-mass end node takes no film link (v_end = 0): its temperature is placed, the ghost is never read
             const double hs = h > 1e-12 ? h : 1e-12;
             lk[f].ghost = wf.air + (rad * (trad - wf.ts) + asol) * rcp_lean(hs);
             lk[f].link = hs * cf.v_end;
         }
     };
 
+#ifdef HB_PHASE_CLOCKS
+    long long wclk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, wlast = clock64();
+#endif
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
         fill_weather(step);
@@ -333,8 +353,13 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
             zone_sources(zc, za0, zb0);
         }
         for (int s = 0; s < S; ++s) {
+#ifdef HB_PHASE_CLOCKS
+            wlast = clock64();
+            wclk[7] += 1;
+#endif
             // ================= face role: border conditions with the old surface temperatures =================
             pre(step, s);
+            HB_WCLK(0)
             // ================= face lanes → node lanes =================
             const double gf = lk[0].ghost, lf = lk[0].link;
             double gb = lk[NF - 1].ghost, lb = lk[NF - 1].link;
@@ -361,8 +386,10 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
                 }
                 T[i] = i == last + 1 ? gb : T[i];   // the slot behind the last node stands for the back ghost
             }
+            HB_WCLK(1)
             // ================= node role: RK4 of the massive nodes =================
             wt_rk4<G, NL>(T, A, B, first, gf, edge, gb);
+            HB_WCLK(2)
             // ================= node lanes → face lanes =================
             ts_f = T[0];
             if constexpr (END) {
@@ -370,6 +397,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
                 t2_f = T[2];
             }
             gather_back();
+            HB_WCLK(3)
             // ================= face role: new film coefficients, flows, zone =================
             double hA_b = 0., hAT_b = 0.;
 #pragma unroll
@@ -390,6 +418,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
                     hAT_b = hA_b * ts;
                 }
             }
+            HB_WCLK(4)
             {   // the lane's own wall is the zone's only surface (its back face): model.rs:489-597, 650-674
                 const double inv_cc = zone_inv_c_t<true>(zvol, zT);
                 const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT_b, zb0 + hA_b);
@@ -398,6 +427,7 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
                     zT = tn;
                 }
             }
+            HB_WCLK(5)
         }
 
         if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
@@ -420,6 +450,10 @@ __global__ void __launch_bounds__(32) __maxnreg__(wt_max_regs(G, NL)) hb_wtile_k
         }
     }
 
+#ifdef HB_PHASE_CLOCKS
+    if (lane == 0 && tile_slot == 0)
+        for (int q = 0; q < 8; ++q) atomicAdd(&hb_wt_clk[q], (unsigned long long)wclk[q]);
+#endif
     // ---- write the state back ----
 #pragma unroll
     for (int i = 0; i < NL; ++i) V.nodeT[tile.node_offset + (int64_t)i * 32 + lane] = T[i];
