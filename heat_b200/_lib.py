@@ -55,7 +55,13 @@ class SeriesC(C.Structure):
         ("weather", C.c_void_p), ("weather_rows", C.c_int64), ("input_mode", C.c_int32), ("ir_mode", C.c_int32),
         ("inputs", C.c_void_p), ("record_every", C.c_int32), ("zone_t_record", C.c_void_p),
         ("state_record", C.c_void_p), ("zone_gain", C.c_void_p),
+        ("zone_infiltration_volume", C.c_void_p), ("zone_infiltration_temperature", C.c_void_p),
+        ("zone_ventilation_volume", C.c_void_p), ("zone_ventilation_temperature", C.c_void_p),
     ]
+
+
+ZONE_SCHEDULES = ("zone_gain", "zone_infiltration_volume", "zone_infiltration_temperature", "zone_ventilation_volume",
+                  "zone_ventilation_temperature")
 
 
 class EnsembleStatsC(C.Structure):
@@ -94,6 +100,10 @@ SYMBOLS = {
     "hb_launch_count": (C.c_int64, [_P]),
     "hb_reduce": (C.c_int32, [_P, C.POINTER(EnsembleStatsC)]),
     "hb_reset_energy": (C.c_int32, [_P]),
+    "hb_comm_unique_id": (C.c_int32, [_P]),
+    "hb_comm_init": (C.c_int32, [_P, _P, C.c_int32, C.c_int32]),
+    "hb_comm_destroy": (C.c_int32, [_P]),
+    "hb_reduce_all": (C.c_int32, [_P, C.POINTER(EnsembleStatsC)]),
     "hb_measure_fp64_peak": (C.c_int32, [C.c_int32, C.POINTER(C.c_double)]),
     "hb_flush_l2": (C.c_int32, [_P, C.c_int64]),
     "hb_read_epw": (C.c_int32, [C.c_char_p, _P, _P, C.c_int64, C.POINTER(C.c_int64)]),

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include "hb_dev.hpp"
 
@@ -58,6 +59,42 @@ struct DevBuf {
     ~DevBuf() { free(); }
 };
 
+// ---- NCCL, resolved at run time (dlopen): the library carries no link-time dependency on it, and a process that
+// already loaded a libnccl.so.2 (torch bundles one) shares that copy ----
+struct Nccl {
+    using Comm = void*;
+    typedef struct { char internal[128]; } UniqueId;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(Comm*, int, UniqueId, int) = nullptr;
+    int (*CommDestroy)(Comm) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    enum { kFloat64 = 8, kSum = 0, kMax = 2, kMin = 3 };   // ncclDataType_t / ncclRedOp_t values of nccl.h
+    static Nccl& get() {
+        static Nccl n = [] {
+            Nccl x;
+            void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+            if (!lib) throw CudaError(std::string("cannot load libnccl.so.2: ") + dlerror());
+            auto sym = [&](const char* name) {
+                void* p = dlsym(lib, name);
+                if (!p) throw CudaError(std::string("libnccl has no symbol ") + name);
+                return p;
+            };
+            x.GetUniqueId = reinterpret_cast<decltype(x.GetUniqueId)>(sym("ncclGetUniqueId"));
+            x.CommInitRank = reinterpret_cast<decltype(x.CommInitRank)>(sym("ncclCommInitRank"));
+            x.CommDestroy = reinterpret_cast<decltype(x.CommDestroy)>(sym("ncclCommDestroy"));
+            x.AllReduce = reinterpret_cast<decltype(x.AllReduce)>(sym("ncclAllReduce"));
+            x.GetErrorString = reinterpret_cast<decltype(x.GetErrorString)>(sym("ncclGetErrorString"));
+            return x;
+        }();
+        return n;
+    }
+    void check(int rc, const char* what) const {
+        if (rc != 0) throw CudaError(std::string(what) + ": " + (GetErrorString ? GetErrorString(rc) : "NCCL error"));
+    }
+};
+
 }  // namespace
 
 struct hb_handle {
@@ -78,6 +115,10 @@ struct hb_handle {
     DevBuf<hb::Tile> tiles;
     DevBuf<double> red_out;
     DevBuf<unsigned long long> red_iout;
+    DevBuf<double> comm_buf;        // staging of hb_reduce_all: 7 sums | 2 minima | 2 + 8 maxima
+    bool zone_has_inf_v = false, zone_has_vent_v = false;   // volumes given with hb_set_zone_inputs
+    void* comm = nullptr;           // ncclComm_t (hb_comm_init)
+    int comm_world = 1;
     DevBuf<double> flush;
 
     // one launch per (lanes-per-wall, kernel variant); each on its own stream so that small groups overlap
@@ -112,6 +153,7 @@ struct hb_handle {
     ~hb_handle() {
         if (device < 0) return;
         cudaSetDevice(device);
+        if (comm) Nccl::get().CommDestroy(comm);
         groups.clear();   // joins and destroys the group streams / events
         if (fork) cudaEventDestroy(fork);
         if (stream) {
@@ -200,7 +242,7 @@ void build_device(hb_handle* h) {
     std::map<std::tuple<int, int, int, int, int, int>, std::vector<int32_t>> by;   // (S bin, fast?, -NL, -G, variant, W)
     for (size_t ti = 0; ti < B.tiles.size(); ++ti) {
         const hb::Tile& t = B.tiles[ti];
-        const int var = (t.flags & hb::TILE_WARP) ? ((t.flags & hb::TILE_END) ? 9 : 8)   // warp tiles (hb_wtile_kernel)
+        const int var = (t.flags & hb::TILE_WARP) ? (!(t.flags & hb::TILE_SIMPLE) ? 10 : (t.flags & hb::TILE_END) ? 9 : 8)   // warp tiles
                         : (t.flags & hb::TILE_DIST) ? 2 : (t.flags & hb::TILE_EXT) ? 1 : (t.flags & hb::TILE_GEN) ? 4 : (t.flags & hb::TILE_PANE) ? 5
                         : (t.flags & hb::TILE_END) ? ((t.flags & hb::TILE_SIMPLE) ? 7 : 3) : ((t.flags & hb::TILE_SIMPLE) ? 6 : 0);
         // slow variants (shared-memory mirror, fixed-point loops) before fast ones inside a bin
@@ -295,7 +337,7 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
         const int var = (g.var == 0 || g.var == 3 || (g.var >= 5 && g.var < 8)) && !P.single_site ? 4 : g.var;
         if (var >= 8) {   // warp tiles (per-site weather is handled inside the kernel)
-            const int mode = var == 9 ? 1 : 0;
+            const int mode = var == 10 ? 3 : var == 9 ? 1 : 0;   // 3: buildings (one zone per model, panes, no-mass ends)
             switch (g.G) {
                 case 1: e = hb::launch_wtile_1(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
                 case 2: e = hb::launch_wtile_2(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
@@ -570,6 +612,8 @@ hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const doubl
         };
         if ((infiltration_temperature && !infiltration_volume) || (ventilation_temperature && !ventilation_volume))
             throw std::runtime_error("Space has infiltration/ventilation temperature but not volume");
+        h->zone_has_inf_v = infiltration_volume != nullptr;
+        h->zone_has_vent_v = ventilation_volume != nullptr;
         scatter(q_internal, 0., h->zq);
         scatter(infiltration_volume, 0., h->zinf_v);
         scatter(infiltration_temperature, NAN, h->zinf_t);
@@ -578,19 +622,33 @@ hb_status hb_set_zone_inputs(hb_handle* h, const double* q_internal, const doubl
     });
 }
 
-// hb_series.zone_gain (host, [n_steps][zones of the description]) -> device table in device zone order.
-static void upload_zone_gain(hb_handle* h, const hb_series* s, DevBuf<double>& d_gain, hb::SeriesDev& P) {
+// hb_series zone schedules (host, [n_steps][zones of the description]) -> device tables in device zone order.
+struct ZoneSchedules {
+    DevBuf<double> gain, inf_v, inf_t, vent_v, vent_t;
+};
+static void upload_zone_schedules(hb_handle* h, const hb_series* s, ZoneSchedules& d, hb::SeriesDev& P) {
     const hb::BatchPlan& B = h->plan;
     P.n_dev_zones = B.n_dev_zones;
-    if (!s->zone_gain || s->n_steps <= 0) return;
+    if (s->n_steps <= 0) return;
+    if ((s->zone_infiltration_temperature && !s->zone_infiltration_volume && !h->zone_has_inf_v) ||
+        (s->zone_ventilation_temperature && !s->zone_ventilation_volume && !h->zone_has_vent_v))
+        throw std::runtime_error("Space has infiltration/ventilation temperature but not volume");
     const int64_t nz = (int64_t)B.dev_zone_of.size();
-    std::vector<double> v((size_t)s->n_steps * B.n_dev_zones, 0.);
-    for (int64_t t = 0; t < s->n_steps; ++t)
-        for (int64_t z = 0; z < nz; ++z) v[(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = s->zone_gain[t * nz + z];
-    d_gain.alloc(v.size());
-    HB_CUDA(cudaMemcpyAsync(d_gain.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    HB_CUDA(cudaStreamSynchronize(h->stream));   // `v` goes out of scope
-    P.zone_gain = d_gain.p;
+    auto up = [&](const double* src, double pad, DevBuf<double>& dst, const double*& out) {
+        if (!src) return;
+        std::vector<double> v((size_t)s->n_steps * B.n_dev_zones, pad);
+        for (int64_t t = 0; t < s->n_steps; ++t)
+            for (int64_t z = 0; z < nz; ++z) v[(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = src[t * nz + z];
+        dst.alloc(v.size());
+        HB_CUDA(cudaMemcpyAsync(dst.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));   // `v` goes out of scope
+        out = dst.p;
+    };
+    up(s->zone_gain, 0., d.gain, P.zone_gain);
+    up(s->zone_infiltration_volume, 0., d.inf_v, P.zone_inf_v);
+    up(s->zone_infiltration_temperature, NAN, d.inf_t, P.zone_inf_t);
+    up(s->zone_ventilation_volume, 0., d.vent_v, P.zone_vent_v);
+    up(s->zone_ventilation_temperature, NAN, d.vent_t, P.zone_vent_t);
 }
 
 hb_status hb_march_series(hb_handle* h, const hb_series* s) {
@@ -601,7 +659,8 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         update_sites(h, s);
         clear_status(h);
         const hb::BatchPlan& B = h->plan;
-        DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec, d_gain;
+        DevBuf<double> d_weather, d_inputs, d_zone_rec, d_node_rec, d_sc_rec;
+        ZoneSchedules d_sched;
         const int64_t wcount = (int64_t)s->n_sites * s->weather_rows * 3;
         d_weather.alloc(wcount);
         HB_CUDA(cudaMemcpyAsync(d_weather.p, s->weather, wcount * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -622,7 +681,7 @@ hb_status hb_march_series(hb_handle* h, const hb_series* s) {
         P.n_desc_surfaces = (int64_t)B.surfaces.size();
         P.record_every = n_rec > 0 && (s->zone_t_record || s->state_record) ? s->record_every : 0;
         P.slab_len = B.node_slab_len;
-        upload_zone_gain(h, s, d_gain, P);
+        upload_zone_schedules(h, s, d_sched, P);
         if (P.record_every) {
             d_zone_rec.alloc((size_t)n_rec * B.n_dev_zones);
             P.zone_rec = d_zone_rec.p;
@@ -704,8 +763,8 @@ hb_status hb_march_series_dev(hb_handle* h, const hb_series* s, float* elapsed_m
         P.n_desc_surfaces = (int64_t)h->plan.surfaces.size();
         P.record_every = 0;
         P.slab_len = h->plan.node_slab_len;
-        DevBuf<double> d_gain;
-        upload_zone_gain(h, s, d_gain, P);
+        ZoneSchedules d_sched;
+        upload_zone_schedules(h, s, d_sched, P);
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (elapsed_ms) {
             HB_CUDA(cudaEventCreate(&e0));
@@ -749,6 +808,73 @@ hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out) {
         out->front_conv_energy_j = o[6]; out->back_conv_energy_j = o[7];
         out->n_zones = (int64_t)io[0]; out->n_nodes = (int64_t)io[1];
         out->nomass_iterations = (int64_t)io[2]; out->status_flags = (int64_t)io[3];
+    });
+}
+
+hb_status hb_comm_unique_id(void* id_out) {
+    return guarded([&] {
+        if (!id_out) throw std::invalid_argument("hb_comm_unique_id: null buffer");
+        Nccl& n = Nccl::get();
+        Nccl::UniqueId id;
+        n.check(n.GetUniqueId(&id), "ncclGetUniqueId");
+        static_assert(sizeof(id) == HB_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+        std::memcpy(id_out, &id, sizeof(id));
+    });
+}
+
+hb_status hb_comm_init(hb_handle* h, const void* id, int32_t rank, int32_t world) {
+    return guarded([&] {
+        need_device(h);
+        if (!id || world < 1 || rank < 0 || rank >= world) throw std::invalid_argument("hb_comm_init: bad id / rank / world");
+        Nccl& n = Nccl::get();
+        if (h->comm) {
+            n.CommDestroy(h->comm);
+            h->comm = nullptr;
+        }
+        Nccl::UniqueId uid;
+        std::memcpy(&uid, id, sizeof(uid));
+        n.check(n.CommInitRank(&h->comm, world, uid, rank), "ncclCommInitRank");
+        h->comm_world = world;
+        h->comm_buf.alloc(7 + 2 + 10);
+    });
+}
+
+hb_status hb_comm_destroy(hb_handle* h) {
+    return guarded([&] {
+        if (h->comm) {
+            need_device(h);
+            Nccl::get().CommDestroy(h->comm);
+            h->comm = nullptr;
+            h->comm_world = 1;
+        }
+    });
+}
+
+hb_status hb_reduce_all(hb_handle* h, hb_ensemble_stats* out) {
+    hb_status rc = hb_reduce(h, out);
+    if (rc != HB_OK || !h->comm || h->comm_world <= 1) return rc;
+    return guarded([&] {
+        Nccl& n = Nccl::get();
+        constexpr int kBits = 8;   // status words: ST_* of hb_dev.hpp, OR-ed as a maximum per bit
+        double v[7 + 2 + 2 + kBits] = {out->sum_zone_t, out->sum_node_t, out->front_conv_energy_j, out->back_conv_energy_j,
+                                       (double)out->n_zones, (double)out->n_nodes, (double)out->nomass_iterations,
+                                       out->min_zone_t, out->min_node_t, out->max_zone_t, out->max_node_t};
+        for (int k = 0; k < kBits; ++k) v[11 + k] = (double)((out->status_flags >> k) & 1);
+        double* d = h->comm_buf.p;
+        HB_CUDA(cudaMemcpyAsync(d, v, sizeof(v), cudaMemcpyHostToDevice, h->stream));
+        n.check(n.AllReduce(d, d, 7, Nccl::kFloat64, Nccl::kSum, h->comm, h->stream), "ncclAllReduce(sum)");
+        n.check(n.AllReduce(d + 7, d + 7, 2, Nccl::kFloat64, Nccl::kMin, h->comm, h->stream), "ncclAllReduce(min)");
+        n.check(n.AllReduce(d + 9, d + 9, 2 + kBits, Nccl::kFloat64, Nccl::kMax, h->comm, h->stream), "ncclAllReduce(max)");
+        HB_CUDA(cudaMemcpyAsync(v, d, sizeof(v), cudaMemcpyDeviceToHost, h->stream));
+        HB_CUDA(cudaStreamSynchronize(h->stream));
+        out->sum_zone_t = v[0]; out->sum_node_t = v[1]; out->front_conv_energy_j = v[2]; out->back_conv_energy_j = v[3];
+        out->n_zones = (int64_t)std::llround(v[4]); out->n_nodes = (int64_t)std::llround(v[5]);
+        out->nomass_iterations = (int64_t)std::llround(v[6]);
+        out->min_zone_t = v[7]; out->min_node_t = v[8]; out->max_zone_t = v[9]; out->max_node_t = v[10];
+        int64_t flags = 0;
+        for (int k = 0; k < kBits; ++k)
+            if (v[11 + k] > 0.5) flags |= (int64_t)1 << k;
+        out->status_flags = flags;
     });
 }
 

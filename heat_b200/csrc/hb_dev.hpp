@@ -115,6 +115,11 @@ struct SeriesDev {
     int64_t slab_len;
     const double* zone_gain; // [n_steps][n_dev_zones] (device zone order) or nullptr: q of the zones during main step t
     int64_t n_dev_zones;
+    // likewise infiltration / ventilation volume flow and temperature (model.rs:524-544), nullptr = constants stay
+    const double* zone_inf_v;
+    const double* zone_inf_t;
+    const double* zone_vent_v;
+    const double* zone_vent_t;
 };
 
 enum { ST_NAN_H = 1, ST_NAN_ERR = 2, ST_NAN_ZONE = 4, ST_ITER_CAP = 8, ST_BAD_GAMMA = 16 };

@@ -311,7 +311,7 @@ void wt_merge_leftovers(BatchPlan& B) {
     std::map<std::pair<int, int>, std::vector<std::vector<int>>> buckets;   // (variant, S) -> geometry -> models
     for (size_t m = 0; m < B.models.size(); ++m) {
         const ModelPlan& M = B.models[m];
-        if (!(M.variant & TILE_WARP)) continue;
+        if (!(M.variant & TILE_WARP) || !(M.variant & TILE_SIMPLE)) continue;   // buildings keep 32 / G >= n_surfaces
         const int k = index_of(M);
         if (k < 0) continue;
         auto& v = buckets[{M.variant & kTileKey, M.dt_subdivisions}];
@@ -320,7 +320,12 @@ void wt_merge_leftovers(BatchPlan& B) {
     }
     for (auto& kv : buckets) {
         const bool end = (kv.first.first & TILE_END) != 0;
-        if (end && kv.first.second >= kBulkSubsteps) continue;   // latency-bound tiles keep their 8-node geometry
+        if (end && kv.first.second >= kBulkSubsteps && kv.second.size() && [&] {
+                size_t c = 0;
+                for (auto& v : kv.second) c += v.size();
+                return c <= 4096;
+            }())
+            continue;   // a few latency-bound tiles keep their 8-node geometry
         auto& per = kv.second;
         auto usable = [&](size_t k) { return !(end && geoms[k].G < 2); };
         std::vector<int> carry;
@@ -425,10 +430,13 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     // Every model goes, whole, into one tile (its surfaces couple through its zones every sub-step).  Tiles are
     // uniform in lanes-per-wall G (from the model's largest wall), kernel variant and sub-step count S, so a block
     // runs one loop shape; models are sorted by (G, variant, S) and packed greedily.
+    std::vector<int32_t> nmax_real_of(d->n_models, 0);
+    int64_t n_end_long = 0;   // walls with no-mass ends and many sub-steps
     for (int m = 0; m < d->n_models; ++m) {
         ModelPlan& M = B.models[m];
         if (M.nmax > kMaxNodesBig) fail("surface has more nodes than the supported maximum (1022)");
         M.variant = 0;
+        nmax_real_of[m] = M.nmax;
         // `rest`: variant of the model without its single panes; a model whose other walls suit the face kernel keeps
         // its panes there too (both faces of a wall in one warp: tiles of at most 16 walls, >= 2 lanes per wall)
         int rest = 0;
@@ -477,6 +485,11 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             const hb_surface& s = B.surfaces[M.surface_begin];
             if (s.back_kind == HB_BOUNDARY_SPACE && s.front_kind != HB_BOUNDARY_SPACE) M.variant |= TILE_SIMPLE;
         }
+        if (M.variant == (TILE_END | TILE_SIMPLE) && M.dt_subdivisions >= kBulkSubsteps) ++n_end_long;
+    }
+    for (int m = 0; m < d->n_models; ++m) {
+        ModelPlan& M = B.models[m];
+        const int nmax_real = nmax_real_of[m];
         M.G = group_of_nodes(M.nmax);
         // A wall with its own zone behind it, all-massive or with no-mass chunks at its ends only: the warp-tile kernel
         // (no block barrier; HB_NO_WTILE=1 keeps the block-tile kernels for A/B measurements)
@@ -489,7 +502,9 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // All-massive walls take the cheapest geometry whatever their sub-step count: 8 nodes per lane does not
         // shorten their sub-step (1690 vs 1700 cycles) and costs 10 % more warp-sub-steps.
         static const std::vector<int> wt_nls_long = {8};
-        const bool end_long = (M.variant & TILE_END) && M.dt_subdivisions >= kBulkSubsteps;
+        // (when such walls are a few stragglers that END the series — configs[2]; where they are the bulk of the ensemble —
+        // configs[4] — throughput decides and they take the cheapest geometry like everybody else)
+        const bool end_long = (M.variant & TILE_END) && M.dt_subdivisions >= kBulkSubsteps && n_end_long <= 4096;
         WtGeom wg{};
         if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) &&
             wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : wt_nls, wg, (M.variant & TILE_END) ? 2 : 1)) {
@@ -498,6 +513,35 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             M.NL = wg.NL;
             M.walls = 32 / wg.G;
             continue;
+        }
+        // A building with ONE zone behind all its walls (every back face looks at it, no front face looks at a zone):
+        // all-massive walls, no-mass ends, single panes — the warp-tile kernel sums the zone over the model's walls with
+        // a segmented shuffle reduction.  All walls of the model sit in one warp: 32 / G >= n_surfaces.
+        if (!no_wtile && M.n_zones == 1 && M.n_surfaces >= 2 &&
+            (M.variant == 0 || M.variant == TILE_END || M.variant == (TILE_END | TILE_PANE))) {
+            bool ok = true;
+            for (int k = 0; k < M.n_surfaces && ok; ++k) {
+                const hb_surface& s = B.surfaces[M.surface_begin + k];
+                ok = s.back_kind == HB_BOUNDARY_SPACE && s.back_zone == 0 && s.front_kind != HB_BOUNDARY_SPACE;
+            }
+            WtGeom best{};
+            bool found = false;
+            if (ok)
+                for (int G = 1; G <= 8; G *= 2)
+                    for (int NL : wt_nls) {
+                        const int cap = G * NL;
+                        if (nmax_real > cap || 32 / G < M.n_surfaces) continue;
+                        if (!found || cap < best.cap || (cap == best.cap && NL > best.NL)) best = WtGeom{cap, G, NL};
+                        found = true;
+                    }
+            if (found) {
+                M.nmax = nmax_real;
+                M.variant = TILE_END | TILE_PANE | TILE_WARP;   // one kernel for all such buildings
+                M.G = best.G;
+                M.NL = best.NL;
+                M.walls = 32 / best.G;
+                continue;
+            }
         }
         const int Wmax = walls_of_group(group_of_nodes(M.nmax));
         if (M.n_surfaces > Wmax || M.n_zones > Wmax)

@@ -144,9 +144,14 @@ __global__ void __launch_bounds__(G* W, HB_MARCH_OCC / (G * W) > 0 ? HB_MARCH_OC
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
         // ---- main-step prologue: weather table, per-step inputs (what the caller writes into SimulationState) ----
-        if (P.zone_gain != nullptr) {   // scheduled gains of this main step (read by the zone lanes after the syncs below)
+        if (P.zone_gain || P.zone_inf_v || P.zone_inf_t || P.zone_vent_v || P.zone_vent_t) {
+            // scheduled zone inputs of this main step (read by the zone lanes after the syncs below)
             __syncthreads();
-            if (tid < tile.n_zones) s_zc[tid].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + tid];
+            if (tid < tile.n_zones) {
+                ZoneC z = s_zc[tid];
+                load_zone_schedule(P, step, (int64_t)tile.zone_begin + tid, z);
+                s_zc[tid] = z;
+            }
             __syncthreads();
         }
         if (P.single_site) {
@@ -779,10 +784,12 @@ __global__ void __launch_bounds__(face_threads(G, W), NL == kNL ? HB_FACE_OCC / 
     int rec = 0;
     for (int step = 0; step < P.n_steps; ++step) {
         if (step + 1 < P.n_steps) fill_weather(step + 1);   // read from the next main step's first pre() on
-        if (P.zone_gain != nullptr && szone) {   // scheduled gains: this main step's q, sources re-summed in the reference's order
+        if (szone) {   // scheduled zone inputs: this main step's values, sources re-summed in the reference's order
             ZoneC zc = s_zc[j];
-            zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + sgz];
-            zone_sources(zc, za0, zb0);
+            if (load_zone_schedule(P, step, sgz, zc)) {
+                s_zc[j] = zc;
+                zone_sources(zc, za0, zb0);
+            }
         }
         for (int s = 0; s < S; ++s) {
 #ifdef HB_PHASE_CLOCKS

@@ -594,6 +594,19 @@ HB_HD void zone_sources(const ZoneC& z, double& a, double& b) {
         b += rho * z.vent_v * cp;
     }
 }
+// Scheduled zone inputs of main step `step` (hb_series.zone_gain / zone_infiltration_* / zone_ventilation_*): what the
+// reference's caller writes into SimulationState before a march call (model.rs:502-544).  Returns whether anything is
+// scheduled (the caller then re-sums the non-surface sources in the reference's order, zone_sources).
+HB_HD bool load_zone_schedule(const SeriesDev& P, int step, int64_t gz, ZoneC& z) {
+    const int64_t o = (int64_t)step * P.n_dev_zones + gz;
+    if (P.zone_gain) z.q = P.zone_gain[o];
+    if (P.zone_inf_v) z.inf_v = P.zone_inf_v[o];
+    if (P.zone_inf_t) z.inf_t = P.zone_inf_t[o];
+    if (P.zone_vent_v) z.vent_v = P.zone_vent_v[o];
+    if (P.zone_vent_t) z.vent_t = P.zone_vent_t[o];
+    return P.zone_gain || P.zone_inf_v || P.zone_inf_t || P.zone_vent_v || P.zone_vent_t;
+}
+
 // 1/c with c = V·ρ(T)·cp(T) (zone.rs:59-65), ρ = 101325·28.97/(8314.46261815324·T_K)
 HB_HD double zone_inv_c(const ZoneC& z, double tz) {
     const double tk = tz + 273.15;

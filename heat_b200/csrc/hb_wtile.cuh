@@ -136,9 +136,10 @@ template <int G, int NL, int MODE, bool SIMPLE>
 __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, MODE))
     hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids, int n_tiles, int s_rows) {
     constexpr bool END = MODE != kFaceLean;   // no-mass chunks of one or two nodes at the ends of walls are possible
+    constexpr bool PANE = MODE == kFacePane;  // … and single panes (two no-mass nodes, both faces solve one 2x2 system)
     constexpr int NF = G == 1 ? 2 : 1;        // faces evaluated by a face lane
     constexpr unsigned FULL = 0xffffffffu;
-    static_assert(SIMPLE, "zones shared by several walls: not in this kernel yet");
+    constexpr int W = 32 / G;
     static_assert(G >= 1 && G <= 32 && (G & (G - 1)) == 0 && NL >= 4, "geometry");
     extern __shared__ double s_dyn[];
     const int tile_slot = blockIdx.x * kWtWarps + (threadIdx.x >> 5);
@@ -177,8 +178,21 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
     const bool bk = part == G - 1;
     const bool face_lane = first || bk;
     const bool fwall = face_lane && n > 0;
-    const bool szone = bk && wl < tile.n_zones;
-    const int64_t sgz = (int64_t)tile.zone_begin + wl;
+    // SIMPLE tiles: wall j has its own zone j.  Otherwise (buildings): every model of the tile has ONE zone, looked at by
+    // the back faces of all its walls [sb, se) and by no front face; the zone lives on the back lane of wall sb.
+    int zown = SIMPLE ? wl : -1, seg_end = wl + 1, zsrc = lane;
+    if constexpr (!SIMPLE) {
+        for (int j = 0; j < tile.n_zones; ++j) {
+            const int sb = V.z_surf_begin[tile.zone_begin + j], se = V.z_surf_end[tile.zone_begin + j];
+            if (sb == wl) zown = j;
+            if (wl >= sb && wl < se) {
+                seg_end = se;
+                zsrc = sb * G + G - 1;
+            }
+        }
+    }
+    const bool szone = bk && zown >= 0 && zown < tile.n_zones;
+    const int64_t sgz = (int64_t)tile.zone_begin + (zown >= 0 ? zown : 0);
     FaceC c[NF];
     FaceS w[NF];
     double ir_state[NF];
@@ -191,7 +205,7 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
         zT = V.zoneT[sgz];
         zone_sources(zc, za0, zb0);
         zvol = zc.vol;
-        simple_ok = zc.sb == wl && zc.se == wl + 1;
+        simple_ok = SIMPLE ? zc.sb == wl && zc.se == wl + 1 : zc.sb == wl && zc.se <= W;
     }
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
@@ -201,16 +215,18 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
         if (fwall) {
             WallC wc;
             load_wallc(V, sg, P.single_site != 0, wc);
-            const bool nm = END && ((wflags >> (back ? 11 : 10)) & 1);
+            const bool pane = PANE && ((wflags >> 12) & 1);
+            const bool nm = END && !pane && ((wflags >> (back ? 11 : 10)) & 1);
             const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
-            load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, c[f], false, 0., 0., nm2f, back ? V.u_b2[sg] : V.u_f2[sg]);
+            load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, c[f], pane, back ? V.abL[sg] : V.af0[sg],
+                       back ? V.ax_b[sg] : V.ax_f[sg], nm2f, back ? V.u_b2[sg] : V.u_f2[sg]);
             w[f].h = V.sc[(0 + kf) * NS + sg]; w[f].flow = V.sc[(2 + kf) * NS + sg];
             w[f].sol = V.sc[(4 + kf) * NS + sg]; w[f].ir = V.sc[(6 + kf) * NS + sg];
-            // one wall with its own zone behind it (TILE_SIMPLE, decided on the host): re-checked here
-            if (back) simple_ok = simple_ok && wc.zb == wl && wc.zf < 0 && szone;
+            // the zone topology decided on the host (TILE_SIMPLE / one zone per model behind its walls): re-checked here
+            if (back) simple_ok = simple_ok && wc.zf < 0 && (SIMPLE ? wc.zb == wl && szone : wc.zb >= 0 && wc.zb < tile.n_zones);
         } else {
             c[f] = FaceC{};   // the lean face path runs unpredicated: lanes without a face work on zeros
-            if (back && face_lane) simple_ok = simple_ok && !szone;
+            if (SIMPLE && back && face_lane) simple_ok = simple_ok && !szone;
         }
         ir_state[f] = w[f].ir;
     }
@@ -302,10 +318,12 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
     };
     // border conditions of sub-step s of main step `step` (old surface temperatures) → links for the node lanes
     WtLinks lk[NF];
+    double zface = zT;   // temperature of the zone this lane's (back) face looks at
+    if constexpr (!SIMPLE) zface = __shfl_sync(FULL, zT, zsrc);
     auto pre = [&](int step, int s) {
+        double h_[NF], rad_[NF], trad_[NF], asol_[NF];
 #pragma unroll
         for (int f = 0; f < NF; ++f) {
-            const bool back = G == 1 ? f == 1 : bk;
             const FaceC& cf = c[f];
             FaceS& wf = w[f];
             SubWeather sw;
@@ -314,14 +332,56 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
             const bool is_out = fl & FC_OUT;
             const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(cf.nx, sw.sin_wd), mul_rn(cf.ny, sw.cos_wd)) > 0.0);
             wf.forced = cf.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
-            wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? zT : cf.amb;
-            const double trad = is_out ? wf.trad_out : wf.air;
+            wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? zface : cf.amb;
+            trad_[f] = is_out ? wf.trad_out : wf.air;
             const double hn = tarp_lean(wf.air - wf.ts, cf.kpos, cf.kneg);
-            const double h = is_out ? hn + wf.forced : hn;
-            if (h != h) wf.status |= ST_NAN_H;
-            const double xr = 273.15 + (trad + wf.ts) / 2.;
-            const double rad = cf.eps4s * ((xr * xr) * xr);
-            const double asol = cf.alpha_end * wf.solar;
+            h_[f] = is_out ? hn + wf.forced : hn;
+            if (h_[f] != h_[f]) wf.status |= ST_NAN_H;
+            const double xr = 273.15 + (trad_[f] + wf.ts) / 2.;
+            rad_[f] = cf.eps4s * ((xr * xr) * xr);
+            asol_[f] = cf.alpha_end * wf.solar;
+        }
+        if constexpr (PANE) {
+            // A pane's two faces (first and last lane of the group; G = 1: the lane's two faces) exchange their border
+            // conditions and both solve the wall's 2x2 no-mass system (solve_pane) with identical inputs; each keeps its node.
+            if constexpr (G == 1) {
+                const double sol0 = c[0].alpha_end * w[0].solar + c[0].alpha_x * w[1].solar;
+                const double sol1 = c[1].alpha_end * w[1].solar + c[1].alpha_x * w[0].solar;
+                if (c[0].fl & FC_PANE) {
+                    double t0 = w[0].ts, t1 = w[1].ts;
+                    unsigned long long it = 0;
+                    solve_pane<true>(w[0].air, h_[0], rad_[0], trad_[0], sol0, w[1].air, h_[1], rad_[1], trad_[1], sol1,
+                                     c[0].u_nb, t0, t1, it, w[0].status);
+                    w[0].nm_iters += it;
+                    w[0].ts = t0;
+                    w[1].ts = t1;
+                }
+            } else {
+                const FaceC& cf = c[0];
+                FaceS& wf = w[0];
+                const int px = G - 1;   // partner lane = lane ^ (G - 1) for the first and the last lane of a group
+                const double sol_own = cf.alpha_end * wf.solar + cf.alpha_x * __shfl_xor_sync(FULL, wf.solar, px);
+                const double p_air = __shfl_xor_sync(FULL, wf.air, px), p_h = __shfl_xor_sync(FULL, h_[0], px);
+                const double p_rad = __shfl_xor_sync(FULL, rad_[0], px), p_trad = __shfl_xor_sync(FULL, trad_[0], px);
+                const double p_ts = __shfl_xor_sync(FULL, wf.ts, px), p_sol = __shfl_xor_sync(FULL, sol_own, px);
+                if (cf.fl & FC_PANE) {
+                    double t0 = bk ? p_ts : wf.ts, t1 = bk ? wf.ts : p_ts;
+                    unsigned long long it = 0;
+                    solve_pane<true>(bk ? p_air : wf.air, bk ? p_h : h_[0], bk ? p_rad : rad_[0], bk ? p_trad : trad_[0],
+                                     bk ? p_sol : sol_own, bk ? wf.air : p_air, bk ? h_[0] : p_h, bk ? rad_[0] : p_rad,
+                                     bk ? trad_[0] : p_trad, bk ? sol_own : p_sol, cf.u_nb, t0, t1, it, wf.status);
+                    if (!bk) wf.nm_iters += it;   // the chunk's iterations are counted once
+                    wf.ts = bk ? t1 : t0;
+                }
+            }
+        }
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            const bool back = G == 1 ? f == 1 : bk;
+            const FaceC& cf = c[f];
+            FaceS& wf = w[f];
+            const int fl = cf.fl;
+            const double h = h_[f], rad = rad_[f], trad = trad_[f], asol = asol_[f];
             lk[f].t_in = 0.;
             if constexpr (END) {
                 if (fl & FC_NM2) {
@@ -348,10 +408,8 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
     for (int step = 0; step < P.n_steps; ++step) {
         fill_weather(step);
         main_step_inputs(step);
-        if (P.zone_gain != nullptr && szone) {   // scheduled gains: this main step's q, sources re-summed in the reference's order
-            zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + sgz];
-            zone_sources(zc, za0, zb0);
-        }
+        // scheduled zone inputs: this main step's values, sources re-summed in the reference's order
+        if (szone && load_zone_schedule(P, step, sgz, zc)) zone_sources(zc, za0, zb0);
         for (int s = 0; s < S; ++s) {
 #ifdef HB_PHASE_CLOCKS
             wlast = clock64();
@@ -413,19 +471,40 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
                 wf.h = h;
                 wf.flow = (ts - wf.air) * h;
                 wf.e += wf.flow * cf.area * dt;
-                if (back) {
+                if (back && (SIMPLE || (cf.fl & FC_SPACE))) {
                     hA_b = h * cf.area;
                     hAT_b = hA_b * ts;
                 }
             }
             HB_WCLK(4)
-            {   // the lane's own wall is the zone's only surface (its back face): model.rs:489-597, 650-674
+            if constexpr (SIMPLE) {   // the lane's own wall is the zone's only surface (its back face): model.rs:489-597, 650-674
                 const double inv_cc = zone_inv_c_t<true>(zvol, zT);
                 const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + hAT_b, zb0 + hA_b);
                 if (szone) {
                     if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
                     zT = tn;
                 }
+                zface = zT;
+            } else {
+                // the back faces of a model's walls [sb, se) sit on every G-th lane: all zones of the tile are summed at once
+                // by a segmented shuffle reduction (deterministic; differs from the reference's sequential order,
+                // model.rs:556-590, by rounding only), advanced by the back lane of wall sb and broadcast to the model's faces
+                double va = hAT_b, vb = hA_b;
+#pragma unroll
+                for (int o = 1; o < W; o <<= 1) {
+                    const double ta = __shfl_down_sync(FULL, va, o * G), tb = __shfl_down_sync(FULL, vb, o * G);
+                    if (wl + o < seg_end) {
+                        va += ta;
+                        vb += tb;
+                    }
+                }
+                const double inv_cc = zone_inv_c_t<true>(zvol, zT);
+                const double tn = zone_advance<true>(zT, dt, inv_cc, za0 + va, zb0 + vb);
+                if (szone) {
+                    if (tn != tn) atomicOr(&V.status[sg], ST_NAN_ZONE);
+                    zT = tn;
+                }
+                zface = __shfl_sync(FULL, zT, zsrc);
             }
             HB_WCLK(5)
         }

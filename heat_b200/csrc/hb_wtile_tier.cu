@@ -9,7 +9,7 @@
 
 namespace hb {
 namespace {
-template <int G, int NL, int MODE>
+template <int G, int NL, int MODE, bool SIMPLE = true>
 cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
     size_t dyn = (size_t)kWtWarps * s_max * sizeof(SubWeather);   // <= 16 KB
     const int blocks = (n_tiles + kWtWarps - 1) / kWtWarps;
@@ -21,7 +21,7 @@ cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V,
         dyn = 225 * 1024;
         static bool configured = false;   // per instantiation
         if (!configured) {
-            cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
             configured = true;
         }
@@ -30,7 +30,7 @@ cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V,
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     cudaMemcpyToSymbol(hb_wt_clk, z, sizeof(z));
 #endif
-    hb_wtile_kernel<G, NL, MODE, true><<<blocks, 32 * kWtWarps, dyn, st>>>(V, P, ids, n_tiles, s_max);
+    hb_wtile_kernel<G, NL, MODE, SIMPLE><<<blocks, 32 * kWtWarps, dyn, st>>>(V, P, ids, n_tiles, s_max);
 #ifdef HB_PHASE_CLOCKS
     cudaStreamSynchronize(st);
     cudaMemcpyFromSymbol(o, hb_wt_clk, sizeof(o));
@@ -47,6 +47,9 @@ cudaError_t launch_wt_mode(int mode, int n_tiles, int s_max, cudaStream_t st, co
     switch (mode) {
         case kFaceLean: return launch_wt<G, NL, kFaceLean>(n_tiles, s_max, st, V, P, ids);
         case kFaceLeanEnd: return launch_wt<G, NL, kFaceLeanEnd>(n_tiles, s_max, st, V, P, ids);
+        case kFacePane:   // buildings: one zone behind all walls of a model, single panes, no-mass ends
+            if constexpr (G <= 8) return launch_wt<G, NL, kFacePane, false>(n_tiles, s_max, st, V, P, ids);
+            return cudaErrorInvalidValue;
         default: return cudaErrorInvalidValue;
     }
 }

@@ -224,18 +224,24 @@ class ThermalBatch:
 
     def march_series(self, n_steps: int, weather, *, weather_mode=_lib.WEATHER_STEP_CONSTANT, inputs=None,
                      input_mode=_lib.INPUT_STATE, ir_mode=_lib.IR_IRRADIANCE, model_site=None, record_every: int = 0,
-                     record_state: bool = False, zone_gain=None):
+                     record_state: bool = False, zone_gain=None, zone_infiltration_volume=None,
+                     zone_infiltration_temperature=None, zone_ventilation_volume=None,
+                     zone_ventilation_temperature=None):
         """Advance every model `n_steps` main steps. Returns (zone_T[rec][zones], state[rec][state_len]) or None.
 
         `zone_gain` [n_steps][zones]: schedule of the zones' HVAC + luminaire power [W] (model.rs:502-516); row t
-        replaces `q_internal` of `set_zone_inputs` during main step t."""
+        replaces `q_internal` of `set_zone_inputs` during main step t.  `zone_infiltration_*` / `zone_ventilation_*`
+        [n_steps][zones]: schedules of the infiltration / ventilation volume flow [m3/s] and temperature [C]
+        (model.rs:524-544; NaN temperature = absent in that step)."""
         keep: list = []
         s = self._series(n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, keep)
-        if zone_gain is not None:
-            zone_gain = _lib.f8(zone_gain)
-            assert zone_gain.size == n_steps * self.n_zones, f"zone_gain has {zone_gain.size} values"
-            s.zone_gain = _lib.ptr(zone_gain)
-            keep.append(zone_gain)
+        for name, table in zip(_lib.ZONE_SCHEDULES, (zone_gain, zone_infiltration_volume, zone_infiltration_temperature,
+                                                     zone_ventilation_volume, zone_ventilation_temperature)):
+            if table is not None:
+                table = _lib.f8(table)
+                assert table.size == n_steps * self.n_zones, f"{name} has {table.size} values"
+                setattr(s, name, _lib.ptr(table))
+                keep.append(table)
         zone_rec = state_rec = None
         if record_every > 0:
             n_rec = n_steps // record_every
@@ -277,6 +283,24 @@ class ThermalBatch:
     def reduce(self) -> _lib.EnsembleStatsC:
         out = _lib.EnsembleStatsC()
         _lib.check(self._lib.hb_reduce(self._h, C.byref(out)))
+        return out
+
+    # ---- the ensemble statistics over all GPUs of a job: NCCL inside the library ----
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """ncclGetUniqueId (rank 0); ship the 128 bytes to the other ranks by any means."""
+        buf = C.create_string_buffer(128)
+        _lib.check(_lib.load().hb_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, world: int) -> None:
+        assert len(unique_id) == 128
+        _lib.check(self._lib.hb_comm_init(self._h, C.c_char_p(unique_id), int(rank), int(world)))
+
+    def reduce_all(self) -> _lib.EnsembleStatsC:
+        """hb_reduce + ncclAllReduce (sum / min / max) — every rank gets the statistics of the whole ensemble."""
+        out = _lib.EnsembleStatsC()
+        _lib.check(self._lib.hb_reduce_all(self._h, C.byref(out)))
         return out
 
     def reset_energy(self) -> None:

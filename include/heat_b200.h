@@ -203,6 +203,15 @@ typedef struct {
                                      main step t (the reference reads these state elements once per sub-step and the
                                      caller rewrites them between march calls); NULL = the constants stay.  Host
                                      memory in hb_march_series AND hb_march_series_dev. */
+    /* Schedules of the zones' infiltration and ventilation (model.rs:524-544: volume flow [m3/s] and temperature [C]
+     * of each stream are state elements the reference reads every sub-step and the caller rewrites between march
+     * calls): HOST tables [n_steps][total zones]; row t replaces the constants of hb_set_zone_inputs during main step
+     * t; a NaN temperature = element absent in that step.  NULL = the constant stays.  A temperature table needs its
+     * volume table (or a volume set with hb_set_zone_inputs). */
+    const double* zone_infiltration_volume;
+    const double* zone_infiltration_temperature;
+    const double* zone_ventilation_volume;
+    const double* zone_ventilation_temperature;
 } hb_series;
 
 /* Advance every model by series->n_steps main steps (each = dt_subdivisions substeps, model.rs:369-424).
@@ -228,9 +237,24 @@ typedef struct {
     int64_t nomass_iterations;    /* total fixed-point iterations (surface.rs:808-896), branch-parity diagnostic */
     int64_t status_flags;         /* OR of per-surface status words (non-zero = HB_ERR_PHYSICS) */
 } hb_ensemble_stats;
-/* Local (this handle / this GPU) statistics; cross-GPU combination is a NCCL all-reduce done by the host layer. */
+/* Local (this handle / this GPU) statistics. */
 hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out);
 hb_status hb_reset_energy(hb_handle* h);
+
+/* ---- the path's only collective: the ensemble statistics over all GPUs of a job ----
+ * One process per GPU, one handle per process; walls and buildings never exchange anything while they march
+ * (a building's surfaces couple only through its own zone, model.rs:556-590).  NCCL (libnccl.so.2, resolved at run
+ * time) lives INSIDE the library: a Rust / C host needs no NCCL binding of its own.
+ *   rank 0:      hb_comm_unique_id(id)  → the host ships the 128 bytes to the other ranks (file, socket, MPI, ...)
+ *   every rank:  hb_comm_init(h, id, rank, world)      (ncclCommInitRank on the handle's device)
+ *   every rank:  hb_reduce_all(h, &stats)               (hb_reduce + ncclAllReduce: sums, minima, maxima; the status
+ *                                                        words are OR-ed bit by bit) — every rank gets the same result
+ * Without hb_comm_init (or with world == 1) hb_reduce_all equals hb_reduce. */
+#define HB_COMM_ID_BYTES 128
+hb_status hb_comm_unique_id(void* id_out);
+hb_status hb_comm_init(hb_handle* h, const void* id, int32_t rank, int32_t world);
+hb_status hb_comm_destroy(hb_handle* h);
+hb_status hb_reduce_all(hb_handle* h, hb_ensemble_stats* out);
 
 /* ---- EPW ingestion (host only; the reference reads weather through the `weather` crate, model.rs:372) ----
  * Hourly records of an EnergyPlus weather file in the layouts hb_series consumes:

@@ -116,8 +116,8 @@ void march_tile(const DevView& V, const SeriesDev& P, const Tile& tile, double* 
     int rec = 0;
     std::vector<double> left(TPB), right(TPB);
     for (int step = 0; step < P.n_steps; ++step) {
-        if (P.zone_gain)   // scheduled gains of this main step
-            for (int t = 0; t < tile.n_zones; ++t) zc[t].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + t];
+        for (int t = 0; t < tile.n_zones; ++t)   // scheduled zone inputs of this main step
+            load_zone_schedule(P, step, (int64_t)tile.zone_begin + t, zc[t]);
         if (P.single_site)
             for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
         for (int t = 0; t < W; ++t) {
@@ -292,7 +292,9 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
     const int S = tile.S;
     const double dt = tile.dt;
     const int64_t NS = V.n_dev_surfaces;
-    if (G * tile.W != 32 || !(tile.flags & TILE_SIMPLE)) throw std::runtime_error("emu: warp tile shape");
+    const bool SIMPLE = tile.flags & TILE_SIMPLE, PANE = !SIMPLE;   // buildings run the pane-capable kernel
+    const int W = 32 / G;
+    if (G * tile.W != 32) throw std::runtime_error("emu: warp tile shape");
     std::vector<double> T(32 * NL), A(32 * NL), B(32 * NL), X(32 * NL);
     struct Lane {
         int wl, part, base, n, last, nm1, nm2, nm3;
@@ -302,9 +304,11 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
         FaceS w[2];
         double ir_state[2];
         WallLinksEmu lk[2];
-        double zT, za0, zb0, zvol;
+        double zT, za0, zb0, zvol, zface;
         ZoneC zc;
         double ts_f, t1_f, t2_f, ts_b, t1_b, t2_b;
+        int zown, seg_end, zsrc;
+        double h_[2], rad_[2], trad_[2], asol_[2];
     };
     std::vector<Lane> L(32);
     std::vector<SubWeather> swt(kMaxSubsteps);
@@ -338,8 +342,15 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
         l.bk = l.part == G - 1;
         l.face_lane = l.first || l.bk;
         l.fwall = l.face_lane && l.n > 0;
-        l.szone = l.bk && l.wl < tile.n_zones;
-        l.sgz = (int64_t)tile.zone_begin + l.wl;
+        l.zown = SIMPLE ? l.wl : -1; l.seg_end = l.wl + 1; l.zsrc = lane;
+        if (!SIMPLE)
+            for (int j = 0; j < tile.n_zones; ++j) {
+                const int sb = V.z_surf_begin[tile.zone_begin + j], se = V.z_surf_end[tile.zone_begin + j];
+                if (sb == l.wl) l.zown = j;
+                if (l.wl >= sb && l.wl < se) { l.seg_end = se; l.zsrc = sb * G + G - 1; }
+            }
+        l.szone = l.bk && l.zown >= 0 && l.zown < tile.n_zones;
+        l.sgz = (int64_t)tile.zone_begin + (l.zown >= 0 ? l.zown : 0);
         l.zT = 0.; l.za0 = 0.; l.zb0 = 0.; l.zvol = 1.;
         l.zc = ZoneC{};
         if (l.szone) {
@@ -350,7 +361,8 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             l.zT = V.zoneT[gz];
             zone_sources(z, l.za0, l.zb0);
             l.zvol = z.vol;
-            if (!(z.sb == l.wl && z.se == l.wl + 1)) throw std::runtime_error("emu: warp tile is not SIMPLE");
+            if (SIMPLE ? !(z.sb == l.wl && z.se == l.wl + 1) : !(z.sb == l.wl && z.se <= W))
+                throw std::runtime_error("emu: warp tile zone topology");
         }
         for (int f = 0; f < NF; ++f) {
             const bool back = G == 1 ? f == 1 : l.bk;
@@ -360,10 +372,11 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             if (l.fwall) {
                 WallC wc;
                 load_wallc(V, l.sg, P.single_site != 0, wc);
-                const bool nm = END && ((wflags >> (back ? 11 : 10)) & 1);
+                const bool pane = PANE && ((wflags >> 12) & 1);
+                const bool nm = END && !pane && ((wflags >> (back ? 11 : 10)) & 1);
                 const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
-                load_facec(wc, back, back ? V.u_b[l.sg] : V.u_f[l.sg], nm, l.c[f], false, 0., 0., nm2f,
-                           back ? V.u_b2[l.sg] : V.u_f2[l.sg]);
+                load_facec(wc, back, back ? V.u_b[l.sg] : V.u_f[l.sg], nm, l.c[f], pane, back ? V.abL[l.sg] : V.af0[l.sg],
+                           back ? V.ax_b[l.sg] : V.ax_f[l.sg], nm2f, back ? V.u_b2[l.sg] : V.u_f2[l.sg]);
                 l.w[f].h = V.sc[(0 + kf) * NS + l.sg]; l.w[f].flow = V.sc[(2 + kf) * NS + l.sg];
                 l.w[f].sol = V.sc[(4 + kf) * NS + l.sg]; l.w[f].ir = V.sc[(6 + kf) * NS + l.sg];
             }
@@ -373,6 +386,7 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
     gather_back();
     for (Lane& l : L)
         for (int f = 0; f < NF; ++f) l.w[f].ts = (G == 1 ? f == 1 : l.bk) ? l.ts_b : l.ts_f;
+    for (Lane& l : L) l.zface = SIMPLE ? l.zT : L[l.zsrc].zT;
 
     auto weather_at = [&](int site, int step, int s, SubWeather& out) {
         const double* wtab = P.weather + (int64_t)site * P.weather_rows * 3;
@@ -418,16 +432,12 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                 }
                 face_begin_main_step(c, w);
             }
-            if (P.zone_gain != nullptr && l.szone) {
-                l.zc.q = P.zone_gain[(int64_t)step * P.n_dev_zones + l.sgz];
-                zone_sources(l.zc, l.za0, l.zb0);
-            }
+            if (l.szone && load_zone_schedule(P, step, l.sgz, l.zc)) zone_sources(l.zc, l.za0, l.zb0);
         }
         for (int s = 0; s < S; ++s) {
             // face role: border conditions with the old surface temperatures
             for (Lane& l : L)
                 for (int f = 0; f < NF; ++f) {
-                    const bool back = G == 1 ? f == 1 : l.bk;
                     const FaceC& cf = l.c[f];
                     FaceS& wf = l.w[f];
                     SubWeather sw;
@@ -436,14 +446,55 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                     const bool is_out = fl & FC_OUT;
                     const bool leeward = (fl & FC_TILTED) && !(add_rn(mul_rn(cf.nx, sw.sin_wd), mul_rn(cf.ny, sw.cos_wd)) > 0.0);
                     wf.forced = cf.forced_c * (leeward ? 0.5 : 1.0) * sw.sqrt_ws;
-                    wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? l.zT : cf.amb;
-                    const double trad = is_out ? wf.trad_out : wf.air;
+                    wf.air = is_out ? sw.t_out : (fl & FC_SPACE) ? l.zface : cf.amb;
+                    l.trad_[f] = is_out ? wf.trad_out : wf.air;
                     const double hn = tarp_lean(wf.air - wf.ts, cf.kpos, cf.kneg);
-                    const double h = is_out ? hn + wf.forced : hn;
-                    if (h != h) wf.status |= ST_NAN_H;
-                    const double xr = 273.15 + (trad + wf.ts) / 2.;
-                    const double rad = cf.eps4s * ((xr * xr) * xr);
-                    const double asol = cf.alpha_end * wf.solar;
+                    l.h_[f] = is_out ? hn + wf.forced : hn;
+                    if (l.h_[f] != l.h_[f]) wf.status |= ST_NAN_H;
+                    const double xr = 273.15 + (l.trad_[f] + wf.ts) / 2.;
+                    l.rad_[f] = cf.eps4s * ((xr * xr) * xr);
+                    l.asol_[f] = cf.alpha_end * wf.solar;
+                }
+            if (PANE) {   // both faces of a pane solve the wall's 2x2 system with identical inputs
+                std::vector<Lane> Q = L;   // values before the exchange (shuffles read the partners' registers)
+                for (int lane = 0; lane < 32; ++lane) {
+                    Lane& l = L[lane];
+                    if (G == 1) {
+                        if (!(l.c[0].fl & FC_PANE)) continue;
+                        const double sol0 = l.c[0].alpha_end * l.w[0].solar + l.c[0].alpha_x * l.w[1].solar;
+                        const double sol1 = l.c[1].alpha_end * l.w[1].solar + l.c[1].alpha_x * l.w[0].solar;
+                        double t0 = l.w[0].ts, t1 = l.w[1].ts;
+                        unsigned long long it = 0;
+                        solve_pane<true>(l.w[0].air, l.h_[0], l.rad_[0], l.trad_[0], sol0, l.w[1].air, l.h_[1], l.rad_[1],
+                                         l.trad_[1], sol1, l.c[0].u_nb, t0, t1, it, l.w[0].status);
+                        l.w[0].nm_iters += it;
+                        l.w[0].ts = t0;
+                        l.w[1].ts = t1;
+                    } else {
+                        if (!(l.c[0].fl & FC_PANE)) continue;
+                        const Lane& p = Q[lane ^ (G - 1)];
+                        const Lane& me = Q[lane];
+                        const double sol_own = me.c[0].alpha_end * me.w[0].solar + me.c[0].alpha_x * p.w[0].solar;
+                        const double p_sol = p.c[0].alpha_end * p.w[0].solar + p.c[0].alpha_x * me.w[0].solar;
+                        const bool bk = l.bk;
+                        double t0 = bk ? p.w[0].ts : me.w[0].ts, t1 = bk ? me.w[0].ts : p.w[0].ts;
+                        unsigned long long it = 0;
+                        solve_pane<true>(bk ? p.w[0].air : me.w[0].air, bk ? p.h_[0] : me.h_[0], bk ? p.rad_[0] : me.rad_[0],
+                                         bk ? p.trad_[0] : me.trad_[0], bk ? p_sol : sol_own, bk ? me.w[0].air : p.w[0].air,
+                                         bk ? me.h_[0] : p.h_[0], bk ? me.rad_[0] : p.rad_[0], bk ? me.trad_[0] : p.trad_[0],
+                                         bk ? sol_own : p_sol, me.c[0].u_nb, t0, t1, it, l.w[0].status);
+                        if (!bk) l.w[0].nm_iters += it;
+                        l.w[0].ts = bk ? t1 : t0;
+                    }
+                }
+            }
+            for (Lane& l : L)
+                for (int f = 0; f < NF; ++f) {
+                    const bool back = G == 1 ? f == 1 : l.bk;
+                    const FaceC& cf = l.c[f];
+                    FaceS& wf = l.w[f];
+                    const int fl = cf.fl;
+                    const double h = l.h_[f], rad = l.rad_[f], trad = l.trad_[f], asol = l.asol_[f];
                     l.lk[f].t_in = 0.;
                     if (END) {
                         if (fl & FC_NM2) {
@@ -530,8 +581,9 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
             }
             gather_back();
             // face role: new film coefficients, flows, zone
-            for (Lane& l : L) {
-                double hA_b = 0., hAT_b = 0.;
+            std::vector<double> va(32, 0.), vb(32, 0.);
+            for (int lane = 0; lane < 32; ++lane) {
+                Lane& l = L[lane];
                 for (int f = 0; f < NF; ++f) {
                     const bool back = G == 1 ? f == 1 : l.bk;
                     const FaceC& cf = l.c[f];
@@ -544,18 +596,34 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                     wf.h = h;
                     wf.flow = (ts - wf.air) * h;
                     wf.e += wf.flow * cf.area * dt;
-                    if (back) {
-                        hA_b = h * cf.area;
-                        hAT_b = hA_b * ts;
+                    if (back && (SIMPLE || (cf.fl & FC_SPACE))) {
+                        vb[lane] = h * cf.area;
+                        va[lane] = vb[lane] * ts;
                     }
                 }
+            }
+            if (!SIMPLE)   // segmented shuffle reduction over the back lanes of each model (stride G)
+                for (int o = 1; o < W; o <<= 1) {
+                    const std::vector<double> pa = va, pb = vb;
+                    for (int lane = 0; lane < 32; ++lane) {
+                        const Lane& l = L[lane];
+                        if (l.wl + o < l.seg_end) {
+                            const int src = lane + o * G < 32 ? lane + o * G : lane;
+                            va[lane] = pa[lane] + pa[src];
+                            vb[lane] = pb[lane] + pb[src];
+                        }
+                    }
+                }
+            for (int lane = 0; lane < 32; ++lane) {
+                Lane& l = L[lane];
                 if (l.szone) {
                     const double inv_cc = zone_inv_c_t<true>(l.zvol, l.zT);
-                    const double tn = zone_advance<true>(l.zT, dt, inv_cc, l.za0 + hAT_b, l.zb0 + hA_b);
+                    const double tn = zone_advance<true>(l.zT, dt, inv_cc, l.za0 + va[lane], l.zb0 + vb[lane]);
                     if (tn != tn) V.status[l.sg] |= ST_NAN_ZONE;
                     l.zT = tn;
                 }
             }
+            for (Lane& l : L) l.zface = SIMPLE ? l.zT : L[l.zsrc].zT;
         }
         if (P.record_every > 0 && (step + 1) % P.record_every == 0) {
             for (const Lane& l : L)
@@ -680,8 +748,8 @@ void march_tile_face(const DevView& V, const SeriesDev& P, const Tile& tile, dou
     int rec = 0;
     std::vector<double> left(NT), right(NT);
     for (int step = 0; step < P.n_steps; ++step) {
-        if (P.zone_gain)   // scheduled gains of this main step
-            for (int t = 0; t < tile.n_zones; ++t) zc[t].q = P.zone_gain[(int64_t)step * P.n_dev_zones + tile.zone_begin + t];
+        for (int t = 0; t < tile.n_zones; ++t)   // scheduled zone inputs of this main step
+            load_zone_schedule(P, step, (int64_t)tile.zone_begin + t, zc[t]);
         if (P.single_site)
             for (int s = 0; s < S; ++s) weather_at(0, step, s, swt[s]);
         for (int t = 0; t < W; ++t) {
@@ -891,13 +959,19 @@ int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, con
         P.single_site = single ? 1 : 0;
         P.slab_len = B.node_slab_len;
         P.n_dev_zones = B.n_dev_zones;
-        std::vector<double> gain_dev;
-        if (s->zone_gain && s->n_steps > 0) {
+        std::vector<double> sched_dev[5];
+        {
+            const double* src[5] = {s->zone_gain, s->zone_infiltration_volume, s->zone_infiltration_temperature,
+                                    s->zone_ventilation_volume, s->zone_ventilation_temperature};
+            const double** dst[5] = {&P.zone_gain, &P.zone_inf_v, &P.zone_inf_t, &P.zone_vent_v, &P.zone_vent_t};
             const int64_t nz = (int64_t)B.dev_zone_of.size();
-            gain_dev.assign((size_t)s->n_steps * B.n_dev_zones, 0.);
-            for (int64_t t = 0; t < s->n_steps; ++t)
-                for (int64_t z = 0; z < nz; ++z) gain_dev[(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = s->zone_gain[t * nz + z];
-            P.zone_gain = gain_dev.data();
+            for (int k = 0; k < 5; ++k) {
+                if (!src[k] || s->n_steps <= 0) continue;
+                sched_dev[k].assign((size_t)s->n_steps * B.n_dev_zones, k == 2 || k == 4 ? NAN : 0.);
+                for (int64_t t = 0; t < s->n_steps; ++t)
+                    for (int64_t z = 0; z < nz; ++z) sched_dev[k][(size_t)t * B.n_dev_zones + B.dev_zone_of[z]] = src[k][t * nz + z];
+                *dst[k] = sched_dev[k].data();
+            }
         }
         const int n_rec = s->record_every > 0 ? s->n_steps / s->record_every : 0;
         std::vector<double> zr, nr, sr;

@@ -77,7 +77,7 @@ class EmuBatch:
                               ventilation_temperature)]
 
     def _run(self, n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, record_every, record_state,
-             zone_gain=None):
+             zone_gain=None, schedules=None):
         s = _lib.SeriesC()
         weather = _lib.f8(weather)
         if weather.ndim == 2:
@@ -95,6 +95,13 @@ class EmuBatch:
             zone_gain = _lib.f8(zone_gain)
             assert zone_gain.size == n_steps * self.n_zones
             s.zone_gain = _lib.ptr(zone_gain)
+        keep = []
+        for name, table in (schedules or {}).items():
+            if table is not None:
+                table = _lib.f8(table)
+                assert table.size == n_steps * self.n_zones
+                setattr(s, name, _lib.ptr(table))
+                keep.append(table)
         zone_rec = state_rec = None
         if record_every > 0:
             n_rec = n_steps // record_every
@@ -117,9 +124,9 @@ class EmuBatch:
         return zone_rec, state_rec
 
     def march_series(self, n_steps, weather, *, weather_mode=0, inputs=None, input_mode=0, ir_mode=0, model_site=None,
-                     record_every=0, record_state=False, zone_gain=None):
+                     record_every=0, record_state=False, zone_gain=None, **schedules):
         return self._run(n_steps, weather, weather_mode, inputs, input_mode, ir_mode, model_site, record_every,
-                         record_state, zone_gain)
+                         record_state, zone_gain, schedules)
 
 
 def run_emu(name, max_steps=None, record_state=False):

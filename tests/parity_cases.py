@@ -684,3 +684,59 @@ def check_marches_again_after_failure(batch_cls):
     b2 = batch_cls(cases.validation_case("massive_full"))
     b2.march_series(3, np.array([[10.0, 90.0, 2.0]] * 3))
     assert np.array_equal(b2.get_state(), s1)
+
+
+def check_scheduled_infiltration_ventilation(batch_cls, n=10, n_steps=8):
+    """Infiltration / ventilation volume flow and temperature as per-main-step schedules (model.rs:524-544: the reference
+    reads these state elements every sub-step and the caller rewrites them between march calls): one series call with
+    the four tables (+ a gain schedule) against the oracle marched step by step with the inputs reset in between.
+    Walls with their own zone (register zone), shoeboxes (shared zone) and double-glazed shoeboxes (general kernel)."""
+    import oracle_py as O
+
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    builders = (lambda: (cases.wall_ensemble(2 * n, seed=91, mixed_fraction=0.4), None),
+                lambda: cases.shoebox_ensemble(n, seed=92, steps_per_hour=2),
+                lambda: cases.shoebox_ensemble(max(2, n // 3), seed=93, steps_per_hour=2, glazing=cases.double_glazing()))
+    for build in builders:
+        d, gains = build()
+        nz = int(d.model_zone_offset[-1])
+        rng = cases.SplitMix64(4321)
+        tab = dict(zone_gain=rng.uniform(n_steps * nz, -300.0, 900.0).reshape(n_steps, nz),
+                   zone_infiltration_volume=rng.uniform(n_steps * nz, 0.0, 0.1).reshape(n_steps, nz),
+                   zone_infiltration_temperature=rng.uniform(n_steps * nz, -5.0, 32.0).reshape(n_steps, nz),
+                   zone_ventilation_volume=rng.uniform(n_steps * nz, 0.0, 0.25).reshape(n_steps, nz),
+                   zone_ventilation_temperature=rng.uniform(n_steps * nz, 12.0, 28.0).reshape(n_steps, nz))
+        tab["zone_ventilation_temperature"][2] = np.nan          # ventilation off during step 2
+        tab["zone_infiltration_temperature"][::3, ::2] = np.nan   # and infiltration absent here and there
+        b = batch_cls(d)
+        if gains is not None:
+            b.set_zone_inputs(q_internal=gains)   # overridden by the schedule while it runs
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1, **tab)
+        got = b.get_state()
+        off = 0
+        zoff = d.model_zone_offset
+        for m in range(d.n_models):
+            z0, z1 = int(zoff[m]), int(zoff[m + 1])
+            om = O.OracleModel(d, m)
+            so = om.initial_state()
+            for t in range(n_steps):
+                om.set_zone_inputs(q_internal=tab["zone_gain"][t, z0:z1],
+                                   infiltration_volume=tab["zone_infiltration_volume"][t, z0:z1],
+                                   infiltration_temperature=tab["zone_infiltration_temperature"][t, z0:z1],
+                                   ventilation_volume=tab["zone_ventilation_volume"][t, z0:z1],
+                                   ventilation_temperature=tab["zone_ventilation_temperature"][t, z0:z1])
+                om.march_series(so, 1, weather[t:t + 2], weather_mode=1, inputs=inputs[t:t + 1], input_mode=1)
+            mine = got[off:off + len(so)]
+            nzm = z1 - z0
+            assert np.abs(mine[:nzm] - so[:nzm]).max() <= 1e-6, (m, mine[:nzm], so[:nzm])
+            for s in range(om.n_surfaces):
+                o = om.state_offset(s)
+                nn = om.n_nodes(s)
+                assert np.abs(mine[o + 8:o + 8 + nn] - so[o + 8:o + 8 + nn]).max() <= 1e-6, (m, s)
+            off += len(so)
+        # the schedules must matter
+        b2 = batch_cls(d)
+        if gains is not None:
+            b2.set_zone_inputs(q_internal=gains)
+        b2.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        assert np.abs(b2.get_state() - got).max() > 1e-3

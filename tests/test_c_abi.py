@@ -29,8 +29,8 @@ def test_struct_layouts_match_header():
     assert desc.LAYER_DTYPE.itemsize == 80      # hb_layer: 2×i32 + 9×f64
     assert desc.SURFACE_DTYPE.itemsize == 120   # hb_surface: 6×i32 + 12×f64
     assert ctypes.sizeof(_lib.BatchDescC) == 88
-    assert ctypes.sizeof(_lib.SeriesC) == 88      # hb_series incl. zone_gain (offset 80)
-    assert _lib.SeriesC.zone_gain.offset == 80
+    assert ctypes.sizeof(_lib.SeriesC) == 120     # hb_series incl. zone_gain (offset 80) + 4 infiltration / ventilation tables
+    assert _lib.SeriesC.zone_gain.offset == 80 and _lib.SeriesC.zone_ventilation_temperature.offset == 112
     assert ctypes.sizeof(_lib.ModelInfoC) == 56
     assert ctypes.sizeof(_lib.SurfaceInfoC) == 64
     assert ctypes.sizeof(_lib.EnsembleStatsC) == 96

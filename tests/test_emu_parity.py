@@ -155,3 +155,7 @@ def test_emulated_terrain_classes():
 
 def test_emulated_tilted_glazing():
     pc.check_tilted_glazing(emu_py.EmuBatch)
+
+
+def test_emulated_scheduled_infiltration_ventilation():
+    pc.check_scheduled_infiltration_ventilation(emu_py.EmuBatch)

@@ -276,3 +276,30 @@ def test_marches_again_after_reported_failure():
     from heat_b200.model import ThermalBatch
 
     pc.check_marches_again_after_failure(ThermalBatch)
+
+
+def test_scheduled_infiltration_ventilation_match_oracle():
+    """hb_series.zone_infiltration_* / zone_ventilation_*: per-main-step schedules (model.rs:524-544)."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_scheduled_infiltration_ventilation(ThermalBatch)
+
+
+def test_reduce_all_without_communicator_equals_reduce():
+    """hb_reduce_all without hb_comm_init (single GPU) is hb_reduce; with a one-rank NCCL communicator too."""
+    import ctypes as C
+    from heat_b200 import cases, _lib
+    from heat_b200.model import ThermalBatch
+
+    d = cases.wall_ensemble(200, seed=11, mixed_fraction=0.3)
+    weather, inputs = cases.synthetic_weather(7)
+    b = ThermalBatch(d)
+    b.march_series(6, weather, weather_mode=1, inputs=inputs[:6], input_mode=1)
+    a = b.reduce()
+    r = b.reduce_all()
+    for f, _ in _lib.EnsembleStatsC._fields_:
+        assert getattr(a, f) == getattr(r, f), f
+    b.comm_init(ThermalBatch.comm_unique_id(), 0, 1)
+    r = b.reduce_all()
+    for f, _ in _lib.EnsembleStatsC._fields_:
+        assert getattr(a, f) == getattr(r, f), f
