@@ -131,22 +131,30 @@ def _random_layers(rng: SplitMix64, n: int):
 
 
 def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, steps_per_hour: int = 1,
-                  max_layers: int = 4, max_nodes: int = 128) -> D.BatchDesc:
+                  max_layers: int = 4, max_nodes: int = 128, planner=None) -> D.BatchDesc:
     """`n_walls` independent models, each one exterior wall + its own zone (massive_full topology).
 
     Massive walls: 1..max_layers random solid layers. Mixed walls (fraction `mixed_fraction`): polyurethane /
     random solid / polyurethane, whose outer layers the reference's rule classifies as no-mass.
     Walls that the reference's discretization rule cuts into more than `max_nodes` nodes (thick layers of very low
     diffusivity) or leaves without any massive node are re-drawn, up to 8 times, then replaced by a 20 cm concrete wall.
+
+    `planner(desc) -> (n_nodes[n_walls], n_massive_chunks[n_walls])`: who evaluates the discretization rule for the
+    re-draw test; default: this library's host planning (`hb_create` with HB_DEVICE_NONE).
     """
     d = _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers)
     if not max_nodes:
         return d
-    from .model import ThermalBatch
+    if planner is None:
+        def planner(desc):
+            from .model import ThermalBatch
+            plan = ThermalBatch(desc, device=-1)  # host-only planning handle (discretization runs on the host anyway)
+            try:
+                return _bulk_n_nodes(plan, n_walls)
+            finally:
+                plan.close()
     for attempt in range(1, 10):
-        plan = ThermalBatch(d, device=-1)  # host-only planning handle (discretization runs on the host anyway)
-        n_nodes, n_massive = _bulk_n_nodes(plan, n_walls)
-        plan.close()
+        n_nodes, n_massive = planner(d)
         # SURVEY §8(d).3: re-draw too, walls whose every layer the rule classifies no-mass (nothing left to march)
         bad = np.nonzero((n_nodes > max_nodes) | (n_massive == 0))[0]
         if bad.size == 0:

@@ -118,6 +118,25 @@ class BatchDesc:
                          self.model_surface_offset[m0:m1 + 1] - s0, self.zone_volume[z0:z1], self.surfaces[s0:s1],
                          self.steps_per_hour, None if self.model_terrain is None else self.model_terrain[m0:m1])
 
+    def select_models(self, idx) -> "BatchDesc":
+        """The models `idx` (any order, any subset) as their own batch; the constructions pool is shared, not copied."""
+        idx = np.asarray(idx, np.int64)
+        zo, so = self.model_zone_offset.astype(np.int64), self.model_surface_offset.astype(np.int64)
+        nz, ns = zo[idx + 1] - zo[idx], so[idx + 1] - so[idx]
+
+        def gather(off, cnt):
+            total = int(cnt.sum())
+            if total == 0:
+                return np.zeros(0, np.int64)
+            start = np.repeat(off[idx], cnt)
+            within = np.arange(total) - np.repeat(np.cumsum(cnt) - cnt, cnt)
+            return start + within
+
+        zsel, ssel = gather(zo, nz), gather(so, ns)
+        return BatchDesc(self.layers, self.construction_offset, np.concatenate([[0], np.cumsum(nz)]),
+                         np.concatenate([[0], np.cumsum(ns)]), self.zone_volume[zsel], self.surfaces[ssel],
+                         self.steps_per_hour, None if self.model_terrain is None else self.model_terrain[idx])
+
     def model(self, m: int) -> "BatchDesc":
         """The single-model batch holding model `m` (constructions pool shared)."""
         z0, z1 = self.model_zone_offset[m], self.model_zone_offset[m + 1]

@@ -19,6 +19,31 @@ def shard_bounds(n_models: int, rank: int, world: int) -> Tuple[int, int]:
     return m0, m0 + base + (1 if rank < extra else 0)
 
 
+def deal_models(substeps, nodes, rank: int, world: int) -> np.ndarray:
+    """Indices of the models `rank` marches when ONE global ensemble is split over `world` GPUs.
+
+    A rank's time is set as much by its longest dependent chains (sub-steps per main step x horizon, in sequence) as by
+    its total work, so contiguous ranges of the sorted ensemble would hand every long chain to rank 0.  The models are
+    sorted by (sub-steps, nodes), both descending, and dealt `world` at a time, the heaviest of each hand to the rank
+    with the least work so far: every rank gets the same share of every part of the (S, N) distribution — equal tails
+    and equal sums of N·S (longest-processing-time rule, one hand at a time)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    substeps, nodes = np.asarray(substeps), np.asarray(nodes)
+    order = np.lexsort((-nodes, -substeps))
+    work = (substeps * nodes).astype(np.float64)[order]
+    load = np.zeros(world)
+    mine = []
+    for i in range(0, order.size, world):
+        hand = work[i:i + world]                       # already heaviest first (sorted by S, then N)
+        ranks = np.argsort(load, kind="stable")[:hand.size]
+        load[ranks] += hand
+        hit = np.nonzero(ranks == rank)[0]
+        if hit.size:
+            mine.append(order[i + hit[0]])
+    return np.sort(np.asarray(mine, np.int64))
+
+
 @dataclasses.dataclass
 class EnsembleStats:
     """Mirror of `hb_ensemble_stats` (include/heat_b200.h) as plain Python numbers."""

@@ -8,7 +8,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_reference_arm_prints_one_json_line_with_the_contract_keys():
-    env = dict(os.environ, HEAT_B200_CPU_SAMPLE_S="0.5")
+    # the reference arm may execute oracle/ only: with the product library unloadable it must still run
+    env = dict(os.environ, HEAT_B200_LIB="/nonexistent/libheat_b200.so")
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
                         "--units", "400", "--hours", "48"], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
@@ -21,7 +22,7 @@ def test_reference_arm_prints_one_json_line_with_the_contract_keys():
         assert k in d, k
     assert d["value"] > 0 and d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
-    assert "workload" in d["config"]
+    assert "workload" in d["config"] and d["config"]["cpu_sample"]["n_sample"] == 400
 
 
 def test_reference_arm_other_ranks_exit_quietly():

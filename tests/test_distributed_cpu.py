@@ -73,6 +73,20 @@ def test_shard_bounds_cover_everything():
             assert max(sizes) - min(sizes) <= 1
 
 
+def test_deal_models_balances_tails_and_work():
+    rng = np.random.default_rng(3)
+    S = rng.choice([2, 4, 10, 20, 58, 118], size=10_000, p=[.3, .3, .2, .15, .04, .01])
+    N = rng.integers(2, 128, size=10_000)
+    for world in (2, 4, 8):
+        parts = [D.deal_models(S, N, r, world) for r in range(world)]
+        allidx = np.sort(np.concatenate(parts))
+        assert np.array_equal(allidx, np.arange(S.size))            # a partition
+        work = np.array([(S[p] * N[p]).sum() for p in parts], float)
+        assert work.max() / work.min() < 1.01
+        tails = [int((S[p] == 118).sum()) for p in parts]
+        assert max(tails) - min(tails) <= 1
+
+
 def test_two_rank_gloo_equals_single_process():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")

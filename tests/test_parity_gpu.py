@@ -296,10 +296,15 @@ def test_reduce_all_without_communicator_equals_reduce():
     b = ThermalBatch(d)
     b.march_series(6, weather, weather_mode=1, inputs=inputs[:6], input_mode=1)
     a = b.reduce()
-    r = b.reduce_all()
-    for f, _ in _lib.EnsembleStatsC._fields_:
-        assert getattr(a, f) == getattr(r, f), f
+
+    def same(r):   # the sums are accumulated with atomics (order varies between calls); everything else is exact
+        for f, _ in _lib.EnsembleStatsC._fields_:
+            x, y = getattr(a, f), getattr(r, f)
+            if f.startswith("sum_") or f.endswith("_energy_j"):
+                assert abs(x - y) <= 1e-12 * max(1.0, abs(x)), f
+            else:
+                assert x == y, f
+
+    same(b.reduce_all())
     b.comm_init(ThermalBatch.comm_unique_id(), 0, 1)
-    r = b.reduce_all()
-    for f, _ in _lib.EnsembleStatsC._fields_:
-        assert getattr(a, f) == getattr(r, f), f
+    same(b.reduce_all())
