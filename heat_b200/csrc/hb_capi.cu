@@ -852,7 +852,7 @@ hb_status hb_comm_destroy(hb_handle* h) {
 
 hb_status hb_reduce_all(hb_handle* h, hb_ensemble_stats* out) {
     hb_status rc = hb_reduce(h, out);
-    if (rc != HB_OK || !h->comm || h->comm_world <= 1) return rc;
+    if (rc != HB_OK || !h->comm) return rc;   // (a one-rank communicator still goes through NCCL)
     return guarded([&] {
         Nccl& n = Nccl::get();
         constexpr int kBits = 8;   // status words: ST_* of hb_dev.hpp, OR-ed as a maximum per bit
