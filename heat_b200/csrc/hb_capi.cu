@@ -106,7 +106,7 @@ struct hb_handle {
     // device buffers (uploaded verbatim from hb::HostArrays)
     DevBuf<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     DevBuf<hb::CavityDev> cav;
-    DevBuf<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL, u_f, u_b, u_f2, u_b2, ax_f, ax_b;
+    DevBuf<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL, u_f, u_b, u_f2, u_b2, ax_f, ax_b, wa1f, wa1b, wa2f, wa2b;
     DevBuf<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     DevBuf<unsigned long long> nm_iters;
     DevBuf<int32_t> status;
@@ -168,6 +168,7 @@ struct hb_handle {
         V.desc_index = desc_index.p; V.area = area.p; V.nx = nx.p; V.ny = ny.p; V.cos_tilt = cos_tilt.p;
         V.forced_c = forced_c.p; V.eps_f = eps_f.p; V.eps_b = eps_b.p; V.amb_f = amb_f.p; V.amb_b = amb_b.p;
         V.hs_ov_f = hs_ov_f.p; V.hs_ov_b = hs_ov_b.p; V.af0 = af0.p; V.abL = abL.p; V.v0 = v0.p; V.vL = vL.p; V.u_f = u_f.p; V.u_b = u_b.p; V.u_f2 = u_f2.p; V.u_b2 = u_b2.p; V.ax_f = ax_f.p; V.ax_b = ax_b.p;
+        V.wa1f = wa1f.p; V.wa1b = wa1b.p; V.wa2f = wa2f.p; V.wa2b = wa2b.p;
         V.nm_off = nm_off.p; V.nm_pairs = nm_pairs.p; V.cav_off = cav_off.p; V.cav = cav.p;
         V.nodeT = nodeT.p; V.coefA = coefA.p; V.coefB = coefB.p;
         V.ext_u = ext_u.p; V.ext_mass = ext_mass.p; V.ext_af = ext_af.p; V.ext_ab = ext_ab.p;
@@ -219,6 +220,7 @@ void build_device(hb_handle* h) {
     h->amb_f.upload(H.amb_f, st); h->amb_b.upload(H.amb_b, st); h->hs_ov_f.upload(H.hs_ov_f, st);
     h->hs_ov_b.upload(H.hs_ov_b, st); h->af0.upload(H.af0, st); h->abL.upload(H.abL, st); h->v0.upload(H.v0, st);
     h->vL.upload(H.vL, st); h->u_f.upload(H.u_f, st); h->u_b.upload(H.u_b, st); h->u_f2.upload(H.u_f2, st); h->u_b2.upload(H.u_b2, st); h->ax_f.upload(H.ax_f, st); h->ax_b.upload(H.ax_b, st);
+    h->wa1f.upload(H.wa1f, st); h->wa1b.upload(H.wa1b, st); h->wa2f.upload(H.wa2f, st); h->wa2b.upload(H.wa2b, st);
     h->nodeT.upload(H.nodeT, st); h->coefA.upload(H.coefA, st); h->coefB.upload(H.coefB, st);
     h->ext_u.upload(H.ext_u, st); h->ext_mass.upload(H.ext_mass, st); h->ext_af.upload(H.ext_af, st);
     h->ext_ab.upload(H.ext_ab, st); h->sc.upload(H.sc, st);

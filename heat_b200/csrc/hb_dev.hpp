@@ -17,6 +17,7 @@ struct DevView {
     // ---- per device surface slot (tile.surface_begin + wall) ----
     const int32_t* n_nodes;   // 0 on padding slots
     const int32_t* flags;     // bits 0-3 front kind, 4-7 back kind, 8 distributed solar, 9 has cavity,
+                              // 15: double-glazed window solved by the front face lane (warp tiles; 10 / 11 clear)
                               // 10 / 11: node 0 / node n-1 is a single-node no-mass chunk (TILE_END tiles)
                               // 13 / 14: the front / back end is a TWO-node no-mass chunk (nodes 0,1 / n-2,n-1; 10 / 11 set too)
                               // 12: the wall is a pane (two no-mass nodes, chunk (0,2); TILE_PANE tiles; 10 and 11 set too)
@@ -45,6 +46,12 @@ struct DevView {
     const double* u_b2;       // conductance of the link node n-3 → n-2 (… at the back end)
     const double* ax_f;       // panes (flags bit 12): absorptance of node 0 for the BACK irradiance
     const double* ax_b;       // panes: absorptance of node n-1 for the FRONT irradiance
+    // double-glazed windows on warp tiles (flags bit 15: pane | gas | pane, four no-mass nodes): absorptances of the two
+    // inner nodes for the front / back irradiance
+    const double* wa1f;
+    const double* wa1b;
+    const double* wa2f;
+    const double* wa2b;
     const int32_t* nm_off;    // CSR over no-mass chunks: pairs (ini, fin)
     const int32_t* nm_pairs;
     const int32_t* cav_off;   // CSR over cavity links
@@ -84,7 +91,7 @@ struct HostArrays {
     std::vector<int32_t> n_nodes, flags, zone_f, zone_b, site, desc_index, nm_off, nm_pairs, cav_off;
     std::vector<CavityDev> cav;
     std::vector<double> area, nx, ny, cos_tilt, forced_c, eps_f, eps_b, amb_f, amb_b, hs_ov_f, hs_ov_b, af0, abL, v0, vL,
-        u_f, u_b, u_f2, u_b2, ax_f, ax_b;
+        u_f, u_b, u_f2, u_b2, ax_f, ax_b, wa1f, wa1b, wa2f, wa2b;
     std::vector<double> nodeT, coefA, coefB, ext_u, ext_mass, ext_af, ext_ab, sc, energy_f, energy_b;
     std::vector<unsigned long long> nm_iters;
     std::vector<int32_t> status;

@@ -273,6 +273,11 @@ inline bool is_pane(const SurfacePlan& P) {
     return P.n_nodes == 2 && P.cavities.empty() && P.nomass_chunks.size() == 2 && P.nomass_chunks[0] == 0 &&
            P.nomass_chunks[1] == 2;
 }
+// Double-glazed window: pane | gas | pane, four nodes without mass, one chunk (0, 4), the cavity between nodes 1 and 2.
+inline bool is_window4(const SurfacePlan& P) {
+    return P.n_nodes == 4 && P.cavities.size() == 1 && P.cavities[0].node == 1 && P.nomass_chunks.size() == 2 &&
+           P.nomass_chunks[0] == 0 && P.nomass_chunks[1] == 4;
+}
 constexpr int kBulkSubsteps = 56;   // below: tiles are scheduled for throughput, not for latency (hb_capi.cu S bins)
 constexpr int kTileKey = TILE_EXT | TILE_DIST | TILE_END | TILE_GEN | TILE_PANE | TILE_SIMPLE | TILE_WARP;   // tiles are uniform in these
 
@@ -431,17 +436,20 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     // uniform in lanes-per-wall G (from the model's largest wall), kernel variant and sub-step count S, so a block
     // runs one loop shape; models are sorted by (G, variant, S) and packed greedily.
     std::vector<int32_t> nmax_real_of(d->n_models, 0);
+    std::vector<char> wt_building_ok(d->n_models, 0);   // walls suit the warp-tile kernel's building mode
     int64_t n_end_long = 0;   // walls with no-mass ends and many sub-steps
     for (int m = 0; m < d->n_models; ++m) {
         ModelPlan& M = B.models[m];
         if (M.nmax > kMaxNodesBig) fail("surface has more nodes than the supported maximum (1022)");
         M.variant = 0;
         nmax_real_of[m] = M.nmax;
+        wt_building_ok[m] = 0;
         // `rest`: variant of the model without its single panes; a model whose other walls suit the face kernel keeps
         // its panes there too (both faces of a wall in one warp: tiles of at most 16 walls, >= 2 lanes per wall)
         int rest = 0;
         bool ends_only = true;   // every no-mass chunk is one node at an end of a wall of >= 3 nodes (panes aside)
         bool panes = false;
+        int rest_wt = 0;          // … and without its double-glazed windows (the warp-tile kernel solves those too)
         for (int k = 0; k < M.n_surfaces; ++k) {
             const SurfacePlan& P = B.plans[M.surface_begin + k];
             int v = 0;
@@ -454,6 +462,8 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
                 continue;
             }
             rest |= v;
+            if (is_window4(P)) continue;
+            rest_wt |= v;
             int nm_nodes = 0;   // no-mass chunks of one or two nodes at the ends, at least one massive node in between
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2) {
                 const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
@@ -462,6 +472,14 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
             }
             if (nm_nodes > 0 && P.n_nodes - nm_nodes < 1) ends_only = false;
         }
+        bool plain_faces = true;   // no film-coefficient override, no AmbientTemperature back face
+        for (int k = 0; k < M.n_surfaces; ++k) {
+            const hb_surface& s = B.surfaces[M.surface_begin + k];
+            if (s.back_kind == HB_BOUNDARY_AMBIENT || s.front_hs_override == s.front_hs_override ||
+                s.back_hs_override == s.back_hs_override)
+                plain_faces = false;
+        }
+        wt_building_ok[m] = (rest_wt == 0 || rest_wt == TILE_EXT) && ends_only && plain_faces;
         if (panes && (rest == 0 || rest == TILE_EXT) && ends_only) {
             const int nmax2 = std::max<int>(M.nmax, kNL - 1);
             if (walls_for_model(group_of_nodes(nmax2), M.n_surfaces, M.n_zones) <= 16) {
@@ -517,8 +535,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         // A building with ONE zone behind all its walls (every back face looks at it, no front face looks at a zone):
         // all-massive walls, no-mass ends, single panes — the warp-tile kernel sums the zone over the model's walls with
         // a segmented shuffle reduction.  All walls of the model sit in one warp: 32 / G >= n_surfaces.
-        if (!no_wtile && M.n_zones == 1 && M.n_surfaces >= 2 &&
-            (M.variant == 0 || M.variant == TILE_END || M.variant == (TILE_END | TILE_PANE))) {
+        if (!no_wtile && M.n_zones == 1 && M.n_surfaces >= 2 && wt_building_ok[m]) {
             bool ok = true;
             for (int k = 0; k < M.n_surfaces && ok; ++k) {
                 const hb_surface& s = B.surfaces[M.surface_begin + k];
@@ -641,7 +658,8 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
     H.site.assign(NS, 0); H.desc_index.assign(NS, 0); H.nm_off.assign(NS + 1, 0); H.cav_off.assign(NS + 1, 0);
     H.nm_pairs.clear(); H.cav.clear();
     for (auto* v : {&H.area, &H.nx, &H.ny, &H.cos_tilt, &H.forced_c, &H.eps_f, &H.eps_b, &H.amb_f, &H.amb_b, &H.af0,
-                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.u_f2, &H.u_b2, &H.ax_f, &H.ax_b, &H.energy_f, &H.energy_b})
+                    &H.abL, &H.v0, &H.vL, &H.u_f, &H.u_b, &H.u_f2, &H.u_b2, &H.ax_f, &H.ax_b, &H.wa1f, &H.wa1b, &H.wa2f, &H.wa2b,
+                    &H.energy_f, &H.energy_b})
         v->assign(NS, 0.);
     H.hs_ov_f.assign(NS, NAN); H.hs_ov_b.assign(NS, NAN);
     H.nodeT.assign(B.node_slab_len, 0.); H.coefA.assign(B.node_slab_len, 0.); H.coefB.assign(B.node_slab_len, 0.);
@@ -666,7 +684,13 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
         H.n_nodes[g] = n;
         H.flags[g] = (s.front_kind & 15) | ((s.back_kind & 15) << 4) | ((P.distributed_solar ? 1 : 0) << 8) |
                      ((P.cavities.empty() ? 0 : 1) << 9);
-        if (tile.flags & TILE_END)
+        const bool win4 = (tile.flags & TILE_WARP) && is_window4(P);
+        if (win4) {   // solved as a whole by the front face lane: no end-node placement (bits 10 / 11 stay clear)
+            H.flags[g] |= 1 << 15;
+            H.wa1f[g] = P.front_alpha[1]; H.wa1b[g] = P.back_alpha[1];
+            H.wa2f[g] = P.front_alpha[2]; H.wa2b[g] = P.back_alpha[2];
+        }
+        if ((tile.flags & TILE_END) && !win4)
             for (size_t c = 0; c + 1 < P.nomass_chunks.size(); c += 2)
             {
                 const int ini = P.nomass_chunks[c], fin = P.nomass_chunks[c + 1];
@@ -714,11 +738,11 @@ void pack_arrays(const BatchPlan& B, HostArrays& H) {
         }
         H.v0[g] = vof(0);
         H.vL[g] = vof(n - 1);
-        if (!P.distributed_solar || pane) {  // distributed: every absorptance goes through the per-node source term
+        if (!P.distributed_solar || pane || win4) {  // distributed: every absorptance goes through the per-node source term
             H.af0[g] = P.front_alpha[0];
             H.abL[g] = P.back_alpha[n - 1];
         }
-        if (pane) {
+        if (pane || win4) {
             H.ax_f[g] = P.back_alpha[0];
             H.ax_b[g] = P.front_alpha[n - 1];
         }
@@ -763,6 +787,7 @@ DevView HostArrays::view(const BatchPlan& B) {
     V.cos_tilt = cos_tilt.data(); V.forced_c = forced_c.data(); V.eps_f = eps_f.data(); V.eps_b = eps_b.data();
     V.amb_f = amb_f.data(); V.amb_b = amb_b.data(); V.hs_ov_f = hs_ov_f.data(); V.hs_ov_b = hs_ov_b.data();
     V.af0 = af0.data(); V.abL = abL.data(); V.v0 = v0.data(); V.vL = vL.data(); V.u_f = u_f.data(); V.u_b = u_b.data(); V.u_f2 = u_f2.data(); V.u_b2 = u_b2.data(); V.ax_f = ax_f.data(); V.ax_b = ax_b.data();
+    V.wa1f = wa1f.data(); V.wa1b = wa1b.data(); V.wa2f = wa2f.data(); V.wa2b = wa2b.data();
     V.nm_off = nm_off.data(); V.nm_pairs = nm_pairs.data(); V.cav_off = cav_off.data(); V.cav = cav.data();
     V.nodeT = nodeT.data(); V.coefA = coefA.data(); V.coefB = coefB.data();
     V.ext_u = ext_u.data(); V.ext_mass = ext_mass.data(); V.ext_af = ext_af.data(); V.ext_ab = ext_ab.data();

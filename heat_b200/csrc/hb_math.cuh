@@ -684,6 +684,7 @@ enum : int32_t {
     FC_FRONT_OUT = 128, FC_FRONT_SPACE = 256,   // kind of the wall's front boundary (needed by FC_BACK_AMB)
     FC_NM2 = 1024,           // FC_NM with a chunk of TWO no-mass nodes at this end (end node + its neighbour)
     FC_PANE = 512,           // face of a two-node all-no-mass wall (single glass pane): both faces solve one 2x2 system
+    FC_WIN4 = 2048,          // face of a double-glazed window (pane | gas | pane, four no-mass nodes; warp tiles)
 };
 // Constants of one face of one wall.
 struct FaceC {
@@ -703,7 +704,7 @@ struct FaceC {
     int32_t fl, zone, zone_front, site, desc_index, n;
 };
 HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f, bool pane = false,
-                      double alpha_own = 0., double alpha_x = 0., bool nm2 = false, double u_nb2 = 0.) {
+                      double alpha_own = 0., double alpha_x = 0., bool nm2 = false, double u_nb2 = 0., bool win4 = false) {
     const int wf = c.fl;
     int fl = back ? FC_BACK : 0;
     if (wf & (back ? WF_B_OUT : WF_F_OUT)) fl |= FC_OUT;
@@ -715,6 +716,7 @@ HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f,
     if (wf & WF_F_SPACE) fl |= FC_FRONT_SPACE;
     if (nm) fl |= FC_NM;
     if (pane) fl |= FC_PANE;
+    if (win4) fl |= FC_WIN4;
     if (nm && nm2) fl |= FC_NM2;
     f.fl = fl;
     f.kpos = back ? c.kpos_b : c.kpos_f;
@@ -722,8 +724,8 @@ HB_HD void load_facec(const WallC& c, bool back, double u_nb, bool nm, FaceC& f,
     f.eps4s = back ? c.eps4s_b : c.eps4s_f;
     f.area = c.area;
     f.v_end = back ? c.vL : c.v0;
-    f.alpha_end = pane ? alpha_own : back ? c.abL : c.af0;
-    f.alpha_x = pane ? alpha_x : 0.;
+    f.alpha_end = pane || win4 ? alpha_own : back ? c.abL : c.af0;
+    f.alpha_x = pane || win4 ? alpha_x : 0.;
     f.amb = back ? c.amb_b : c.amb_f;
     f.ov = back ? c.ov_b : c.ov_f;
     f.forced_c = c.forced_c; f.nx = c.nx; f.ny = c.ny;
@@ -889,6 +891,58 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
         if (count > 100000) { status |= ST_ITER_CAP; break; }
     }
 }
+// A double-glazed window: pane | gas | pane, four no-mass nodes, one chunk (0, 4) — solve_nomass written out for m = 4,
+// ini = 0, fin = n, with the cavity's temperature-dependent conductance (cavity.rs:59-69, gas.rs:82-315) re-evaluated
+// in every pass of the damped fixed point (surface.rs:790-898 around discretization.rs:596-700).
+// u01 / u23: conductance of the panes; sol[j]: absorbed solar of node j; t[0..3] in/out.
+HB_HD_NOINLINE void solve_window4(double air_f, double h_f, double rad_f, double trad_f, double air_b, double h_b,
+                                  double rad_b, double trad_b, const double (&sol)[4], double u01, double u23,
+                                  const CavityDev& cav, double (&t)[4], unsigned long long& iters, int& status) {
+    double old_err = 99999.;
+    int count = 0;
+    while (true) {
+        ++iters;
+        const double u12 = cavity_u(cav, t[1], t[2], status);
+        // assemble (discretization.rs:622-697): interior links, then the film edges
+        double dd[4] = {0., 0., 0., 0.}, du[3], rhs[4] = {0., 0., 0., 0.};
+        const double uu[3] = {u01, u12, u23};
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            dd[j] += -uu[j];
+            dd[j + 1] = dd[j + 1] - uu[j];
+            du[j] = uu[j];
+        }
+        rhs[0] += air_f * h_f + rad_f * (trad_f - t[0]);
+        dd[0] += -h_f;
+        rhs[3] += air_b * h_b + rad_b * (trad_b - t[3]);
+        dd[3] += -h_b;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rhs[j] = -(rhs[j] + sol[j]);   // surface.rs:828-832
+        // 3-diagonal Gaussian elimination without pivoting (surface.rs:834); the lower diagonal equals the upper one
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const double f = du[j] / dd[j];
+            dd[j + 1] -= f * du[j];
+            rhs[j + 1] -= f * rhs[j];
+        }
+        rhs[3] = rhs[3] / dd[3];
+#pragma unroll
+        for (int j = 2; j >= 0; --j) rhs[j] = (rhs[j] - du[j] * rhs[j + 1]) / dd[j];
+        double err = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) err += fabs(rhs[j] - t[j]);
+        if (err > old_err) break;                         // surface.rs:842-848
+        if (err != err) { status |= ST_NAN_ERR; break; }  // reference panics, :850
+#pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = (t[j] + rhs[j]) * 0.5;   // :878-883
+        const double tol = count < 100 ? 0.01 : 0.5;     // :885
+        if (err / 4.0 < tol) break;
+        old_err = err;
+        ++count;
+        if (count > 100000) { status |= ST_ITER_CAP; break; }
+    }
+}
+
 // Two no-mass nodes at an end of a wall (chunk (0,2) or (n-2,n)): the chunk's 2x2 system is solve_pane's with the
 // inner side replaced by the link to the massive neighbour (h := u2, air := T_neighbour, no radiation, no solar);
 // the chunk's first node is the end node at the front, the inner node at the back (solve_nomass's ordering).

@@ -32,8 +32,8 @@ __host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) { return 
 // T[k], k lane-dependent, as a select tree (registers cannot be indexed)
 template <int NL>
 __device__ __forceinline__ double wt_mux(const double (&T)[NL], int k) {
-    constexpr int P = NL <= 8 ? 8 : 16;
-    static_assert(NL <= 16, "wt_mux covers 16 slots");
+    constexpr int P = NL <= 8 ? 8 : NL <= 16 ? 16 : 32;
+    static_assert(NL <= 32, "wt_mux covers 32 slots");
     double m[P / 2];
 #pragma unroll
     for (int i = 0; i < P / 2; ++i) {
@@ -216,10 +216,11 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
             WallC wc;
             load_wallc(V, sg, P.single_site != 0, wc);
             const bool pane = PANE && ((wflags >> 12) & 1);
+            const bool win4 = PANE && ((wflags >> 15) & 1);
             const bool nm = END && !pane && ((wflags >> (back ? 11 : 10)) & 1);
             const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
             load_facec(wc, back, back ? V.u_b[sg] : V.u_f[sg], nm, c[f], pane, back ? V.abL[sg] : V.af0[sg],
-                       back ? V.ax_b[sg] : V.ax_f[sg], nm2f, back ? V.u_b2[sg] : V.u_f2[sg]);
+                       back ? V.ax_b[sg] : V.ax_f[sg], nm2f, back ? V.u_b2[sg] : V.u_f2[sg], win4);
             w[f].h = V.sc[(0 + kf) * NS + sg]; w[f].flow = V.sc[(2 + kf) * NS + sg];
             w[f].sol = V.sc[(4 + kf) * NS + sg]; w[f].ir = V.sc[(6 + kf) * NS + sg];
             // the zone topology decided on the host (TILE_SIMPLE / one zone per model behind its walls): re-checked here
@@ -229,6 +230,15 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
             if (SIMPLE && back && face_lane) simple_ok = simple_ok && !szone;
         }
         ir_state[f] = w[f].ir;
+    }
+    // double-glazed windows (flags bit 15): the front face lane solves the wall's four no-mass nodes (all in its slots)
+    const bool win4_lane = PANE && first && n == 4 && ((wflags >> 15) & 1);
+    double w_a1f = 0., w_a1b = 0., w_a2f = 0., w_a2b = 0., w_u23 = 0.;
+    CavityDev w_cav{0, 0, 1., 1., 0., 1., 1.};
+    if (win4_lane) {
+        w_a1f = V.wa1f[sg]; w_a1b = V.wa1b[sg]; w_a2f = V.wa2f[sg]; w_a2b = V.wa2b[sg];
+        w_u23 = V.u_b[sg];
+        w_cav = V.cav[V.cav_off[sg]];
     }
     if (!__all_sync(FULL, simple_ok) && lane == 0) atomicOr(&V.status[tile.surface_begin], ST_NAN_ZONE);
 
@@ -356,11 +366,24 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
                     w[0].ts = t0;
                     w[1].ts = t1;
                 }
+                if (win4_lane) {
+                    const double sol[4] = {sol0, w_a1f * w[0].solar + w_a1b * w[1].solar,
+                                           w_a2f * w[0].solar + w_a2b * w[1].solar, sol1};
+                    double t[4] = {T[0], T[1], T[2], T[3]};
+                    unsigned long long it = 0;
+                    solve_window4(w[0].air, h_[0], rad_[0], trad_[0], w[1].air, h_[1], rad_[1], trad_[1], sol, c[0].u_nb,
+                                  w_u23, w_cav, t, it, w[0].status);
+                    w[0].nm_iters += it;
+                    T[0] = t[0]; T[1] = t[1]; T[2] = t[2]; T[3] = t[3];
+                    w[0].ts = t[0];
+                    w[1].ts = t[3];
+                }
             } else {
                 const FaceC& cf = c[0];
                 FaceS& wf = w[0];
                 const int px = G - 1;   // partner lane = lane ^ (G - 1) for the first and the last lane of a group
-                const double sol_own = cf.alpha_end * wf.solar + cf.alpha_x * __shfl_xor_sync(FULL, wf.solar, px);
+                const double p_solar = __shfl_xor_sync(FULL, wf.solar, px);
+                const double sol_own = cf.alpha_end * wf.solar + cf.alpha_x * p_solar;
                 const double p_air = __shfl_xor_sync(FULL, wf.air, px), p_h = __shfl_xor_sync(FULL, h_[0], px);
                 const double p_rad = __shfl_xor_sync(FULL, rad_[0], px), p_trad = __shfl_xor_sync(FULL, trad_[0], px);
                 const double p_ts = __shfl_xor_sync(FULL, wf.ts, px), p_sol = __shfl_xor_sync(FULL, sol_own, px);
@@ -372,6 +395,17 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
                                      bk ? trad_[0] : p_trad, bk ? sol_own : p_sol, cf.u_nb, t0, t1, it, wf.status);
                     if (!bk) wf.nm_iters += it;   // the chunk's iterations are counted once
                     wf.ts = bk ? t1 : t0;
+                }
+                if (win4_lane) {   // front lane: own values are the front face's, the partner's the back face's
+                    const double sol[4] = {sol_own, w_a1f * wf.solar + w_a1b * p_solar, w_a2f * wf.solar + w_a2b * p_solar,
+                                           p_sol};
+                    double t[4] = {T[0], T[1], T[2], T[3]};
+                    unsigned long long it = 0;
+                    solve_window4(wf.air, h_[0], rad_[0], trad_[0], p_air, p_h, p_rad, p_trad, sol, cf.u_nb, w_u23, w_cav, t,
+                                  it, wf.status);
+                    wf.nm_iters += it;
+                    T[0] = t[0]; T[1] = t[1]; T[2] = t[2]; T[3] = t[3];
+                    wf.ts = t[0];
                 }
             }
         }

@@ -63,6 +63,10 @@ cudaError_t HB_CAT(launch_wtile_, HB_TIER)(int mode, int nl, int n_tiles, int s_
         case 10: return launch_wt_mode<G, 10>(mode, n_tiles, s_max, st, V, P, ids);
         case 12: return launch_wt_mode<G, 12>(mode, n_tiles, s_max, st, V, P, ids);
         case 16: return launch_wt_mode<G, 16>(mode, n_tiles, s_max, st, V, P, ids);
+#ifdef HB_WT_BIG_NL
+        case 20: return launch_wt_mode<G, 20>(mode, n_tiles, s_max, st, V, P, ids);
+        case 24: return launch_wt_mode<G, 24>(mode, n_tiles, s_max, st, V, P, ids);
+#endif
         default: return cudaErrorInvalidValue;
     }
 }

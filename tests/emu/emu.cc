@@ -309,6 +309,9 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
         double ts_f, t1_f, t2_f, ts_b, t1_b, t2_b;
         int zown, seg_end, zsrc;
         double h_[2], rad_[2], trad_[2], asol_[2];
+        bool win4_lane;
+        double w_a1f, w_a1b, w_a2f, w_a2b, w_u23;
+        CavityDev w_cav;
     };
     std::vector<Lane> L(32);
     std::vector<SubWeather> swt(kMaxSubsteps);
@@ -342,6 +345,14 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
         l.bk = l.part == G - 1;
         l.face_lane = l.first || l.bk;
         l.fwall = l.face_lane && l.n > 0;
+        l.win4_lane = PANE && l.first && l.n == 4 && ((wflags >> 15) & 1);
+        l.w_a1f = l.w_a1b = l.w_a2f = l.w_a2b = l.w_u23 = 0.;
+        l.w_cav = CavityDev{0, 0, 1., 1., 0., 1., 1.};
+        if (l.win4_lane) {
+            l.w_a1f = V.wa1f[l.sg]; l.w_a1b = V.wa1b[l.sg]; l.w_a2f = V.wa2f[l.sg]; l.w_a2b = V.wa2b[l.sg];
+            l.w_u23 = V.u_b[l.sg];
+            l.w_cav = V.cav[V.cav_off[l.sg]];
+        }
         l.zown = SIMPLE ? l.wl : -1; l.seg_end = l.wl + 1; l.zsrc = lane;
         if (!SIMPLE)
             for (int j = 0; j < tile.n_zones; ++j) {
@@ -373,10 +384,11 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                 WallC wc;
                 load_wallc(V, l.sg, P.single_site != 0, wc);
                 const bool pane = PANE && ((wflags >> 12) & 1);
+                const bool win4 = PANE && ((wflags >> 15) & 1);
                 const bool nm = END && !pane && ((wflags >> (back ? 11 : 10)) & 1);
                 const bool nm2f = nm && ((wflags >> (back ? 14 : 13)) & 1);
                 load_facec(wc, back, back ? V.u_b[l.sg] : V.u_f[l.sg], nm, l.c[f], pane, back ? V.abL[l.sg] : V.af0[l.sg],
-                           back ? V.ax_b[l.sg] : V.ax_f[l.sg], nm2f, back ? V.u_b2[l.sg] : V.u_f2[l.sg]);
+                           back ? V.ax_b[l.sg] : V.ax_f[l.sg], nm2f, back ? V.u_b2[l.sg] : V.u_f2[l.sg], win4);
                 l.w[f].h = V.sc[(0 + kf) * NS + l.sg]; l.w[f].flow = V.sc[(2 + kf) * NS + l.sg];
                 l.w[f].sol = V.sc[(4 + kf) * NS + l.sg]; l.w[f].ir = V.sc[(6 + kf) * NS + l.sg];
             }
@@ -459,6 +471,23 @@ void march_tile_warp(const DevView& V, const SeriesDev& P, const Tile& tile, dou
                 std::vector<Lane> Q = L;   // values before the exchange (shuffles read the partners' registers)
                 for (int lane = 0; lane < 32; ++lane) {
                     Lane& l = L[lane];
+                    if (l.win4_lane) {   // the front lane solves the window's four no-mass nodes
+                        const Lane& me = Q[lane];
+                        const int fb = G == 1 ? 1 : 0;                     // index of the back face's values …
+                        const Lane& p = G == 1 ? me : Q[lane ^ (G - 1)];   // … on this lane (G = 1) or on the partner
+                        const double sf = me.w[0].solar, sb = p.w[fb].solar;
+                        const double sol[4] = {me.c[0].alpha_end * sf + me.c[0].alpha_x * sb, l.w_a1f * sf + l.w_a1b * sb,
+                                               l.w_a2f * sf + l.w_a2b * sb, p.c[fb].alpha_end * sb + p.c[fb].alpha_x * sf};
+                        double t[4] = {T[lane * NL + 0], T[lane * NL + 1], T[lane * NL + 2], T[lane * NL + 3]};
+                        unsigned long long it = 0;
+                        solve_window4(me.w[0].air, me.h_[0], me.rad_[0], me.trad_[0], p.w[fb].air, p.h_[fb], p.rad_[fb],
+                                      p.trad_[fb], sol, me.c[0].u_nb, l.w_u23, l.w_cav, t, it, l.w[0].status);
+                        l.w[0].nm_iters += it;
+                        for (int q = 0; q < 4; ++q) T[lane * NL + q] = t[q];
+                        l.w[0].ts = t[0];
+                        if (G == 1) l.w[1].ts = t[3];
+                        continue;
+                    }
                     if (G == 1) {
                         if (!(l.c[0].fl & FC_PANE)) continue;
                         const double sol0 = l.c[0].alpha_end * l.w[0].solar + l.c[0].alpha_x * l.w[1].solar;
