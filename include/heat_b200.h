@@ -25,6 +25,15 @@
  * hand-written CUDA for sm_100a.  There is NO CPU fallback: every entry point that needs the device
  * fails with HB_ERR_CUDA when no CUDA device is usable.
  *
+ * Limits of this implementation where the reference has none (hb_create / hb_march_series return HB_ERR_INVALID with a
+ * message; nothing is silently approximated):
+ *   - a model's surfaces and zones must fit one tile: 32 surfaces / 32 zones when its largest wall has <= 62 nodes,
+ *     16 up to 126 nodes, 8 beyond (ThermalModel::new, model.rs:245-323, loops over any number);
+ *   - a no-mass chunk INSIDE a wall (between massive layers) may have at most 8 nodes (surface.rs:790-898 solves any
+ *     length); chunks at the ends of walls: one or two nodes, single panes, pane | gas | pane windows on the fast path;
+ *   - at most 128 sub-steps per main step (n >= 1 step per hour gives <= 120: min_dt = 60 s, model.rs:237,326-331);
+ *   - walls of more than 1022 nodes; more than 254 nodes only for all-massive walls / walls with no-mass ends.
+ *
  * Conventions: plain pointers and sizes only; all `double*` are HOST pointers unless the name ends in
  * `_dev`; a handle is not re-entrant; no global state except the thread-local last-error string.
  */
