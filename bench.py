@@ -87,13 +87,21 @@ def oracle_planner(desc):
     import ctypes as C
     import oracle_py as O
     n = desc.n_models
-    n_nodes, n_massive = np.zeros(n, np.int64), np.zeros(n, np.int64)
-    buf = np.zeros(2 * 1100, np.int32)
+    from heat_b200 import cases
+    n_nodes, n_massive, rk4 = np.zeros(n, np.int64), np.zeros(n, np.int64), np.zeros(n)
+    mass, u, buf = np.zeros(1100), np.zeros(1100), np.zeros(2 * 1100, np.int32)
     for m in range(n):
         om = O.OracleModel(desc, m)
-        n_nodes[m] = om.n_nodes(0)
+        k = n_nodes[m] = om.n_nodes(0)
         n_massive[m] = om._lib.ho_surface_chunks(om._m, 0, 1, buf.ctypes.data, buf.size)
-    return n_nodes, n_massive
+        om._lib.ho_surface_segments(om._m, 0, mass.ctypes.data, u.ctypes.data)
+        # dt·λmax <= 2·dt·max (left + right link) / mass (Gershgorin): only walls near the limit need the eigenvalue
+        link = np.where(u[:k] < 0.0, 8.0, u[:k])
+        row = (np.concatenate(([cases.FILM_MAX], link[:k - 1])) + np.concatenate((link[:k - 1], [cases.FILM_MAX]))) / mass[:k]
+        rk4[m] = 2.0 * om.dt * float(row.max())
+        if rk4[m] > 0.9 * cases.RK4_STABILITY_LIMIT:
+            rk4[m] = cases.rk4_number_np(mass[:k], u[:k], buf[:2 * n_massive[m]], om.dt)
+    return n_nodes, n_massive, rk4
 
 
 def make_ensemble(kind: str, units: int, seed: int, planner=None):

@@ -90,6 +90,7 @@ SYMBOLS = {
     "hb_get_model_info": (C.c_int32, [_P, C.c_int32, C.POINTER(ModelInfoC)]),
     "hb_get_surface_info": (C.c_int32, [_P, C.c_int64, C.POINTER(SurfaceInfoC)]),
     "hb_get_surface_arrays": (C.c_int32, [_P, C.c_int64, _P, _P, _P, _P, _P, _P, _P]),
+    "hb_surface_rk4_number": (C.c_int32, [_P, C.c_int64, C.c_double, _P]),
     "hb_set_state": (C.c_int32, [_P, _P]),
     "hb_get_state": (C.c_int32, [_P, _P]),
     "hb_set_zone_inputs": (C.c_int32, [_P, _P, _P, _P, _P, _P]),

@@ -130,6 +130,46 @@ def _random_layers(rng: SplitMix64, n: int):
     return k, rho, cp, th
 
 
+RK4_STABILITY_LIMIT = 2.785293563405282   # |R(z)| <= 1 of the classical RK4 on the negative real axis: -2.7853 <= z <= 0
+FILM_MAX = 30.0                           # W/m²K: TARP forced convection at the synthetic weather's 6 m/s + linearised IR
+
+
+def rk4_number_np(mass, u, massive_chunks, dt: float, film: float = FILM_MAX) -> float:
+    """dt·λmax(C⁻¹K) over the massive chunks of a wall — numpy statement of hb_surface_rk4_number (include/heat_b200.h)
+    for planners that must not load the library (bench.py's reference arm) and for the cross-check in tests/."""
+    mass, u = np.asarray(mass, np.float64), np.asarray(u, np.float64)
+    link = np.where(u < 0.0, 8.0, u)
+    n_nodes, worst = len(mass), 0.0
+    for ini, fin in np.asarray(massive_chunks).reshape(-1, 2):
+        n = int(fin - ini)
+        if n <= 0:
+            continue
+        g = np.arange(ini, fin)
+        left = np.where(g == 0, film, link[np.maximum(g - 1, 0)])
+        right = np.where(g == n_nodes - 1, film, link[g])
+        a = np.diag((left + right) / mass[g])
+        if n > 1:
+            e = link[g[:-1]] / np.sqrt(mass[g[:-1]] * mass[g[1:]])
+            a -= np.diag(e, 1) + np.diag(e, -1)
+        worst = max(worst, float(np.linalg.eigvalsh(a)[-1]))
+    return worst * dt
+
+
+def unstable_wall(steps_per_hour: int = 1) -> D.BatchDesc:
+    """Wall 347550 of the raw 800 000-wall draw of seed 42 (the 8-GPU configs[2] job): four solid layers, the third —
+    4 cm at k = 2.34 — left without inner nodes by the reference's rule between two light layers.  At the rule's
+    sub-step (30.5 s) its interface nodes give dt·λmax = 2.807 > RK4_STABILITY_LIMIT: the reference's march diverges
+    within a simulated day and panics."""
+    stack = [(0.26476804, 0.79516467, 473.21812667, 1954.91784947), (0.10924581, 0.05198719, 385.13555222, 934.12034676),
+             (0.04085655, 2.33743229, 462.85227834, 1455.90056047), (0.05593663, 0.0571488, 1276.53881926, 754.52769089)]
+    layers = [D.solid_layer(th, conductivity=k, density=rho, specific_heat=cp, front_emissivity=0.87629394,
+                            back_emissivity=0.87629394, front_solar_abs=0.8935592, back_solar_abs=0.8935592)
+              for th, k, rho, cp in stack]
+    s = D.surface(0, 60.0, 46.0, (-0.26801150678176583, -0.9634157110160533, 0.0), 1.5, front=(D.BOUNDARY_OUTDOOR, 0),
+                  back=(D.BOUNDARY_SPACE, 0))
+    return D.single_model([layers], [351.44779206], [s], steps_per_hour)
+
+
 def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, steps_per_hour: int = 1,
                   max_layers: int = 4, max_nodes: int = 128, planner=None) -> D.BatchDesc:
     """`n_walls` independent models, each one exterior wall + its own zone (massive_full topology).
@@ -138,9 +178,14 @@ def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, 
     random solid / polyurethane, whose outer layers the reference's rule classifies as no-mass.
     Walls that the reference's discretization rule cuts into more than `max_nodes` nodes (thick layers of very low
     diffusivity) or leaves without any massive node are re-drawn, up to 8 times, then replaced by a 20 cm concrete wall.
+    So are the few stacks (about 1 in 10^5: a thin, very conductive layer the rule leaves without inner nodes, between
+    lighter ones) on which the reference's own explicit RK4 is unstable at the sub-step its rule picks — dt·λmax above
+    RK4_STABILITY_LIMIT, see hb_surface_rk4_number: the reference marches such a wall to NaN and panics, and so, to the
+    same message, does this library (tests/parity_cases.py check_unstable_wall_fails_like_reference); they are not valid
+    input of the path.
 
-    `planner(desc) -> (n_nodes[n_walls], n_massive_chunks[n_walls])`: who evaluates the discretization rule for the
-    re-draw test; default: this library's host planning (`hb_create` with HB_DEVICE_NONE).
+    `planner(desc) -> (n_nodes[n_walls], n_massive_chunks[n_walls], rk4_number[n_walls])`: who evaluates the
+    discretization rule for the re-draw test; default: this library's host planning (`hb_create` with HB_DEVICE_NONE).
     """
     d = _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers)
     if not max_nodes:
@@ -154,9 +199,9 @@ def wall_ensemble(n_walls: int, seed: int = 42, *, mixed_fraction: float = 0.0, 
             finally:
                 plan.close()
     for attempt in range(1, 10):
-        n_nodes, n_massive = planner(d)
+        n_nodes, n_massive, rk4 = planner(d)
         # re-draw too, walls whose every layer the rule classifies no-mass (nothing left to march)
-        bad = np.nonzero((n_nodes > max_nodes) | (n_massive == 0))[0]
+        bad = np.nonzero((n_nodes > max_nodes) | (n_massive == 0) | (rk4 > RK4_STABILITY_LIMIT))[0]
         if bad.size == 0:
             return d
         # the layers to re-draw: every layer of a bad wall except the fixed polyurethane skins of mixed walls
@@ -178,13 +223,17 @@ def _bulk_n_nodes(plan, n: int) -> np.ndarray:
     from . import _lib
     out = np.empty(n, np.int64)
     massive = np.empty(n, np.int64)
-    info = _lib.SurfaceInfoC()
-    fn, h = plan._lib.hb_get_surface_info, plan._h
+    rk4 = np.empty(n, np.float64)
+    info, number = _lib.SurfaceInfoC(), C.c_double(0.0)
+    fn, fr, h = plan._lib.hb_get_surface_info, plan._lib.hb_surface_rk4_number, plan._h
+    pi, pn, film = C.byref(info), C.byref(number), C.c_double(FILM_MAX)
     for s in range(n):
-        fn(h, s, C.byref(info))
+        fn(h, s, pi)
+        fr(h, s, film, pn)
         out[s] = info.n_nodes
         massive[s] = info.n_massive_chunks
-    return out, massive
+        rk4[s] = number.value
+    return out, massive, rk4
 
 
 def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layers) -> D.BatchDesc:
@@ -234,12 +283,13 @@ def _wall_ensemble_draw(n_walls, seed, mixed_fraction, steps_per_hour, max_layer
     return D.BatchDesc(layers, off.astype(np.int32), ar, ar, volume, surfaces, steps_per_hour)
 
 
-def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 1, glazing=None):
+def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 1, glazing=None, params=None):
     """`n_buildings` single-zone shoeboxes: 4 walls + roof (Outdoor ↔ Space), floor (AmbientTemperature front) and one
     single-layer window, parametric sweep. Returns (BatchDesc, q_internal[n_buildings]).
 
     `glazing`: list of layers of the window construction shared by all buildings (default: one 6 mm pane); e.g.
-    `double_glazing()` — panes + gas cavity, ISO 9050 optics (glazing.rs:180-286) and Cavity::u_value (cavity.rs:59-69)."""
+    `double_glazing()` — panes + gas cavity, ISO 9050 optics (glazing.rs:180-286) and Cavity::u_value (cavity.rs:59-69).
+    `params`: (n_lay[n], k, rho, cp, th [Σ n_lay], eps[n], alpha[n], volume[n], gains[n]) instead of the seeded draw."""
     rng = SplitMix64(seed)
     n = n_buildings
     # one opaque construction per building (1-3 layers) + one glazing construction shared by all
@@ -254,6 +304,11 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     alpha = rng.uniform(n, 0.2, 0.9)
     volume = rng.uniform(n, 50.0, 600.0)
     gains = rng.uniform(n, 0.0, 500.0)
+    if params is not None:
+        n_lay, k, rho, cp, th, eps, alpha, volume, gains = (np.asarray(a) for a in params)
+        np.cumsum(n_lay, out=off[1:n + 1])
+        total = int(off[n])
+        off[n + 1] = total + len(glazing)
     layers = np.zeros(total + len(glazing), D.LAYER_DTYPE)
     layers["kind"] = D.LAYER_SOLID
     layers["thickness"][:total], layers["conductivity"][:total] = th, k
@@ -297,6 +352,18 @@ def shoebox_ensemble(n_buildings: int, seed: int = 43, *, steps_per_hour: int = 
     zo = np.arange(n + 1, dtype=np.int32)
     so = (np.arange(n + 1, dtype=np.int64) * 7).astype(np.int32)
     return D.BatchDesc(layers, off.astype(np.int32), zo, so, volume, surfaces.reshape(-1), steps_per_hour), gains
+
+
+def slow_nomass_shoebox():
+    """Building 872809 of the 10^6-shoebox draw of seed 43 (the 8-GPU configs[3] job): one 3 cm light, conductive layer,
+    so all seven surfaces are pairs of no-mass nodes and the zone is the only mass.  In hour 65 of the synthetic weather
+    the reference's damped fixed point (surface.rs:808-896) creeps: about 1.4·10^5 passes in one main step, more than
+    10^5 of them in a single solve — far below the reference's own limit of 99 199 000, which is the only limit there is.
+    Returns (BatchDesc, q_internal[1])."""
+    one = lambda v: np.array([v])
+    return shoebox_ensemble(1, params=(one(1), one(1.8548797806167274), one(361.55561998828756), one(748.820901506258),
+                                       one(0.031159117865444532), one(0.8685396147411738), one(0.4314982273132669),
+                                       one(303.80703082049365), one(108.11485792021885)))
 
 
 def double_glazing(gas=D.GAS_ARGON, gap=0.012):

@@ -459,7 +459,12 @@ void check_status(hb_handle* h) {
         if (st[g] & hb::ST_NAN_ZONE) what += " Future temperatures is NaN;";
         if (st[g] & hb::ST_ITER_CAP) what += " Excessive number of iterations;";
         if (st[g] & hb::ST_BAD_GAMMA) what += " cavity tilt out of range;";
-        throw std::domain_error("physics failure on device surface slot " + std::to_string(g) + ":" + what);
+        // name the surface the way the caller knows it (descriptor order), not only the device slot
+        int64_t surf = -1, model = -1;
+        for (size_t gd = 0; gd < h->plan.dev_surface_of.size(); ++gd)
+            if (h->plan.dev_surface_of[gd] == (int32_t)g) { surf = (int64_t)gd; model = h->plan.surface_model[gd]; break; }
+        throw std::domain_error("physics failure on surface " + std::to_string(surf) + " of the batch (model " +
+                                std::to_string(model) + ", device surface slot " + std::to_string(g) + "):" + what);
     }
 }
 
@@ -548,6 +553,14 @@ hb_status hb_get_surface_info(const hb_handle* h, int64_t s, hb_surface_info* ou
         out->back_emissivity = P.back_emissivity;
         out->wind_speed_modifier = P.wind_speed_modifier;
         out->cos_tilt = P.cos_tilt;
+    });
+}
+
+hb_status hb_surface_rk4_number(const hb_handle* h, int64_t s, double film, double* out) {
+    return guarded([&] {
+        if (s < 0 || s >= (int64_t)h->plan.plans.size()) throw std::runtime_error("surface index out of range");
+        if (!out || !(film >= 0.)) throw std::runtime_error("hb_surface_rk4_number: film must be >= 0 and out non-NULL");
+        *out = hb::rk4_number(h->plan.plans[s], h->plan.models[h->plan.surface_model[s]].dt, film);
     });
 }
 

@@ -358,6 +358,52 @@ void wt_merge_leftovers(BatchPlan& B) {
     }
 }
 
+// dt · λmax(C⁻¹K) over the massive chunks of a wall: what the classical RK4 of surface.rs:228-308 needs below 2.7853
+// (its stability interval on the negative real axis) for the march to stay bounded.  K is the chunk's tridiagonal
+// conductance matrix (discretization.rs:596-700): solid links between its nodes, plus — on the diagonal only — the link
+// to whatever lies beyond either end: the film (`film` W/m²K, convective + linearised IR) at a face of the wall, the
+// solid link to a no-mass neighbour, 8 W/m²K for a gas cavity.  C⁻¹K is similar to the symmetric tridiagonal
+// (d_i, e_i) = ((K_ii / m_i), u_i / sqrt(m_i m_{i+1})); its largest eigenvalue lies between max d_i and the Gershgorin
+// bound and is found by bisection on the Sturm count to 1e-7 relative.
+double rk4_number(const SurfacePlan& P, double dt, double film) {
+    constexpr double kCavityU = 8.;
+    auto link = [&](int i) { return P.u[i] < 0. ? kCavityU : P.u[i]; };   // node i ↔ node i+1
+    double worst = 0.;
+    std::vector<double> d, e2;
+    for (size_t c = 0; c + 1 < P.massive_chunks.size(); c += 2) {
+        const int ini = P.massive_chunks[c], fin = P.massive_chunks[c + 1], n = fin - ini;
+        if (n <= 0) continue;
+        d.assign(n, 0.);
+        e2.assign(n, 0.);   // e2[i] = e_i² couples i and i+1
+        double lo = 0., hi = 0.;
+        for (int i = 0; i < n; ++i) {
+            const int g = ini + i;
+            const double left = g == 0 ? film : link(g - 1), right = g == P.n_nodes - 1 ? film : link(g);
+            d[i] = (left + right) / P.mass[g];
+            if (i + 1 < n) e2[i] = link(g) * link(g) / (P.mass[g] * P.mass[g + 1]);
+            lo = std::max(lo, d[i]);
+        }
+        for (int i = 0; i < n; ++i)
+            hi = std::max(hi, d[i] + (i ? std::sqrt(e2[i - 1]) : 0.) + (i + 1 < n ? std::sqrt(e2[i]) : 0.));
+        // all n eigenvalues are below x  <=>  every pivot of the LDLᵀ factorisation of (x·I − A) is positive
+        auto all_below = [&](double x) {
+            double q = x - d[0];
+            if (q <= 0.) return false;
+            for (int i = 1; i < n; ++i) {
+                q = x - d[i] - e2[i - 1] / q;
+                if (q <= 0.) return false;
+            }
+            return true;
+        };
+        while (hi - lo > 1e-7 * hi) {
+            const double mid = 0.5 * (lo + hi);
+            (all_below(mid) ? hi : lo) = mid;
+        }
+        worst = std::max(worst, hi);
+    }
+    return worst * dt;
+}
+
 void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
     if (!d) fail("null descriptor");
     if (d->steps_per_hour <= 0) fail("steps_per_hour must be positive");

@@ -181,5 +181,7 @@ struct BatchPlan {
 void plan_surface(const hb_layer* layers, int n_layers, const hb_surface& s, int terrain, double main_dt,
                   SurfacePlan& out);
 void plan_batch(const hb_batch_desc* desc, BatchPlan& out, bool build_tiles = true);
+// dt·λmax of the explicit march of a wall's massive chunks (see hb_surface_rk4_number in heat_b200.h)
+double rk4_number(const SurfacePlan& P, double dt, double film);
 
 }  // namespace hb

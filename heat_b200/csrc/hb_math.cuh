@@ -25,6 +25,10 @@
 namespace hb {
 
 constexpr double kPi = 3.14159265358979323846;
+// passes the no-mass fixed point may take before the reference gives up ("Excessive number of iterations",
+// surface.rs:869-873).  A solve that gets anywhere near it is a lane spinning for seconds — as the reference's would be:
+// some all-no-mass shoeboxes need > 10^5 passes in a sub-step and the reference carries on (tests: check_slow_nomass_…).
+constexpr int kNoMassIterCap = 99199000;
 
 HB_HD double hb_nan() {
 #if defined(__CUDA_ARCH__)
@@ -475,12 +479,12 @@ HB_HD_NOINLINE void solve_nomass(const WallC& c, WallS& w, const ExtWall& X, con
         for (int j = 0; j < m; ++j) err += fabs(rhs[j] - tl[j + 1]);
         if (err > old_err) break;                           // surface.rs:842-848
         if (err != err) { w.status |= ST_NAN_ERR; break; }  // reference panics, :850
+        if (!(count < kNoMassIterCap)) { w.status |= ST_ITER_CAP; break; }   // surface.rs:869-873
         for (int j = 0; j < m; ++j) tl[j + 1] = (tl[j + 1] + rhs[j]) * 0.5;  // :878-883
         const double tol = count < 100 ? 0.01 : 0.5;       // :885
         if (err / (double)m < tol) break;
         old_err = err;
         ++count;
-        if (count > 100000) { w.status |= ST_ITER_CAP; break; }
     }
     for (int j = 0; j < m; ++j) X.setT(ini + j, tl[j + 1]);
 }
@@ -788,12 +792,12 @@ HB_HD double solve_end_node(double air, double h, double rad, double trad, doubl
             const double err = fabs(x - t);
             if (err > old_err) break;
             if (err != err) { status |= ST_NAN_ERR; break; }
+            if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
             t = (t + x) * 0.5;
             const double tol = count < 100 ? 0.01 : 0.5;
             if (err < tol) break;
             old_err = err;
             ++count;
-            if (count > 100000) { status |= ST_ITER_CAP; break; }
         }
         return t;
     }
@@ -805,12 +809,12 @@ HB_HD double solve_end_node(double air, double h, double rad, double trad, doubl
         const double err = fabs(x - t);
         if (err > old_err) break;
         if (err != err) { status |= ST_NAN_ERR; break; }
+        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
         t = (t + x) * 0.5;
         const double tol = count < 100 ? 0.01 : 0.5;
         if (err < tol) break;
         old_err = err;
         ++count;
-        if (count > 100000) { status |= ST_ITER_CAP; break; }
     }
     return t;
 }
@@ -860,13 +864,13 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
             const double err = fabs(x0 - t0) + fabs(x1 - t1);
             if (err > old_err) break;
             if (err != err) { status |= ST_NAN_ERR; break; }
+            if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
             t0 = (t0 + x0) * 0.5;
             t1 = (t1 + x1) * 0.5;
             const double tol = count < 100 ? 0.01 : 0.5;
             if (err * 0.5 < tol) break;
             old_err = err;
             ++count;
-            if (count > 100000) { status |= ST_ITER_CAP; break; }
         }
         return;
     }
@@ -882,13 +886,13 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
         const double err = fabs(x0 - t0) + fabs(x1 - t1);
         if (err > old_err) break;
         if (err != err) { status |= ST_NAN_ERR; break; }
+        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
         t0 = (t0 + x0) * 0.5;
         t1 = (t1 + x1) * 0.5;
         const double tol = count < 100 ? 0.01 : 0.5;
         if (err / 2.0 < tol) break;
         old_err = err;
         ++count;
-        if (count > 100000) { status |= ST_ITER_CAP; break; }
     }
 }
 // A double-glazed window: pane | gas | pane, four no-mass nodes, one chunk (0, 4) — solve_nomass written out for m = 4,
@@ -933,13 +937,13 @@ HB_HD_NOINLINE void solve_window4(double air_f, double h_f, double rad_f, double
         for (int j = 0; j < 4; ++j) err += fabs(rhs[j] - t[j]);
         if (err > old_err) break;                         // surface.rs:842-848
         if (err != err) { status |= ST_NAN_ERR; break; }  // reference panics, :850
+        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
 #pragma unroll
         for (int j = 0; j < 4; ++j) t[j] = (t[j] + rhs[j]) * 0.5;   // :878-883
         const double tol = count < 100 ? 0.01 : 0.5;     // :885
         if (err / 4.0 < tol) break;
         old_err = err;
         ++count;
-        if (count > 100000) { status |= ST_ITER_CAP; break; }
     }
 }
 

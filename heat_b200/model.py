@@ -173,6 +173,12 @@ class ThermalBatch:
         out["n_nodes"] = info.n_nodes
         return out
 
+    def surface_rk4_number(self, s: int, film: float = 30.0) -> float:
+        """dt·λmax of the wall's explicit march (bounded below 2.7853), hb_surface_rk4_number."""
+        out = C.c_double(0.0)
+        _lib.check(self._lib.hb_surface_rk4_number(self._h, s, float(film), C.byref(out)))
+        return out.value
+
     # ---- state ----
     def get_state(self, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:

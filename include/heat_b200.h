@@ -161,6 +161,14 @@ hb_status hb_get_surface_arrays(const hb_handle* h, int64_t surface, int32_t* n_
                                 double* front_alpha, double* back_alpha, int32_t* massive_chunks,
                                 int32_t* nomass_chunks);
 
+/* Diagnostic with no counterpart in the reference: dt·λmax(C⁻¹K) of the surface's massive chunks at the model's
+ * sub-step dt, films of `film` W/m²K (convective + linearised IR) on both faces.  The reference's explicit RK4
+ * (surface.rs:228-308) is bounded only below 2.7853; its discretization rule (discretization.rs:95-544) looks at whole
+ * layers and lets a few stacks through whose half-cell interface nodes exceed that — such a wall marches to NaN in the
+ * reference ("Future temperatures is NaN" / NaN film coefficients) and, identically, here (HB_ERR_PHYSICS).  Generators
+ * of synthetic ensembles use this to re-draw them (heat_b200/cases.py). */
+hb_status hb_surface_rk4_number(const hb_handle* h, int64_t surface, double film, double* out);
+
 /* ---- state: reference slot order, models concatenated ----
  * per model: [zone T × n_zones] then per surface (surfaces, then fenestrations):
  * front h, back h, front conv. flow, back conv. flow, front solar irr., back solar irr., front IR irr.,

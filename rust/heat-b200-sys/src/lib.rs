@@ -171,6 +171,7 @@ extern "C" {
     pub fn hb_get_surface_arrays(h: *const hb_handle, surface: i64, n_elements: *mut i32, mass: *mut c_double,
                                  u: *mut c_double, front_alpha: *mut c_double, back_alpha: *mut c_double,
                                  massive_chunks: *mut i32, nomass_chunks: *mut i32) -> hb_status;
+    pub fn hb_surface_rk4_number(h: *const hb_handle, surface: i64, film: c_double, out: *mut c_double) -> hb_status;
     pub fn hb_set_state(h: *mut hb_handle, state: *const c_double) -> hb_status;
     pub fn hb_get_state(h: *mut hb_handle, state: *mut c_double) -> hb_status;
     pub fn hb_set_zone_inputs(h: *mut hb_handle, q_internal: *const c_double, infiltration_volume: *const c_double,

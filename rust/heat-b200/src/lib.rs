@@ -92,6 +92,12 @@ impl ThermalBatch {
         check(unsafe { sys::hb_get_surface_info(self.h, surface, &mut out) })?;
         Ok(out)
     }
+    /// dt·λmax of the wall's explicit march (bounded below 2.7853); see `hb_surface_rk4_number`.
+    pub fn surface_rk4_number(&self, surface: i64, film: f64) -> Result<f64, String> {
+        let mut out = 0.0f64;
+        check(unsafe { sys::hb_surface_rk4_number(self.h, surface, film, &mut out) })?;
+        Ok(out)
+    }
     pub fn get_state(&mut self, state: &mut [f64]) -> Result<(), String> {
         assert_eq!(state.len(), self.state_len());
         check(unsafe { sys::hb_get_state(self.h, state.as_mut_ptr()) })

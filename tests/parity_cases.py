@@ -686,6 +686,62 @@ def check_marches_again_after_failure(batch_cls):
     assert np.array_equal(b2.get_state(), s1)
 
 
+def check_unstable_wall_fails_like_reference(batch_cls, hours=36):
+    """A wall on which the reference's explicit RK4 is unstable at the sub-step its own rule picks (cases.unstable_wall:
+    dt·λmax = 2.807 > 2.7853) diverges and ends in the reference's panic — here in HB_ERR_PHYSICS with the same words,
+    not in silently wrong numbers; while it is still bounded (the first hours) the two agree."""
+    import oracle_py as O
+    from heat_b200 import HeatB200Error
+
+    d = cases.unstable_wall()
+    weather, inputs = cases.synthetic_weather(hours + 1)
+    om = O.OracleModel(d, 0)
+    arr = om.surface_arrays(0, 4)
+    number = cases.rk4_number_np(arr["mass"], arr["u"], arr["massive_chunks"], om.dt)
+    assert 2.80 < number < 2.81 and number > cases.RK4_STABILITY_LIMIT, number
+    so = om.initial_state()
+    om.march_series(so, 3, weather, weather_mode=1, inputs=inputs[:3], input_mode=1)
+    b = batch_cls(d)
+    b.march_series(3, weather, weather_mode=1, inputs=inputs[:3], input_mode=1)
+    assert np.abs(b.get_state() - so).max() <= 1e-6
+    with np.errstate(all="ignore"):
+        try:
+            om.march_series(so, hours - 3, weather[3:], weather_mode=1, inputs=inputs[3:hours], input_mode=1)
+            raise AssertionError("the oracle must panic on the unstable wall")
+        except O.OracleError as e:
+            assert "NaN" in str(e), e
+    try:
+        b.march_series(hours - 3, weather[3:], weather_mode=1, inputs=inputs[3:hours], input_mode=1)
+        failed = bool(getattr(b, "status", 0))   # the emulator reports through its status word
+    except HeatB200Error as e:
+        failed = e.status == 3 and "NaN" in str(e)
+    assert failed, "the unstable wall must be reported as a physics failure"
+
+
+def check_slow_nomass_convergence(batch_cls, hours=68):
+    """cases.slow_nomass_shoebox: a main step in which the reference's no-mass fixed point takes > 10^5 passes in one
+    solve.  The reference's only limit is 99 199 000 passes (surface.rs:869-873); the library must carry on like it —
+    same pass count, same temperatures — instead of reporting a failure of its own making."""
+    import oracle_py as O
+
+    d, gains = cases.slow_nomass_shoebox()
+    weather, inputs = cases.synthetic_weather(hours + 1)
+    om = O.OracleModel(d, 0)
+    om.set_zone_inputs(q_internal=gains)
+    so = om.initial_state()
+    om.march_series(so, hours - 3, weather, weather_mode=1, inputs=inputs[:hours - 3], input_mode=1)
+    before = om.nomass_iterations
+    om.march_series(so, 3, weather[hours - 3:], weather_mode=1, inputs=inputs[hours - 3:hours], input_mode=1)
+    assert om.nomass_iterations - before > 120_000, (before, om.nomass_iterations)   # hour 65 alone: ~1.4·10^5
+    b = batch_cls(d)
+    b.set_zone_inputs(q_internal=gains)
+    b.march_series(hours, weather, weather_mode=1, inputs=inputs[:hours], input_mode=1)
+    got = b.get_state()
+    assert np.all(np.isfinite(got)) and np.abs(got - so).max() <= 1e-6, np.abs(got - so).max()
+    its = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
+    assert its == om.nomass_iterations, (its, om.nomass_iterations)
+
+
 def check_scheduled_infiltration_ventilation(batch_cls, n=10, n_steps=8):
     """Infiltration / ventilation volume flow and temperature as per-main-step schedules (model.rs:524-544: the reference
     reads these state elements every sub-step and the caller rewrites them between march calls): one series call with

@@ -159,3 +159,11 @@ def test_emulated_tilted_glazing():
 
 def test_emulated_scheduled_infiltration_ventilation():
     pc.check_scheduled_infiltration_ventilation(emu_py.EmuBatch)
+
+
+def test_emulated_unstable_wall_fails_like_reference():
+    pc.check_unstable_wall_fails_like_reference(emu_py.EmuBatch)
+
+
+def test_emulated_slow_nomass_convergence():
+    pc.check_slow_nomass_convergence(emu_py.EmuBatch)

@@ -75,6 +75,48 @@ def test_random_wall_ensemble_zero_mismatches():
     assert b.updates_per_step == sum(b.model_info(m).nodes * b.model_info(m).dt_subdivisions for m in range(d.n_models))
 
 
+def test_rk4_number_matches_numpy_statement():
+    """hb_surface_rk4_number (Sturm bisection in hb_host.cc) against the dense-eigenvalue statement in cases.py, on walls
+    with massive chunks at the ends, between no-mass layers, and next to a gas cavity."""
+    descs = [cases.wall_ensemble(300, seed=321, mixed_fraction=0.4), cases.validation_case("trombe_wall_full"),
+             cases.validation_case("mixed_full"), cases.unstable_wall()]
+    checked = 0
+    for d in descs:
+        b = plan(d)
+        for g in range(b.n_surfaces):
+            a = b.surface_arrays(g)
+            dt = b.model_info(int(np.searchsorted(d.model_surface_offset, g, side="right")) - 1).dt
+            for film in (0.0, 30.0):
+                want = cases.rk4_number_np(a["mass"], a["u"], a["massive_chunks"], dt, film)
+                got = b.surface_rk4_number(g, film)
+                assert abs(got - want) <= 1e-6 * max(want, 1e-12), (g, film, got, want)
+            checked += 1
+    assert checked > 300
+    assert plan(cases.unstable_wall()).surface_rk4_number(0) > cases.RK4_STABILITY_LIMIT
+
+
+def test_wall_ensemble_redraws_unstable_walls():
+    """The generator's third re-draw test: a planner that reports wall 5 unstable once gets wall 5 re-drawn, the others
+    stay as drawn; the benchmark ensemble of one GPU (seed 42) has no such wall, so it is what round 1 measured."""
+    raw = cases._wall_ensemble_draw(40, 11, 0.0, 1, 4)
+    calls = []
+
+    def planner(desc):
+        calls.append(1)
+        rk4 = np.full(desc.n_models, 1.0)
+        if len(calls) == 1:
+            rk4[5] = 3.0
+        return np.full(desc.n_models, 20), np.ones(desc.n_models, np.int64), rk4
+
+    d = cases.wall_ensemble(40, seed=11, planner=planner)
+    assert len(calls) == 2
+    lo, hi = raw.construction_offset[5], raw.construction_offset[6]
+    same = raw.layers["thickness"] == d.layers["thickness"]
+    assert not same[lo:hi].any() and same[:lo].all() and same[hi:].all()
+    b = plan(cases.wall_ensemble(4000, seed=42))
+    assert max(b.surface_rk4_number(g) for g in range(4000)) < cases.RK4_STABILITY_LIMIT
+
+
 def test_shoebox_ensemble_zero_mismatches():
     d, _ = cases.shoebox_ensemble(60, seed=77, steps_per_hour=2)
     b = plan(d)

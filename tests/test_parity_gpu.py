@@ -278,6 +278,22 @@ def test_marches_again_after_reported_failure():
     pc.check_marches_again_after_failure(ThermalBatch)
 
 
+def test_unstable_wall_fails_like_reference():
+    """dt·λmax > 2.7853 under the reference's own sub-step: the reference panics with NaN, the library reports
+    HB_ERR_PHYSICS naming the surface (found by the 8-GPU configs[2] job: wall 347550 of the 800 000-wall draw)."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_unstable_wall_fails_like_reference(ThermalBatch)
+
+
+def test_slow_nomass_convergence_matches_oracle():
+    """More than 10^5 passes of the no-mass fixed point in one solve (found by the 8-GPU configs[3] job): not a failure
+    — the reference's limit is 99 199 000 passes."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_slow_nomass_convergence(ThermalBatch)
+
+
 def test_scheduled_infiltration_ventilation_match_oracle():
     """hb_series.zone_infiltration_* / zone_ventilation_*: per-main-step schedules (model.rs:524-544)."""
     from heat_b200.model import ThermalBatch
