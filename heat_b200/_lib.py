@@ -113,6 +113,24 @@ SYMBOLS = {
 _lib = None
 
 
+def _point_at_bundled_nccl() -> None:
+    """HEAT_B200_NCCL (read by hb_comm_*): the libnccl.so.2 of the `nvidia-nccl` wheel torch is built against, when there
+    is one — a process holds one NCCL, and if this library loaded the system's older copy first, a later `import torch`
+    would miss symbols.  Nothing is imported or loaded here; a value set by the user wins."""
+    if os.environ.get("HEAT_B200_NCCL"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for root in (spec.submodule_search_locations if spec else ()):
+            path = os.path.join(root, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                os.environ["HEAT_B200_NCCL"] = path
+                return
+    except (ImportError, ValueError, AttributeError):
+        pass
+
+
 def load() -> C.CDLL:
     """Load the CUDA library. Raises if it has not been built (`python -c 'import __graft_entry__ as g; g.build()'`)."""
     global _lib
@@ -120,6 +138,7 @@ def load() -> C.CDLL:
         if not os.path.exists(LIB_PATH):
             raise ImportError(
                 f"{LIB_PATH} is missing: build it with `make -C heat_b200/csrc` (there is no CPU fallback)")
+        _point_at_bundled_nccl()
         lib = C.CDLL(LIB_PATH)
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(lib, name)

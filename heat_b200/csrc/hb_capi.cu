@@ -73,7 +73,13 @@ struct Nccl {
     static Nccl& get() {
         static Nccl n = [] {
             Nccl x;
-            void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            // A process holds ONE libnccl.so.2 (the loader matches by soname): whoever loads it first decides which.
+            // HEAT_B200_NCCL names the copy to take when this library is first — heat_b200/_lib.py points it at the
+            // NCCL that ships with torch, so that a later `import torch` still finds the symbols it was built against.
+            void* lib = nullptr;
+            if (const char* path = std::getenv("HEAT_B200_NCCL"))
+                if (path[0]) lib = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+            if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
             if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
             if (!lib) throw CudaError(std::string("cannot load libnccl.so.2: ") + dlerror());
             auto sym = [&](const char* name) {

@@ -1043,6 +1043,18 @@ int emu_run(const hb_batch_desc* desc, int use_initial_state, double* state, con
     }
 }
 
+// tiles of the plan the library builds for `desc` (what hb_reduce_noalloc's HB_REDUCE_NOALLOC_MAX_TILES counts)
+long long emu_n_tiles(const hb_batch_desc* desc) {
+    try {
+        BatchPlan B;
+        plan_batch(desc, B);
+        return (long long)B.tiles.size();
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+
 long long emu_state_len(const hb_batch_desc* desc) {
     try {
         BatchPlan B;

@@ -26,6 +26,8 @@ def load():
         lib.emu_last_error.restype = C.c_char_p
         lib.emu_state_len.restype = C.c_longlong
         lib.emu_state_len.argtypes = [C.POINTER(_lib.BatchDescC)]
+        lib.emu_n_tiles.restype = C.c_longlong
+        lib.emu_n_tiles.argtypes = [C.POINTER(_lib.BatchDescC)]
         lib.emu_run.restype = C.c_int
         lib.emu_run.argtypes = [C.POINTER(_lib.BatchDescC), C.c_int] + [C.c_void_p] * 6 + [
             C.POINTER(_lib.SeriesC), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
@@ -60,6 +62,10 @@ class EmuBatch:
         self._zone_inputs = [None] * 5
         self.nomass_iterations = 0
         self.status = 0
+
+    @property
+    def n_tiles(self) -> int:
+        return int(self.lib.emu_n_tiles(C.byref(self._d)))
 
     def get_state(self):
         if self._state is None:
