@@ -100,6 +100,7 @@ SYMBOLS = {
     "hb_march_series_dev": (C.c_int32, [_P, C.POINTER(SeriesC), C.POINTER(C.c_float)]),
     "hb_launch_count": (C.c_int64, [_P]),
     "hb_reduce": (C.c_int32, [_P, C.POINTER(EnsembleStatsC)]),
+    "hb_reduce_noalloc": (C.c_int32, [_P, _P, _P]),
     "hb_reset_energy": (C.c_int32, [_P]),
     "hb_comm_unique_id": (C.c_int32, [_P]),
     "hb_comm_init": (C.c_int32, [_P, _P, C.c_int32, C.c_int32]),

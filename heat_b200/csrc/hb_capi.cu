@@ -6,6 +6,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <tuple>
@@ -13,6 +14,7 @@
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <math_constants.h>
 
 #include "hb_dev.hpp"
 
@@ -952,3 +954,171 @@ hb_status hb_flush_l2(hb_handle* h, int64_t bytes) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// hb_reduce_noalloc — the K3 reduction for callers that cannot allocate (CUDA graph capture, serving loops).
+// No counterpart in the reference (see include/heat_b200.h).
+//
+// Variant of hb_reduce_kernel (hb_kernels.cuh) without atomics and without the handle's accumulator buffers: stage 1
+// writes one 12-word partial per tile into a file-scope device array, stage 2 (one block) folds the partials in tile
+// order — the sums are the same from call to call.  The array lives in every GPU that loads the library, until exit.
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kNaWords = 12;                 // 8 doubles (sums / extrema / energies) + 4 integers per tile
+constexpr int kNaBlock = 128;                // threads of a stage-1 block: one block per tile (G·W <= 128 lanes)
+constexpr int kNaFoldBlock = 1024;
+static_assert(sizeof(hb_ensemble_stats) == kNaWords * 8, "hb_ensemble_stats is 8 doubles + 4 int64");
+
+// [HB_REDUCE_NOALLOC_MAX_TILES][12] partials, then the folded hb_ensemble_stats.  In HOST code this name is only a
+// stand-in for the symbol — never a device address: hb_reduce_noalloc asks cudaGetSymbolAddress once per device.
+static __device__ __align__(256) unsigned long long hb_na_scratch[((size_t)HB_REDUCE_NOALLOC_MAX_TILES + 1) * kNaWords];
+
+__global__ void __launch_bounds__(kNaBlock) hb_na_tile_kernel(hb::DevView V, int n_tiles, unsigned long long* scratch) {
+    __shared__ unsigned long long s_part[kNaBlock / 32][kNaWords];
+    const int ti = blockIdx.x, t = threadIdx.x;
+    if (ti >= n_tiles) return;
+    double sz = 0., mnz = CUDART_INF, mxz = -CUDART_INF, sn = 0., mnn = CUDART_INF, mxn = -CUDART_INF, ef = 0., eb = 0.;
+    unsigned long long nz = 0, nn = 0, it = 0, st = 0;
+    const hb::Tile tile = V.tiles[ti];
+    const int TPB = tile.G * tile.W;
+    for (int th = t; th < TPB; th += kNaBlock) {
+        const int wl = th / tile.G, part = th % tile.G;
+        const int n = V.n_nodes[(int64_t)tile.surface_begin + wl];
+        for (int i = 0; i < tile.NL; ++i) {
+            const int slot = part * tile.NL + i;
+            // block tiles: slots 1..n hold the nodes (0 and n+1 are ghosts); warp tiles: slots 0..n-1
+            if ((tile.flags & hb::TILE_WARP) ? slot < n : (slot >= 1 && slot <= n)) {
+                const double v = V.nodeT[tile.node_offset + (int64_t)i * TPB + th];
+                sn += v;
+                mnn = fmin(mnn, v);
+                mxn = fmax(mxn, v);
+                nn += 1;
+            }
+        }
+    }
+    if (t < tile.W) {
+        const int64_t g = (int64_t)tile.surface_begin + t;
+        if (V.n_nodes[g] > 0) {
+            ef += V.energy_f[g];
+            eb += V.energy_b[g];
+            it += V.nm_iters[g];
+            st |= (unsigned long long)V.status[g];
+        }
+        if (t < tile.n_zones) {
+            const double v = V.zoneT[(int64_t)tile.zone_begin + t];
+            sz += v;
+            mnz = fmin(mnz, v);
+            mxz = fmax(mxz, v);
+            nz += 1;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        sz += __shfl_down_sync(0xffffffffu, sz, o);
+        sn += __shfl_down_sync(0xffffffffu, sn, o);
+        ef += __shfl_down_sync(0xffffffffu, ef, o);
+        eb += __shfl_down_sync(0xffffffffu, eb, o);
+        mnz = fmin(mnz, __shfl_down_sync(0xffffffffu, mnz, o));
+        mxz = fmax(mxz, __shfl_down_sync(0xffffffffu, mxz, o));
+        mnn = fmin(mnn, __shfl_down_sync(0xffffffffu, mnn, o));
+        mxn = fmax(mxn, __shfl_down_sync(0xffffffffu, mxn, o));
+        nz += __shfl_down_sync(0xffffffffu, nz, o);
+        nn += __shfl_down_sync(0xffffffffu, nn, o);
+        it += __shfl_down_sync(0xffffffffu, it, o);
+        st |= __shfl_down_sync(0xffffffffu, st, o);
+    }
+    if ((t & 31) == 0) {
+        unsigned long long* p = s_part[t >> 5];
+        p[0] = __double_as_longlong(sz); p[1] = __double_as_longlong(mnz); p[2] = __double_as_longlong(mxz);
+        p[3] = __double_as_longlong(sn); p[4] = __double_as_longlong(mnn); p[5] = __double_as_longlong(mxn);
+        p[6] = __double_as_longlong(ef); p[7] = __double_as_longlong(eb);
+        p[8] = nz; p[9] = nn; p[10] = it; p[11] = st;
+    }
+    __syncthreads();
+    if (t == 0) {   // the block's warps in order: every word of the tile's partial is (re)written, nothing is accumulated
+        for (int w = 1; w < kNaBlock / 32; ++w) {
+            const unsigned long long* p = s_part[w];
+            sz += __longlong_as_double(p[0]); mnz = fmin(mnz, __longlong_as_double(p[1])); mxz = fmax(mxz, __longlong_as_double(p[2]));
+            sn += __longlong_as_double(p[3]); mnn = fmin(mnn, __longlong_as_double(p[4])); mxn = fmax(mxn, __longlong_as_double(p[5]));
+            ef += __longlong_as_double(p[6]); eb += __longlong_as_double(p[7]);
+            nz += p[8]; nn += p[9]; it += p[10]; st |= p[11];
+        }
+        unsigned long long* o = scratch + (size_t)ti * kNaWords;
+        o[0] = __double_as_longlong(sz); o[1] = __double_as_longlong(mnz); o[2] = __double_as_longlong(mxz);
+        o[3] = __double_as_longlong(sn); o[4] = __double_as_longlong(mnn); o[5] = __double_as_longlong(mxn);
+        o[6] = __double_as_longlong(ef); o[7] = __double_as_longlong(eb);
+        o[8] = nz; o[9] = nn; o[10] = it; o[11] = st;
+    }
+}
+
+// word k of the statistics: 0,3,6,7 sums; 1,4 minima; 2,5 maxima; 8-10 integer sums; 11 OR
+__device__ __forceinline__ unsigned long long na_fold(int k, unsigned long long a, unsigned long long b) {
+    if (k >= 8) return k == 11 ? (a | b) : a + b;
+    const double x = __longlong_as_double(a), y = __longlong_as_double(b);
+    return __double_as_longlong(k == 1 || k == 4 ? fmin(x, y) : k == 2 || k == 5 ? fmax(x, y) : x + y);
+}
+
+__global__ void __launch_bounds__(kNaFoldBlock) hb_na_fold_kernel(int n_tiles, unsigned long long* scratch,
+                                                                   hb_ensemble_stats* out_dev) {
+    __shared__ unsigned long long s_acc[kNaFoldBlock / 32][kNaWords];
+    const int t = threadIdx.x;
+    const unsigned long long inf = __double_as_longlong(CUDART_INF), ninf = __double_as_longlong(-CUDART_INF);
+    unsigned long long acc[kNaWords];
+#pragma unroll
+    for (int k = 0; k < kNaWords; ++k) acc[k] = k == 1 || k == 4 ? inf : k == 2 || k == 5 ? ninf : 0ull;   // 0.0 is all-zero bits
+    for (int ti = t; ti < n_tiles; ti += kNaFoldBlock) {
+#pragma unroll
+        for (int k = 0; k < kNaWords; ++k) acc[k] = na_fold(k, acc[k], scratch[(size_t)ti * kNaWords + k]);
+    }
+#pragma unroll
+    for (int k = 0; k < kNaWords; ++k)
+        for (int o = 16; o > 0; o >>= 1) acc[k] = na_fold(k, acc[k], __shfl_down_sync(0xffffffffu, acc[k], o));
+    if ((t & 31) == 0)
+        for (int k = 0; k < kNaWords; ++k) s_acc[t >> 5][k] = acc[k];
+    __syncthreads();
+    if (t < kNaWords) {
+        unsigned long long v = s_acc[0][t];
+        for (int w = 1; w < kNaFoldBlock / 32; ++w) v = na_fold(t, v, s_acc[w][t]);
+        scratch[(size_t)HB_REDUCE_NOALLOC_MAX_TILES * kNaWords + t] = v;
+        if (out_dev) reinterpret_cast<unsigned long long*>(out_dev)[t] = v;   // same 12-word layout as hb_ensemble_stats
+    }
+}
+
+// device address of hb_na_scratch, per device: resolved once, with that device current
+unsigned long long* na_scratch_of(int device) {
+    constexpr int kMaxDevices = 64;
+    static unsigned long long* ptr[kMaxDevices] = {};
+    static std::mutex mu;
+    if (device < 0 || device >= kMaxDevices) throw std::invalid_argument("hb_reduce_noalloc: device index beyond 63");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[device]) {
+        void* p = nullptr;
+        HB_CUDA(cudaGetSymbolAddress(&p, hb_na_scratch));   // the handle's device is current (need_device)
+        ptr[device] = static_cast<unsigned long long*>(p);
+    }
+    return ptr[device];
+}
+
+}  // namespace
+
+extern "C" hb_status hb_reduce_noalloc(hb_handle* h, hb_ensemble_stats* out_host, hb_ensemble_stats* out_dev) {
+    return guarded([&] {
+        need_device(h);
+        if (!out_host && !out_dev) throw std::invalid_argument("hb_reduce_noalloc: both outputs are NULL");
+        const int64_t n_tiles = (int64_t)h->plan.tiles.size();
+        if (n_tiles > HB_REDUCE_NOALLOC_MAX_TILES)
+            throw std::invalid_argument("hb_reduce_noalloc: the batch has " + std::to_string(n_tiles) +
+                                        " tiles, the static scratch holds HB_REDUCE_NOALLOC_MAX_TILES = " +
+                                        std::to_string(HB_REDUCE_NOALLOC_MAX_TILES) + "; use hb_reduce");
+        unsigned long long* scratch = na_scratch_of(h->device);
+        if (n_tiles > 0) hb_na_tile_kernel<<<(int)n_tiles, kNaBlock, 0, h->stream>>>(h->view(), (int)n_tiles, scratch);
+        hb_na_fold_kernel<<<1, kNaFoldBlock, 0, h->stream>>>((int)n_tiles, scratch, out_dev);
+        HB_CUDA(cudaGetLastError());
+        h->launches += n_tiles > 0 ? 2 : 1;
+        if (out_host) {
+            HB_CUDA(cudaMemcpyAsync(out_host, scratch + (size_t)HB_REDUCE_NOALLOC_MAX_TILES * kNaWords, sizeof(*out_host),
+                                    cudaMemcpyDeviceToHost, h->stream));
+            HB_CUDA(cudaStreamSynchronize(h->stream));
+        }
+    });
+}

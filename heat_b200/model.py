@@ -291,6 +291,14 @@ class ThermalBatch:
         _lib.check(self._lib.hb_reduce(self._h, C.byref(out)))
         return out
 
+    def reduce_noalloc(self, out_dev: int = 0, host: bool = True) -> Optional[_lib.EnsembleStatsC]:
+        """hb_reduce_noalloc: the same statistics without any allocation (static device scratch, at most
+        HB_REDUCE_NOALLOC_MAX_TILES tiles).  `out_dev`: device address of 96 bytes the kernel also writes (no
+        synchronize); `host=False`: device output only, returns None."""
+        out = _lib.EnsembleStatsC() if host else None
+        _lib.check(self._lib.hb_reduce_noalloc(self._h, C.byref(out) if host else None, C.c_void_p(out_dev or None)))
+        return out
+
     # ---- the ensemble statistics over all GPUs of a job: NCCL inside the library ----
     @staticmethod
     def comm_unique_id() -> bytes:

@@ -258,6 +258,23 @@ typedef struct {
 hb_status hb_reduce(hb_handle* h, hb_ensemble_stats* out);
 hb_status hb_reset_energy(hb_handle* h);
 
+/* hb_reduce for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same statistics as hb_reduce, from a variant of the K3 kernel whose scratch — one 96-byte partial per tile, folded in
+ * tile order by a second one-block kernel, so the sums do not depend on atomic order — is a file-scope device array of
+ * (HB_REDUCE_NOALLOC_MAX_TILES + 1) x 96 bytes = 1.5 MiB that every GPU loading the library holds until exit.  The call
+ * makes no cudaMalloc / cudaFree and uses no allocating library routine; the first call on a device also resolves the
+ * array's device address (cudaGetSymbolAddress) — make that one outside a capture.
+ *   out_host  host memory, filled after a stream synchronize; may be NULL
+ *   out_dev   DEVICE memory of the caller (sizeof(hb_ensemble_stats), 8-byte aligned), written by the kernel with no
+ *             synchronize — ordered after the handle's earlier work; may be NULL (not both)
+ * Limit: a batch of more than HB_REDUCE_NOALLOC_MAX_TILES tiles (about 2.3·10^5 walls of configs[2]) is rejected with
+ * HB_ERR_INVALID — use hb_reduce.  All calls, on all handles of a device, share the one array, which keeps the last
+ * call's partials (every word a call reads it has written first: nothing needs clearing): calls that overlap on the
+ * GPU — two handles, two host threads — race; serialise them. */
+#define HB_REDUCE_NOALLOC_MAX_TILES 16384
+hb_status hb_reduce_noalloc(hb_handle* h, hb_ensemble_stats* out_host, hb_ensemble_stats* out_dev);
+
 /* ---- the path's only collective: the ensemble statistics over all GPUs of a job ----
  * One process per GPU, one handle per process; walls and buildings never exchange anything while they march
  * (a building's surfaces couple only through its own zone, model.rs:556-590).  NCCL (libnccl.so.2, resolved at run

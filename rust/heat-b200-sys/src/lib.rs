@@ -12,6 +12,7 @@ pub const HB_ERR_CUDA: hb_status = 2;
 pub const HB_ERR_PHYSICS: hb_status = 3;
 pub const HB_ERR_UNSUPPORTED: hb_status = 4;
 pub const HB_DEVICE_NONE: i32 = -1;
+pub const HB_REDUCE_NOALLOC_MAX_TILES: usize = 16384;
 pub const HB_COMM_ID_BYTES: usize = 128;
 
 pub const HB_BOUNDARY_OUTDOOR: i32 = 0;
@@ -183,6 +184,7 @@ extern "C" {
     pub fn hb_march_series_dev(h: *mut hb_handle, series: *const hb_series, elapsed_ms: *mut c_float) -> hb_status;
     pub fn hb_launch_count(h: *const hb_handle) -> i64;
     pub fn hb_reduce(h: *mut hb_handle, out: *mut hb_ensemble_stats) -> hb_status;
+    pub fn hb_reduce_noalloc(h: *mut hb_handle, out_host: *mut hb_ensemble_stats, out_dev: *mut hb_ensemble_stats) -> hb_status;
     pub fn hb_reset_energy(h: *mut hb_handle) -> hb_status;
     // the path's only collective (NCCL inside the library)
     pub fn hb_comm_unique_id(id_out: *mut c_void) -> hb_status;
