@@ -1,5 +1,6 @@
 // hb_capi.cu — the C ABI declared in include/heat_b200.h: handle, device buffers, launches.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -151,6 +152,10 @@ struct hb_handle {
     };
     std::vector<std::unique_ptr<Group>> groups;
     cudaEvent_t fork = nullptr;
+    // "block has started" flags of the launches that take an SM per block (hb::wt_isolated): pinned host memory the
+    // kernels write and launch_series polls
+    static constexpr int kStartedSlots = 256;
+    volatile int32_t* started = nullptr;
     std::vector<int32_t> host_site;  // per device surface slot (rebuilt when model_site changes)
     std::vector<int32_t> model_site_cache;
     bool single_site = true;
@@ -164,6 +169,7 @@ struct hb_handle {
         if (comm) Nccl::get().CommDestroy(comm);
         groups.clear();   // joins and destroys the group streams / events
         if (fork) cudaEventDestroy(fork);
+        if (started) cudaFreeHost(const_cast<int32_t*>(started));
         if (stream) {
             cudaStreamSynchronize(stream);
             cudaStreamDestroy(stream);
@@ -261,6 +267,12 @@ void build_device(hb_handle* h) {
     int prio_lo = 0, prio_hi = 0;   // numerically lower = higher priority
     HB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     HB_CUDA(cudaEventCreateWithFlags(&h->fork, cudaEventDisableTiming));
+    {
+        void* p = nullptr;
+        HB_CUDA(cudaHostAlloc(&p, hb_handle::kStartedSlots * sizeof(int32_t), cudaHostAllocMapped | cudaHostAllocPortable));
+        std::memset(p, 0, hb_handle::kStartedSlots * sizeof(int32_t));
+        h->started = static_cast<volatile int32_t*>(p);
+    }
     for (auto& kv : by) {
         auto grp = std::make_unique<hb_handle::Group>();
         grp->NL = -std::get<2>(kv.first);
@@ -274,17 +286,28 @@ void build_device(hb_handle* h) {
         grp->ids.upload(kv.second, st);
         h->groups.push_back(std::move(grp));
     }
-    // launch order = longest chains first (the block scheduler serves kernels in launch order), on streams of
-    // decreasing priority
-    // (first of all the few no-mass-end tiles that ask for an SM of their own, hb_wtile_tier.cu: they need empty SMs)
-    auto rank = [](const hb_handle::Group& g) { return g.var == 9 && g.s_max >= 96 && g.n_tiles <= 64 ? 1 : 0; };
+    // Launch order and stream priority: first the few no-mass-end tiles that take an SM per block (they need empty SMs),
+    // then by class of chain length (longest first: they bound the series), and inside a class the kernels compiled
+    // for 255 registers before those for 168 — on streams of decreasing priority in the same order.  A sub-partition's
+    // register file holds 2 warps of 255 registers or 3 of 168, but only 1 + 1 of a mix (a sixth of its nodes fewer in
+    // flight): with the 255-register blocks ahead in every class, SMs fill with one kind and go over to the other
+    // only when its queue is empty, instead of mixing them at random (run-to-run spread of a series: 6 % -> see
+    // profiles/r2_summary.md).
+    auto mode_of = [](const hb_handle::Group& g) { return g.var == 10 ? 3 : g.var == 9 ? 1 : 0; };
+    auto rank = [&](const hb_handle::Group& g) { return g.var >= 8 && hb::wt_isolated(mode_of(g), g.s_max, g.n_tiles) ? 1 : 0; };
+    auto heavy = [](const hb_handle::Group& g) { return g.var >= 8 ? (g.NL > 12 || g.var != 8 ? 1 : 0) : 1; };
+    static const bool by_regs = !(std::getenv("HB_PRIO_BY_REGS") && std::getenv("HB_PRIO_BY_REGS")[0] == '0');
     std::stable_sort(h->groups.begin(), h->groups.end(),
                      [&](const std::unique_ptr<hb_handle::Group>& a, const std::unique_ptr<hb_handle::Group>& b) {
-                         return rank(*a) != rank(*b) ? rank(*a) > rank(*b) : a->s_max > b->s_max;
+                         if (rank(*a) != rank(*b)) return rank(*a) > rank(*b);
+                         if (by_regs && s_class(a->s_max) != s_class(b->s_max)) return s_class(a->s_max) < s_class(b->s_max);
+                         if (by_regs && heavy(*a) != heavy(*b)) return heavy(*a) > heavy(*b);
+                         return a->s_max > b->s_max;
                      });
     for (auto& grp : h->groups) {
         const int cls = s_class(grp->s_max);
-        HB_CUDA(cudaStreamCreateWithPriority(&grp->stream, cudaStreamNonBlocking, std::max(prio_hi, std::min(prio_lo, prio_hi + cls))));
+        const int level = by_regs ? (rank(*grp) ? 0 : 2 * cls + (heavy(*grp) ? 0 : 1)) : cls;
+        HB_CUDA(cudaStreamCreateWithPriority(&grp->stream, cudaStreamNonBlocking, std::max(prio_hi, std::min(prio_lo, prio_hi + level))));
         HB_CUDA(cudaEventCreateWithFlags(&grp->done, cudaEventDisableTiming));
     }
     HB_CUDA(cudaStreamSynchronize(st));
@@ -327,8 +350,40 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         HB_CUDA(cudaEventCreate(&tl0));
         HB_CUDA(cudaEventRecord(tl0, h->stream));
     }
+    // The groups that take an SM per block come first (create() sorts them so).  Blocks are not placed in launch order
+    // across hardware queues: if the bulk fills the SMs first, such a block waits until one DRAINS — measured: 40–110 ms
+    // of a 410 ms series for the last of four such groups.  So every one of their blocks reports when it begins (a flag
+    // in pinned host memory) and the bulk is launched once all have, or after 2 ms (the series goes on regardless).
+    int n_started = 0;
+    bool gate_open = false;
+    for (int i = 0; i < hb_handle::kStartedSlots; ++i) h->started[i] = 0;
+    auto wait_for_isolated = [&] {
+        gate_open = true;
+        if (n_started == 0 || group_times) return;
+        const auto t_begin = std::chrono::steady_clock::now(), t_end = t_begin + std::chrono::milliseconds(2);
+        int seen = 0;
+        do {
+            seen = 0;
+            for (int i = 0; i < n_started; ++i) seen += h->started[i] != 0;
+        } while (seen < n_started && std::chrono::steady_clock::now() < t_end);
+        if (timeline)
+            std::fprintf(stderr, "[hb tl] %d of %d SM-per-block blocks had begun after %.0f us\n", seen, n_started,
+                         std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count());
+    };
     for (auto& gp : h->groups) {
         hb_handle::Group& g = *gp;
+        hb::SeriesDev Pg = P;
+        {
+            const int mode = g.var == 10 ? 3 : g.var == 9 ? 1 : 0;
+            const int blocks = hb::wt_isolated_blocks(g.n_tiles);
+            if (!gate_open && g.var >= 8 && hb::wt_isolated(mode, g.s_max, g.n_tiles) &&
+                n_started + blocks <= hb_handle::kStartedSlots) {
+                HB_CUDA(cudaHostGetDevicePointer((void**)&Pg.started, const_cast<int32_t*>(h->started) + n_started, 0));
+                n_started += blocks;
+            } else if (!gate_open) {
+                wait_for_isolated();
+            }
+        }
         HB_CUDA(cudaStreamWaitEvent(g.stream, h->fork, 0));
         cudaEvent_t t0 = nullptr, t1 = nullptr;
         if (group_times) {
@@ -343,30 +398,49 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             HB_CUDA(cudaEventRecord(a, g.stream));
             tl.emplace_back(a, b);
         }
-        cudaError_t e;
+        cudaError_t e = cudaSuccess;
         // the lean face kernel (variant 0) reads one weather table per tile: per-site weather takes the general one
         const int var = (g.var == 0 || g.var == 3 || (g.var >= 5 && g.var < 8)) && !P.single_site ? 4 : g.var;
+        // A group's blocks march the whole series one after the other on the SM slots they get: a series is a list
+        // schedule of (tiles) jobs on (resident warps) slots, and its tail — slots idle while the last jobs end — is
+        // about half a job.  The groups of few sub-steps are the filler that runs last (lowest stream priority): their
+        // jobs are cut into segments of about kSegmentMs, launched back to back on the group's stream (the state goes
+        // through HBM in between: 40 B per node, nothing).  Long chains are never cut: a segment would wait for a slot.
+        int segments = 1;
+        if (var >= 8 && !Pg.started && g.s_max < 20 && P.record_every == 0 && P.ir_mode != HB_IR_NET_GAIN && !group_times) {
+            static const double seg_ms = std::getenv("HB_WT_SEGMENT_MS") ? std::atof(std::getenv("HB_WT_SEGMENT_MS")) : 20.;
+            const double job_ms = (double)P.n_steps * g.s_max * 3800. / 1.9e6;   // ~3800 cycles per sub-step when the SM is full
+            if (seg_ms > 0.) segments = (int)std::min(32., std::max(1., std::floor(job_ms / seg_ms)));
+        }
+        Pg.step_begin = 0;
+        Pg.step_end = P.n_steps;
+        for (int seg = 0; seg < segments && e == cudaSuccess; ++seg) {
+        if (segments > 1) {
+            Pg.step_begin = (int32_t)((int64_t)P.n_steps * seg / segments);
+            Pg.step_end = (int32_t)((int64_t)P.n_steps * (seg + 1) / segments);
+        }
         if (var >= 8) {   // warp tiles (per-site weather is handled inside the kernel)
             const int mode = var == 10 ? 3 : var == 9 ? 1 : 0;   // 3: buildings (one zone per model, panes, no-mass ends)
             switch (g.G) {
-                case 1: e = hb::launch_wtile_1(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-                case 2: e = hb::launch_wtile_2(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-                case 4: e = hb::launch_wtile_4(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-                case 8: e = hb::launch_wtile_8(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-                case 16: e = hb::launch_wtile_16(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-                default: e = hb::launch_wtile_32(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+                case 1: e = hb::launch_wtile_1(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+                case 2: e = hb::launch_wtile_2(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+                case 4: e = hb::launch_wtile_4(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+                case 8: e = hb::launch_wtile_8(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+                case 16: e = hb::launch_wtile_16(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+                default: e = hb::launch_wtile_32(mode, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
             }
         } else
         switch (g.G) {
-            case 1: e = hb::launch_march_1(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 2: e = hb::launch_march_2(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 4: e = hb::launch_march_4(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 8: e = hb::launch_march_8(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            case 16: e = hb::launch_march_16(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
-            default: e = hb::launch_march_32(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, P, g.ids.p); break;
+            case 1: e = hb::launch_march_1(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+            case 2: e = hb::launch_march_2(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+            case 4: e = hb::launch_march_4(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+            case 8: e = hb::launch_march_8(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+            case 16: e = hb::launch_march_16(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+            default: e = hb::launch_march_32(var, g.W, g.NL, g.n_tiles, g.s_max, g.stream, V, Pg, g.ids.p); break;
+        }
+        h->launches += 1;
         }
         HB_CUDA(e);
-        h->launches += 1;
         if (group_times) {
             HB_CUDA(cudaEventRecord(t1, g.stream));
             HB_CUDA(cudaEventSynchronize(t1));
@@ -393,6 +467,14 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
             cudaEventDestroy(tl[i].second);
         }
         cudaEventDestroy(tl0);
+        if (n_started > 0) {   // when each of those blocks began (~µs, GPU clock), relative to the first
+            int32_t lo = INT32_MAX;
+            for (int i = 0; i < n_started; ++i) if (h->started[i]) lo = std::min(lo, (int32_t)(h->started[i] & 0xfffff));
+            std::fprintf(stderr, "[hb tl] SM-per-block blocks: SM id @ begin (us):");
+            for (int i = 0; i < n_started; ++i)
+                std::fprintf(stderr, " %d@%d", (int)((h->started[i] >> 20) & 0x3ff), h->started[i] ? (int)((h->started[i] & 0xfffff) - lo) : -1);
+            std::fprintf(stderr, "\n");
+        }
     }
 }
 

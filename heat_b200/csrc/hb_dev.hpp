@@ -1,6 +1,7 @@
 // hb_dev.hpp — views of the packed SoA buffers (shared by the host packer, the launchers and the kernels).
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <vector>
 
 #include "hb_internal.hpp"
@@ -127,7 +128,34 @@ struct SeriesDev {
     const double* zone_inf_t;
     const double* zone_vent_v;
     const double* zone_vent_t;
+    // launches that take an SM per block (wt_isolated): block b sets started[b] = 1 when it begins — host-mapped memory
+    // the host polls before it launches the bulk, so that such a block never waits for an SM to drain.  nullptr otherwise.
+    volatile int32_t* started;
+    // hb_wtile_kernel marches the main steps [step_begin, step_end) of the series (a group of short tiles is launched
+    // as several such segments one after the other, launch_series); the other kernels always march [0, n_steps)
+    int32_t step_begin, step_end;
 };
+
+// Warps per block of hb_wtile_kernel: the warps of a block are spread over the SM's four sub-partitions (one register
+// file and one FP64 pipe each); every warp is an independent tile and never synchronises with the others.
+constexpr int kWtWarps = 4;
+// … and of its launches that take an SM per block (wt_isolated): two latency-bound warps per sub-partition
+// (HB_WT_ISO_WARPS, diagnostic: 4 or 8)
+constexpr int kWtWarpsMax = 8;
+inline int wt_isolated_warps() {
+    static const int w = std::getenv("HB_WT_ISO_WARPS") ? std::atoi(std::getenv("HB_WT_ISO_WARPS")) : kWtWarpsMax;
+    return w == 4 ? 4 : kWtWarpsMax;
+}
+// blocks of such a launch: pairs (clusters of two, the two SMs of a TPC — see the end of hb_wtile_kernel)
+inline int wt_isolated_blocks(int n_tiles) { return ((n_tiles + wt_isolated_warps() - 1) / wt_isolated_warps() + 1) & ~1; }
+
+// A handful of warp tiles with the longest chains of a series END it (S x n_steps sub-steps in sequence): their launch
+// asks for most of an SM's shared memory per block, so that such a block has its SM to itself instead of time-slicing the
+// FP64 pipes with the throughput-bound bulk (HB_WT_ISOLATE=0 switches it off).  mode: 0 all-massive (never isolated).
+inline bool wt_isolated(int mode, int s_max, int n_tiles) {
+    static const bool on = !(std::getenv("HB_WT_ISOLATE") && std::getenv("HB_WT_ISOLATE")[0] == '0');
+    return on && mode != 0 && s_max >= 96 && n_tiles <= 64;
+}
 
 enum { ST_NAN_H = 1, ST_NAN_ERR = 2, ST_NAN_ZONE = 4, ST_ITER_CAP = 8, ST_BAD_GAMMA = 16 };
 

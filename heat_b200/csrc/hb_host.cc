@@ -568,10 +568,11 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         static const std::vector<int> wt_nls_long = {8};
         // (when such walls are a few stragglers that END the series — configs[2]; where they are the bulk of the ensemble —
         // configs[4] — throughput decides and they take the cheapest geometry like everybody else)
+        static const int end_long_min_g = std::getenv("HB_END_MIN_G") ? std::atoi(std::getenv("HB_END_MIN_G")) : 8;
         const bool end_long = (M.variant & TILE_END) && M.dt_subdivisions >= kBulkSubsteps && n_end_long <= 4096;
         WtGeom wg{};
         if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) &&
-            wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : wt_nls, wg, (M.variant & TILE_END) ? 2 : 1)) {
+            wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : wt_nls, wg, (M.variant & TILE_END) ? (end_long ? end_long_min_g : 2) : 1)) {
             M.variant |= TILE_WARP;
             M.G = wg.G;
             M.NL = wg.NL;

@@ -128,22 +128,17 @@ struct WtLinks {
     double t_in;          // two-node no-mass end chunk: the chunk's inner node
 };
 
-// Warps per block: the warps of a block are spread over the SM's four sub-partitions (one register file and one FP64
-// pipe each); every warp is an independent tile and never synchronises with the others.
-constexpr int kWtWarps = 4;
 
+// One warp marches tile `tile_slot` of its launch group over the whole series.
 template <int G, int NL, int MODE, bool SIMPLE>
-__global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, MODE))
-    hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids, int n_tiles, int s_rows) {
+__device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev& P, const int32_t* tile_ids, int tile_slot,
+                                              int s_rows, double* s_dyn) {
     constexpr bool END = MODE != kFaceLean;   // no-mass chunks of one or two nodes at the ends of walls are possible
     constexpr bool PANE = MODE == kFacePane;  // … and single panes (two no-mass nodes, both faces solve one 2x2 system)
     constexpr int NF = G == 1 ? 2 : 1;        // faces evaluated by a face lane
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int W = 32 / G;
     static_assert(G >= 1 && G <= 32 && (G & (G - 1)) == 0 && NL >= 4, "geometry");
-    extern __shared__ double s_dyn[];
-    const int tile_slot = blockIdx.x * kWtWarps + (threadIdx.x >> 5);
-    if (tile_slot >= n_tiles) return;   // whole warp
     // [S] sub-step weather of the current main step, one table per warp
     SubWeather* const s_w = reinterpret_cast<SubWeather*>(s_dyn) + (size_t)(threadIdx.x >> 5) * s_rows;
 
@@ -417,6 +412,9 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
             const int fl = cf.fl;
             const double h = h_[f], rad = rad_[f], trad = trad_[f], asol = asol_[f];
             lk[f].t_in = 0.;
+            // (1/h does not wait for the no-mass solve below: started here, it overlaps with it)
+            const double hs = h > 1e-12 ? h : 1e-12;
+            const double inv_hs = rcp_lean(hs);
             if constexpr (END) {
                 if (fl & FC_NM2) {
                     double t_in = back ? t1_b : t1_f;
@@ -429,8 +427,7 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
                 }
             }
             // a no-mass end node takes no film link (v_end = 0): its temperature is placed, the ghost is never read
-            const double hs = h > 1e-12 ? h : 1e-12;
-            lk[f].ghost = wf.air + (rad * (trad - wf.ts) + asol) * rcp_lean(hs);
+            lk[f].ghost = wf.air + (rad * (trad - wf.ts) + asol) * inv_hs;
             lk[f].link = hs * cf.v_end;
         }
     };
@@ -438,8 +435,8 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
 #ifdef HB_PHASE_CLOCKS
     long long wclk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, wlast = clock64();
 #endif
-    int rec = 0;
-    for (int step = 0; step < P.n_steps; ++step) {
+    int rec = P.record_every > 0 ? P.step_begin / P.record_every : 0;
+    for (int step = P.step_begin; step < P.step_end; ++step) {
         fill_weather(step);
         main_step_inputs(step);
         // scheduled zone inputs: this main step's values, sources re-summed in the reference's order
@@ -583,6 +580,28 @@ __global__ void __launch_bounds__(32 * kWtWarps) __maxnreg__(wt_max_regs(G, NL, 
         }
     }
     if (szone) V.zoneT[sgz] = zT;
+}
+
+template <int G, int NL, int MODE, bool SIMPLE>
+__global__ void __launch_bounds__(32 * kWtWarpsMax) __maxnreg__(wt_max_regs(G, NL, MODE))
+    hb_wtile_kernel(DevView V, SeriesDev P, const int32_t* tile_ids, int n_tiles, int s_rows) {
+    extern __shared__ double s_dyn[];
+    if (P.started != nullptr && threadIdx.x == 0) {   // tell the host this block has its SM (launch_series waits for it)
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        // non-zero; SM id and a ~µs stamp for HB_GROUP_TIMELINE
+        P.started[blockIdx.x] = (int32_t)(((ns >> 10) & 0xfffffull) | ((unsigned long long)(smid & 0x3ff) << 20) | (1ull << 30));
+        __threadfence_system();
+    }
+    const int tile_slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (tile_slot < n_tiles) wt_march_tile<G, NL, MODE, SIMPLE>(V, P, tile_ids, tile_slot, s_rows, s_dyn);   // whole warp
+    // The launches that take an SM per block run as clusters of two blocks — the two SMs of one TPC (hb_wtile_tier.cu):
+    // a warp of such a block that shares its TPC with a bulk-loaded SM runs a third slower (measured: 3170 against 2370
+    // cycles per sub-step).  A block that is done (or the one that pads an odd grid) keeps its SM until its partner is
+    // done too.  Every other launch is a cluster of one: the barrier falls through.
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 }  // namespace hb

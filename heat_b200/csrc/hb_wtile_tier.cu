@@ -13,12 +13,9 @@ template <int G, int NL, int MODE, bool SIMPLE = true>
 cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
     size_t dyn = (size_t)kWtWarps * s_max * sizeof(SubWeather);   // <= 16 KB
     const int blocks = (n_tiles + kWtWarps - 1) / kWtWarps;
-    // A handful of tiles with the longest chains of the series END it (S x n_steps sub-steps in sequence): ask for most of an
-    // SM's shared memory per block, so that such a block has its SM to itself instead of time-slicing the FP64 pipes
-    // with the throughput-bound bulk (HB_WT_ISOLATE=0 switches it off).
-    static const bool isolate = !(std::getenv("HB_WT_ISOLATE") && std::getenv("HB_WT_ISOLATE")[0] == '0');
-    if (isolate && MODE != kFaceLean && s_max >= 96 && n_tiles <= 64) {
-        dyn = 225 * 1024;
+    if (wt_isolated(MODE, s_max, n_tiles)) {   // an SM per block (hb_dev.hpp)
+        static const int kb = std::getenv("HB_WT_ISOLATE_KB") ? std::atoi(std::getenv("HB_WT_ISOLATE_KB")) : 225;
+        dyn = (size_t)kb * 1024;
         static bool configured = false;   // per instantiation
         if (!configured) {
             cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
@@ -30,7 +27,25 @@ cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V,
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     cudaMemcpyToSymbol(hb_wt_clk, z, sizeof(z));
 #endif
-    hb_wtile_kernel<G, NL, MODE, SIMPLE><<<blocks, 32 * kWtWarps, dyn, st>>>(V, P, ids, n_tiles, s_max);
+    if (wt_isolated(MODE, s_max, n_tiles)) {
+        // pairs of blocks on the two SMs of a TPC (see the end of hb_wtile_kernel); an odd grid is padded by an empty block
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)wt_isolated_blocks(n_tiles));
+        cfg.blockDim = dim3(32 * wt_isolated_warps());
+        cfg.dynamicSmemBytes = dyn;
+        cfg.stream = st;
+        cudaLaunchAttribute attr{};
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = 2;
+        attr.val.clusterDim.y = 1;
+        attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, hb_wtile_kernel<G, NL, MODE, SIMPLE>, V, P, ids, n_tiles, s_max);
+        if (e != cudaSuccess) return e;
+    } else {
+        hb_wtile_kernel<G, NL, MODE, SIMPLE><<<blocks, 32 * kWtWarps, dyn, st>>>(V, P, ids, n_tiles, s_max);
+    }
 #ifdef HB_PHASE_CLOCKS
     cudaStreamSynchronize(st);
     cudaMemcpyFromSymbol(o, hb_wt_clk, sizeof(o));
