@@ -129,24 +129,30 @@ def shard_of(kind: str, units: int, rank: int, world: int, planner=None, plan_in
         return make_ensemble(kind, units, seed + (1000 * rank if kind == "mixed" else 0), planner)
     from heat_b200 import dist
     d, gains = make_ensemble(kind, units * world, seed, planner)
-    S, N = plan_info(d)
-    idx = dist.deal_models(S, N, rank, world)
+    S, N, K = plan_info(d)
+    idx = dist.deal_models(S, N, rank, world, kind=K)
     return d.select_models(idx), (None if gains is None else gains[idx])
 
 
 def gpu_plan_info(desc):
-    """(sub-steps, nodes) per model from the library's host planning (hb_create with HB_DEVICE_NONE)."""
+    """(sub-steps, nodes, kind) per model from the library's host planning (hb_create with HB_DEVICE_NONE); kind: 1 for a
+    one-wall model whose wall has no-mass chunks (it marches on other kernels than an all-massive wall), else 0."""
     import ctypes as C
     from heat_b200 import _lib
     from heat_b200.model import ThermalBatch
     plan = ThermalBatch(desc, device=-1)
     try:
-        mi = _lib.ModelInfoC()
+        mi, si = _lib.ModelInfoC(), _lib.SurfaceInfoC()
         S, N = np.zeros(desc.n_models, np.int64), np.zeros(desc.n_models, np.int64)
+        K = np.zeros(desc.n_models, np.int64)
+        one_wall = int(desc.model_surface_offset[-1]) == desc.n_models
         for m in range(desc.n_models):
             plan._lib.hb_get_model_info(plan._h, m, C.byref(mi))
             S[m], N[m] = mi.dt_subdivisions, mi.nodes
-        return S, N
+            if one_wall:
+                plan._lib.hb_get_surface_info(plan._h, m, C.byref(si))
+                K[m] = 1 if si.n_nomass_chunks > 0 else 0
+        return S, N, K
     finally:
         plan.close()
 

@@ -407,7 +407,8 @@ void launch_series(hb_handle* h, hb::SeriesDev P) {
         // jobs are cut into segments of about kSegmentMs, launched back to back on the group's stream (the state goes
         // through HBM in between: 40 B per node, nothing).  Long chains are never cut: a segment would wait for a slot.
         int segments = 1;
-        if (var >= 8 && !Pg.started && g.s_max < 20 && P.record_every == 0 && P.ir_mode != HB_IR_NET_GAIN && !group_times) {
+        static const int seg_smax = std::getenv("HB_WT_SEGMENT_SMAX") ? std::atoi(std::getenv("HB_WT_SEGMENT_SMAX")) : 20;
+        if (var >= 8 && !Pg.started && g.s_max < seg_smax && P.record_every == 0 && P.ir_mode != HB_IR_NET_GAIN && !group_times) {
             static const double seg_ms = std::getenv("HB_WT_SEGMENT_MS") ? std::atof(std::getenv("HB_WT_SEGMENT_MS")) : 20.;
             const double job_ms = (double)P.n_steps * g.s_max * 3800. / 1.9e6;   // ~3800 cycles per sub-step when the SM is full
             if (seg_ms > 0.) segments = (int)std::min(32., std::max(1., std::floor(job_ms / seg_ms)));

@@ -478,8 +478,8 @@ HB_HD_NOINLINE void solve_nomass(const WallC& c, WallS& w, const ExtWall& X, con
         double err = 0.0;
         for (int j = 0; j < m; ++j) err += fabs(rhs[j] - tl[j + 1]);
         if (err > old_err) break;                           // surface.rs:842-848
-        if (err != err) { w.status |= ST_NAN_ERR; break; }  // reference panics, :850
-        if (!(count < kNoMassIterCap)) { w.status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+        // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+        if (err != err || !(count < kNoMassIterCap)) { w.status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
         for (int j = 0; j < m; ++j) tl[j + 1] = (tl[j + 1] + rhs[j]) * 0.5;  // :878-883
         const double tol = count < 100 ? 0.01 : 0.5;       // :885
         if (err / (double)m < tol) break;
@@ -805,8 +805,8 @@ HB_HD double solve_end_node(double air, double h, double rad, double trad, doubl
             e *= rho;
             err = fabs(e);
             if (err > old_err) break;
-            if (err != err) { status |= ST_NAN_ERR; break; }
-            if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+            // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+            if (err != err || !(count < kNoMassIterCap)) { status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
             t = fma(0.5, e, t);
             const double tol = count < 100 ? 0.01 : 0.5;
             if (err < tol) break;
@@ -822,8 +822,8 @@ HB_HD double solve_end_node(double air, double h, double rad, double trad, doubl
         const double x = rhs * r;
         const double err = fabs(x - t);
         if (err > old_err) break;
-        if (err != err) { status |= ST_NAN_ERR; break; }
-        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+        // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+        if (err != err || !(count < kNoMassIterCap)) { status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
         t = (t + x) * 0.5;
         const double tol = count < 100 ? 0.01 : 0.5;
         if (err < tol) break;
@@ -877,8 +877,8 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
             const double x0 = fma(n01, x1, fma(n00, t0, c0));
             const double err = fabs(x0 - t0) + fabs(x1 - t1);
             if (err > old_err) break;
-            if (err != err) { status |= ST_NAN_ERR; break; }
-            if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+            // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+            if (err != err || !(count < kNoMassIterCap)) { status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
             t0 = (t0 + x0) * 0.5;
             t1 = (t1 + x1) * 0.5;
             const double tol = count < 100 ? 0.01 : 0.5;
@@ -899,8 +899,8 @@ HB_HD void solve_pane(double air_f, double h_f, double rad_f, double trad_f, dou
         const double x0 = LEAN ? (r0 - u * x1) * i0 : (r0 - u * x1) / dd0;
         const double err = fabs(x0 - t0) + fabs(x1 - t1);
         if (err > old_err) break;
-        if (err != err) { status |= ST_NAN_ERR; break; }
-        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+        // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+        if (err != err || !(count < kNoMassIterCap)) { status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
         t0 = (t0 + x0) * 0.5;
         t1 = (t1 + x1) * 0.5;
         const double tol = count < 100 ? 0.01 : 0.5;
@@ -950,8 +950,8 @@ HB_HD_NOINLINE void solve_window4(double air_f, double h_f, double rad_f, double
 #pragma unroll
         for (int j = 0; j < 4; ++j) err += fabs(rhs[j] - t[j]);
         if (err > old_err) break;                         // surface.rs:842-848
-        if (err != err) { status |= ST_NAN_ERR; break; }  // reference panics, :850
-        if (!(count < kNoMassIterCap)) { status |= ST_ITER_CAP; break; }   // surface.rs:869-873
+        // reference: panics on a NaN error (:850), then on the pass limit (surface.rs:869-873) — one cold branch here
+        if (err != err || !(count < kNoMassIterCap)) { status |= err != err ? ST_NAN_ERR : ST_ITER_CAP; break; }
 #pragma unroll
         for (int j = 0; j < 4; ++j) t[j] = (t[j] + rhs[j]) * 0.5;   // :878-883
         const double tol = count < 100 ? 0.01 : 0.5;     // :885

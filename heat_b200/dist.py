@@ -19,18 +19,23 @@ def shard_bounds(n_models: int, rank: int, world: int) -> Tuple[int, int]:
     return m0, m0 + base + (1 if rank < extra else 0)
 
 
-def deal_models(substeps, nodes, rank: int, world: int) -> np.ndarray:
+def deal_models(substeps, nodes, rank: int, world: int, kind=None) -> np.ndarray:
     """Indices of the models `rank` marches when ONE global ensemble is split over `world` GPUs.
 
     A rank's time is set as much by its longest dependent chains (sub-steps per main step x horizon, in sequence) as by
     its total work, so contiguous ranges of the sorted ensemble would hand every long chain to rank 0.  The models are
     sorted by (sub-steps, nodes), both descending, and dealt `world` at a time, the heaviest of each hand to the rank
     with the least work so far: every rank gets the same share of every part of the (S, N) distribution — equal tails
-    and equal sums of N·S (longest-processing-time rule, one hand at a time)."""
+    and equal sums of N·S (longest-processing-time rule, one hand at a time).
+
+    `kind` (optional, one small integer per model): what else decides which kernel a model goes to — e.g. 1 for walls
+    with a no-mass end.  It becomes the first sort key, so that every rank also gets the same number (± 1) of models of
+    every kind in every sub-step class, hence the same launch groups with the same numbers of tiles."""
     if not (0 <= rank < world):
         raise ValueError("rank out of range")
     substeps, nodes = np.asarray(substeps), np.asarray(nodes)
-    order = np.lexsort((-nodes, -substeps))
+    kind = np.zeros(substeps.shape, np.int64) if kind is None else np.asarray(kind)
+    order = np.lexsort((-nodes, -substeps, -kind))
     work = (substeps * nodes).astype(np.float64)[order]
     load = np.zeros(world)
     mine = []

@@ -10,8 +10,8 @@ from heat_b200.model import ThermalBatch
 
 rank, hours = int(sys.argv[1]), int(sys.argv[2])
 d, _ = bench.make_ensemble("walls", 800000, 42)
-S, N = bench.gpu_plan_info(d)
-sd = d.select_models(dist.deal_models(S, N, rank, 8))
+S, N, K = bench.gpu_plan_info(d)
+sd = d.select_models(dist.deal_models(S, N, rank, 8, kind=K))
 p = ThermalBatch(sd, device=-1)
 pick = []
 for m in range(sd.n_models):

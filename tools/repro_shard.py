@@ -10,8 +10,8 @@ from heat_b200.model import ThermalBatch
 
 rank, world, hours, chunk = (int(a) for a in sys.argv[1:5])
 d, _ = bench.make_ensemble("walls", 100_000 * world, 42)
-S, N = bench.gpu_plan_info(d)
-idx = dist.deal_models(S, N, rank, world)
+S, N, K = bench.gpu_plan_info(d)
+idx = dist.deal_models(S, N, rank, world, kind=K)
 sd = d.select_models(idx)
 weather, inputs = cases.synthetic_weather(hours + 1)
 inputs = np.ascontiguousarray(inputs[:hours])

@@ -18,21 +18,26 @@ for kind, hours in jobs:
     t0 = time.time()
     if kind != "mixed":
         d, gains = bench.make_ensemble(kind, units * world, bench.WORKLOADS[kind]["seed"])
-        S, N = bench.gpu_plan_info(d)
+        S, N, K = bench.gpu_plan_info(d)
         print(f"{kind}: global ensemble of {d.n_models} in {time.time() - t0:.1f} s", flush=True)
     for rank in (int(r) for r in os.environ.get("SWEEP_RANKS", ",".join(map(str, range(world)))).split(",")):
         if kind == "mixed":
             sd, sg = bench.make_ensemble(kind, units, bench.WORKLOADS[kind]["seed"] + 1000 * rank)
         else:
-            idx = dist.deal_models(S, N, rank, world)
+            idx = dist.deal_models(S, N, rank, world, kind=K)
             sd, sg = d.select_models(idx), (None if gains is None else gains[idx])
         b = ThermalBatch(sd)
         if sg is not None:
             b.set_zone_inputs(q_internal=sg)
         w, i = b.upload(weather), b.upload(inputs)
         try:
+            s0 = b.get_state()
+            allms = []
             for _ in range(int(os.environ.get("SWEEP_REPS", "1")) - 1):
-                b.march_series_dev(hours, w, hours + 1, 1, weather_mode=_lib.WEATHER_LINEAR, inputs_dev=i, input_mode=_lib.INPUT_SITE)
+                allms.append(b.march_series_dev(hours, w, hours + 1, 1, weather_mode=_lib.WEATHER_LINEAR, inputs_dev=i, input_mode=_lib.INPUT_SITE))
+                b.set_state(s0)
+            if allms:
+                print("   earlier reps:", " ".join(f"{x:.0f}" for x in allms), flush=True)
             ms = b.march_series_dev(hours, w, hours + 1, 1, weather_mode=_lib.WEATHER_LINEAR, inputs_dev=i, input_mode=_lib.INPUT_SITE)
             st = b.reduce()
             print(f"{kind} shard {rank}/{world}: ok, {ms:.1f} ms, {b.updates_per_step * hours / ms / 1e6:.1f} G updates/s, "
