@@ -192,9 +192,9 @@ __device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev&
     FaceS w[NF];
     double ir_state[NF];
     double zT = 0., za0 = 0., zb0 = 0., zvol = 1.;
-    ZoneC zc{};
     bool simple_ok = true;
     if (szone) {
+        ZoneC zc{};
         zc.vol = V.zvol[sgz]; zc.q = V.zq[sgz]; zc.inf_v = V.zinf_v[sgz]; zc.inf_t = V.zinf_t[sgz];
         zc.vent_v = V.zvent_v[sgz]; zc.vent_t = V.zvent_t[sgz]; zc.sb = V.z_surf_begin[sgz]; zc.se = V.z_surf_end[sgz];
         zT = V.zoneT[sgz];
@@ -440,7 +440,14 @@ __device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev&
         fill_weather(step);
         main_step_inputs(step);
         // scheduled zone inputs: this main step's values, sources re-summed in the reference's order
-        if (szone && load_zone_schedule(P, step, sgz, zc)) zone_sources(zc, za0, zb0);
+        // (the zone's constants are re-read here rather than kept in registers over the series: 14 registers)
+        if (szone && (P.zone_gain || P.zone_inf_v || P.zone_inf_t || P.zone_vent_v || P.zone_vent_t)) {
+            ZoneC zs;
+            zs.vol = V.zvol[sgz]; zs.q = V.zq[sgz]; zs.inf_v = V.zinf_v[sgz]; zs.inf_t = V.zinf_t[sgz];
+            zs.vent_v = V.zvent_v[sgz]; zs.vent_t = V.zvent_t[sgz]; zs.sb = 0; zs.se = 0;
+            load_zone_schedule(P, step, sgz, zs);
+            zone_sources(zs, za0, zb0);
+        }
         for (int s = 0; s < S; ++s) {
 #ifdef HB_PHASE_CLOCKS
             wlast = clock64();

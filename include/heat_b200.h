@@ -33,6 +33,10 @@
  *     length); chunks at the ends of walls: one or two nodes, single panes, pane | gas | pane windows on the fast path;
  *   - at most 128 sub-steps per main step (n >= 1 step per hour gives <= 120: min_dt = 60 s, model.rs:237,326-331);
  *   - walls of more than 1022 nodes; more than 254 nodes only for all-massive walls / walls with no-mass ends.
+ * Not limits: the no-mass fixed point gives up where the reference does (99 199 000 passes, surface.rs:869-873 —
+ * HB_ERR_PHYSICS "Excessive number of iterations"), and a wall on which the reference's explicit RK4 is unstable at the
+ * sub-step its discretization rule picks (see hb_surface_rk4_number) ends, as in the reference, in NaN → HB_ERR_PHYSICS.
+ * A physics failure names the surface (batch order), its model and the device slot.
  *
  * Conventions: plain pointers and sizes only; all `double*` are HOST pointers unless the name ends in
  * `_dev`; a handle is not re-entrant; no global state except the thread-local last-error string.
