@@ -20,6 +20,10 @@ cudaError_t launch_variant(int n_tiles, cudaStream_t st, const DevView& V, const
             configured = true;
         }
     }
+    if (!ids) {   // preload (hb_create): resolve the function now — its first launch would wait for whatever is running
+        cudaFuncAttributes a;
+        return cudaFuncGetAttributes(&a, hb_march_kernel<G, W, VAR>);
+    }
     hb_march_kernel<G, W, VAR><<<n_tiles, G * W, dyn, st>>>(V, P, ids);
     return cudaGetLastError();
 }
@@ -27,6 +31,10 @@ template <int G, int W, int END, bool SIMPLE, int NL = kNL>
 cudaError_t launch_face(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P,
                         const int32_t* ids) {
     const size_t dyn = (size_t)2 * s_max * sizeof(SubWeather);   // <= 8 KB: no opt-in needed
+    if (!ids) {   // preload (hb_create)
+        cudaFuncAttributes a;
+        return cudaFuncGetAttributes(&a, hb_face_kernel<G, W, END, SIMPLE, NL>);
+    }
 #ifdef HB_PHASE_CLOCKS
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     cudaMemcpyToSymbol(hb_phase_clk, z, sizeof(z));

@@ -23,6 +23,10 @@ cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V,
             configured = true;
         }
     }
+    if (!ids) {   // preload (hb_create): resolve the function now — its first launch would wait for whatever is running
+        cudaFuncAttributes a;
+        return cudaFuncGetAttributes(&a, hb_wtile_kernel<G, NL, MODE, SIMPLE>);
+    }
 #ifdef HB_PHASE_CLOCKS
     unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     cudaMemcpyToSymbol(hb_wt_clk, z, sizeof(z));
