@@ -22,7 +22,7 @@ constexpr int kMaxNodes = kMaxG * kNL - 2;  // 254: the largest wall of the regu
 constexpr int kNLBig = 16, kNLHuge = 32;
 constexpr int kMaxNodesBig = kMaxG * kNLHuge - 2;  // 1022
 constexpr int kMaxWalls = 32;        // walls (and zones) per tile; == warp size (scalar role)
-constexpr int kMaxNomassChunk = 8;   // longest no-mass chunk the kernels solve
+constexpr int kMaxNomassChunk = 32;  // longest no-mass chunk the kernels solve (tridiagonal elimination in local arrays)
 constexpr int kMaxSubsteps = 128;    // shared weather table rows (S <= 120 for n >= 1 step/hour)
 
 // Tile widths.  walls_of_group: the largest tile of a tier (256 node lanes) and the width of the shared-memory-mirror

@@ -29,8 +29,9 @@
  * message; nothing is silently approximated):
  *   - a model's surfaces and zones must fit one tile: 32 surfaces / 32 zones when its largest wall has <= 62 nodes,
  *     16 up to 126 nodes, 8 beyond (ThermalModel::new, model.rs:245-323, loops over any number);
- *   - a no-mass chunk INSIDE a wall (between massive layers) may have at most 8 nodes (surface.rs:790-898 solves any
- *     length); chunks at the ends of walls: one or two nodes, single panes, pane | gas | pane windows on the fast path;
+ *   - a no-mass chunk (consecutive no-mass nodes, anywhere in a wall) may have at most 32 nodes (surface.rs:790-898
+ *     solves any length); chunks of one or two nodes at the ends of walls, single panes and pane | gas | pane windows
+ *     are on the fast path, everything else on the general kernel;
  *   - at most 128 sub-steps per main step (n >= 1 step per hour gives <= 120: min_dt = 60 s, model.rs:237,326-331);
  *   - walls of more than 1022 nodes; more than 254 nodes only for all-massive walls / walls with no-mass ends.
  * Not limits: the no-mass fixed point gives up where the reference does (99 199 000 passes, surface.rs:869-873 —

@@ -372,6 +372,37 @@ def check_two_node_end_chunks(batch_cls, n_steps=48):
         assert iters == om.nomass_iterations, cons
 
 
+def check_long_nomass_chunks(batch_cls, n_steps=24):
+    """No-mass chunks of 9 … 31 nodes (surface.rs:790-898 solves any length): inside a wall between massive layers, at
+    an end, and a wall that is one long no-mass chunk — the general kernel's tridiagonal elimination."""
+    import oracle_py as O
+
+    thin = lambda k: [("polyurethane", 0.004 + 0.0005 * (i % 3)) for i in range(k)]
+    stacks = [[("concrete", 0.12)] + thin(10) + [("concrete", 0.1)],          # chunk of 9 inner nodes
+              thin(14) + [("concrete", 0.15)],                                  # 14-node chunk at the front
+              [("concrete", 0.15)] + thin(22),                                  # 22-node chunk at the back
+              thin(30)]                                                         # the whole wall: 31 no-mass nodes
+    weather, inputs = cases.synthetic_weather(n_steps + 1)
+    longest = 0
+    for cons in stacks:
+        d = cases.single_zone_test_building(cons, zone_volume=600.0, surface_height=3.0, surface_width=20.0,
+                                            emissivity=0.9, solar_absorbtance=0.7, steps_per_hour=4,
+                                            back_emissivity_override=0.0)
+        om = O.OracleModel(d, 0)
+        chunks = om.surface_arrays(0, len(cons))["nomass_chunks"]
+        longest = max(longest, int((chunks[:, 1] - chunks[:, 0]).max()))
+        b = batch_cls(d)
+        b.march_series(n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        got = b.get_state()
+        so = om.initial_state()
+        om.march_series(so, n_steps, weather, weather_mode=1, inputs=inputs[:n_steps], input_mode=1)
+        assert abs(got[0] - so[0]) <= 1e-6, cons
+        assert np.abs(got[9:] - so[9:]).max() <= 1e-6, (len(cons), np.abs(got[9:] - so[9:]).max())
+        iters = b.nomass_iterations if hasattr(b, "nomass_iterations") else b.reduce().nomass_iterations
+        assert iters == om.nomass_iterations, cons
+    assert longest >= 31, longest
+
+
 def _dense_layer(th, eps=0.9, alpha=0.7):
     """Low-diffusivity solid (k = 0.05, rho = 2500, cp = 2000): ~1200 nodes per metre under a 30 s sub-step."""
     return D.solid_layer(th, conductivity=0.05, density=2500.0, specific_heat=2000.0, front_emissivity=eps,

@@ -167,3 +167,7 @@ def test_emulated_unstable_wall_fails_like_reference():
 
 def test_emulated_slow_nomass_convergence():
     pc.check_slow_nomass_convergence(emu_py.EmuBatch)
+
+
+def test_emulated_long_nomass_chunks():
+    pc.check_long_nomass_chunks(emu_py.EmuBatch)

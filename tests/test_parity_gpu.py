@@ -278,6 +278,13 @@ def test_marches_again_after_reported_failure():
     pc.check_marches_again_after_failure(ThermalBatch)
 
 
+def test_long_nomass_chunks_match_oracle():
+    """No-mass chunks of up to 31 nodes (round 1 rejected more than 8; the reference has no limit)."""
+    from heat_b200.model import ThermalBatch
+
+    pc.check_long_nomass_chunks(ThermalBatch)
+
+
 def test_unstable_wall_fails_like_reference():
     """dt·λmax > 2.7853 under the reference's own sub-step: the reference panics with NaN, the library reports
     HB_ERR_PHYSICS naming the surface (found by the 8-GPU configs[2] job: wall 347550 of the 800 000-wall draw)."""
