@@ -506,7 +506,10 @@ def main():
             "roofline": roofline_of(main_run, True),
             "roofline_hbm": {"bound": "hbm", "achieved": main_run["alg_bytes"] / main_run["t_step"] / 1e9, "peak": hbm_peak,
                              "unit": "GB/s", "frac": main_run["alg_bytes"] / main_run["t_step"] / 1e9 / hbm_peak,
-                             "peak_source": hbm_src},
+                             "peak_source": hbm_src,
+                             "note": "algorithmic bytes = one pass over the state per series; the launch groups of the "
+                                     "shortest chains run as time segments and re-read their state per segment: "
+                                     "roofline.traffic is the measured total, still ~1e-4 of the HBM roofline"},
             "e2e": main_run["e2e"], "gpu_launches": main_run["gpu_launches"], "clocks": main_run["clocks"],
         }
         if secondary:
