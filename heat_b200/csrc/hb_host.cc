@@ -297,17 +297,48 @@ const std::vector<int>& wt_nodes_per_lane() {
     return nls;
 }
 
+// … and for all-massive walls (HB_WT_NLS_LEAN): with 24 / 32 the kernels keep the coefficients in shared memory
+const std::vector<int>& wt_nodes_per_lane_lean() {
+    static const std::vector<int> nls = [] {
+        std::vector<int> v;
+        if (const char* e = std::getenv("HB_WT_NLS_LEAN"))
+            for (const char* p = e; *p;) {
+                v.push_back(std::atoi(p));
+                while (*p && *p != ',') ++p;
+                if (*p == ',') ++p;
+            }
+        if (v.empty()) {
+            v = wt_nodes_per_lane();
+            if (!std::getenv("HB_WT_NLS")) v = {8, 12, 16, 24, 32};
+        }
+        std::sort(v.begin(), v.end());
+        return v;
+    }();
+    return nls;
+}
+
 // Warp tiles cost S sub-steps of a whole warp however many of their wall slots are filled.  Within a bucket of equal
 // kernel variant and sub-step count, the walls left over after the last FULL tile of a geometry move up to the next
 // larger geometry (a wall fits any geometry of at least its size) when they would fill at most 3/4 of a tile there:
 // 8.5 % fewer FP64 warp instructions on the 10^5-wall ensemble of BASELINE.json configs[2].
+void wt_merge_leftovers_on(BatchPlan& B, const std::vector<WtGeom>& geoms, bool lean);
 void wt_merge_leftovers(BatchPlan& B) {
-    std::vector<WtGeom> geoms;
-    for (int G = 1; G <= 32; G *= 2)
-        for (int NL : wt_nodes_per_lane())
-            if (G * NL <= kWtMaxNodes) geoms.push_back(WtGeom{G * NL, G, NL});
-    std::sort(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap != b.cap ? a.cap < b.cap : a.NL > b.NL; });
-    geoms.erase(std::unique(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap == b.cap; }), geoms.end());
+    auto geoms_of = [](const std::vector<int>& nls) {
+        std::vector<WtGeom> geoms;
+        for (int G = 1; G <= 32; G *= 2)
+            for (int NL : nls)
+                if (G * NL <= kWtMaxNodes && wt_geom_exists(G, NL)) geoms.push_back(WtGeom{G * NL, G, NL});
+        std::sort(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap != b.cap ? a.cap < b.cap : a.NL > b.NL; });
+        geoms.erase(std::unique(geoms.begin(), geoms.end(), [](const WtGeom& a, const WtGeom& b) { return a.cap == b.cap; }), geoms.end());
+        return geoms;
+    };
+    // two ladders: the all-massive buckets merge on theirs, those with no-mass ends on the common one
+    wt_merge_leftovers_on(B, geoms_of(wt_nodes_per_lane_lean()), true);
+    wt_merge_leftovers_on(B, geoms_of(wt_nodes_per_lane()), false);
+}
+
+// (one pass over the all-massive buckets (`lean`) or over those with no-mass ends, on the ladder `geoms`)
+void wt_merge_leftovers_on(BatchPlan& B, const std::vector<WtGeom>& geoms, bool lean) {
     auto index_of = [&](const ModelPlan& M) {
         for (size_t k = 0; k < geoms.size(); ++k)
             if (geoms[k].G == M.G && geoms[k].NL == M.NL) return (int)k;
@@ -317,6 +348,7 @@ void wt_merge_leftovers(BatchPlan& B) {
     for (size_t m = 0; m < B.models.size(); ++m) {
         const ModelPlan& M = B.models[m];
         if (!(M.variant & TILE_WARP) || !(M.variant & TILE_SIMPLE)) continue;   // buildings keep 32 / G >= n_surfaces
+        if (lean != !(M.variant & TILE_END)) continue;
         const int k = index_of(M);
         if (k < 0) continue;
         auto& v = buckets[{M.variant & kTileKey, M.dt_subdivisions}];
@@ -572,7 +604,7 @@ void plan_batch(const hb_batch_desc* d, BatchPlan& B, bool build_tiles) {
         const bool end_long = (M.variant & TILE_END) && M.dt_subdivisions >= kBulkSubsteps && n_end_long <= 4096;
         WtGeom wg{};
         if (!no_wtile && (M.variant == TILE_SIMPLE || M.variant == (TILE_END | TILE_SIMPLE)) &&
-            wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : wt_nls, wg, (M.variant & TILE_END) ? (end_long ? end_long_min_g : 2) : 1)) {
+            wt_geom_of_nodes(M.nmax, end_long ? wt_nls_long : (M.variant & TILE_END) ? wt_nls : wt_nodes_per_lane_lean(), wg, (M.variant & TILE_END) ? (end_long ? end_long_min_g : 2) : 1)) {
             M.variant |= TILE_WARP;
             M.G = wg.G;
             M.NL = wg.NL;

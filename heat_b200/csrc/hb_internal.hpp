@@ -64,12 +64,15 @@ struct WtGeom { int cap, G, NL; };
 constexpr int kWtMaxNodes = 512;
 // Smallest-capacity geometry (G lanes x NL nodes) that holds a wall of n nodes, NL taken from `nls` (ascending);
 // ties go to the larger NL (fewer lanes per wall: the face work is shared by more walls).
+// Geometries the kernels exist for: more than 16 nodes per lane (coefficients in shared memory, all-massive walls only)
+// with at most 4 lanes per wall, 32 nodes per lane with one lane per wall only (registers).
+inline bool wt_geom_exists(int G, int NL) { return NL <= 16 || (G <= 4 && (NL < 32 || G == 1)); }
 inline bool wt_geom_of_nodes(int n, const std::vector<int>& nls, WtGeom& out, int min_G = 1) {
     bool found = false;
     for (int G = min_G; G <= 32; G *= 2)
         for (int NL : nls) {
             const int cap = G * NL;
-            if (n > cap || cap > kWtMaxNodes) continue;
+            if (n > cap || cap > kWtMaxNodes || !wt_geom_exists(G, NL)) continue;
             if (!found || cap < out.cap || (cap == out.cap && NL > out.NL)) out = WtGeom{cap, G, NL};
             found = true;
         }

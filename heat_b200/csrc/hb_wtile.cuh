@@ -27,7 +27,20 @@ namespace hb {
 // that form at 168 registers whatever the block count asked for.)
 // Tiles with no-mass ends (MODE != lean) carry two fixed-point solvers and are, in the ensembles of BASELINE.json, the
 // walls with the most sub-steps — the longest dependent chains of a series: they get all the registers there are.
-__host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) { return NL <= 12 && MODE == kFaceLean ? 168 : 255; }
+#ifndef HB_WT_CSM16
+#define HB_WT_CSM16 1   // all-massive tiles of 16 nodes per lane: coefficients in shared memory, 168 registers
+#endif
+__host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) {
+    return (NL <= 12 || (HB_WT_CSM16 && NL == 16)) && MODE == kFaceLean ? 168 : 255;
+}
+// Geometries of more than 16 nodes per lane keep only T and the RK4 increment in registers: the coefficients A, B live
+// in shared memory ([slot][lane] pairs, one 16-byte load per node and sweep, conflict-free) — half the registers per
+// node, so a face evaluation is shared by twice the nodes.
+__host__ __device__ constexpr bool wt_coef_in_smem(int NL, int MODE) { return NL > 16 || (HB_WT_CSM16 && NL == 16 && MODE == kFaceLean); }
+// bytes of shared memory per warp: the sub-step weather table + (NL > 16) the coefficient pairs
+__host__ __device__ constexpr size_t wt_smem_per_warp(int NL, int MODE, int s_rows) {
+    return (size_t)s_rows * sizeof(SubWeather) + (wt_coef_in_smem(NL, MODE) ? (size_t)NL * 32 * sizeof(double2) : 0);
+}
 
 // T[k], k lane-dependent, as a select tree (registers cannot be indexed)
 template <int NL>
@@ -115,6 +128,71 @@ __device__ __forceinline__ void wt_rk4(double (&T)[NL], const double (&A)[NL], c
     }
 }
 
+// The same with the coefficients in shared memory: ab[i * 32] = (A[i], B[i]) of this lane.
+template <int G, int NL>
+__device__ __forceinline__ void wt_rk4_smem(double (&T)[NL], const double2* ab, bool first, double gf, bool edge, double gb) {
+    constexpr unsigned FULL = 0xffffffffu;
+    double X[NL];
+    double left = gf, right = gb;
+    if constexpr (G > 1) {
+        const double l = __shfl_up_sync(FULL, T[NL - 1], 1, G), r = __shfl_down_sync(FULL, T[0], 1, G);
+        left = first ? gf : l;
+        right = edge ? gb : r;
+    }
+    const double2 c0 = ab[0], cl = ab[(NL - 1) * 32];
+    {
+        const double d0 = T[1] - T[0], dl = T[0] - left;
+        const double dr = right - T[NL - 1], dm = T[NL - 1] - T[NL - 2];
+        X[0] = c0.x * d0 - c0.y * dl;
+        X[NL - 1] = cl.x * dr - cl.y * dm;
+        if constexpr (G > 1) {
+            const double l = __shfl_up_sync(FULL, X[NL - 1], 1, G), r = __shfl_down_sync(FULL, X[0], 1, G);
+            left = first ? 0. : l;
+            right = edge ? 0. : r;
+        } else {
+            left = 0.;
+            right = 0.;
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double2 c = ab[i * 32];
+            const double dnext = T[i + 1] - T[i];
+            X[i] = c.x * dnext - c.y * dprev;
+            dprev = dnext;
+        }
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] += X[i];
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double c = k == 0 ? 1. / 2. : k == 1 ? 1. / 6. : 1. / 24.;
+        const double d0 = X[1] - X[0], dl = X[0] - left;
+        const double dr = right - X[NL - 1], dm = X[NL - 1] - X[NL - 2];
+        const double x0 = c0.x * d0 - c0.y * dl;
+        const double xl = cl.x * dr - cl.y * dm;
+        if constexpr (G > 1) {
+            if (k < 2) {
+                const double l = __shfl_up_sync(FULL, xl, 1, G), r = __shfl_down_sync(FULL, x0, 1, G);
+                left = first ? 0. : l;
+                right = edge ? 0. : r;
+            }
+        }
+        double dprev = d0;
+#pragma unroll
+        for (int i = 1; i < NL - 1; ++i) {
+            const double2 cc = ab[i * 32];
+            const double dnext = (i + 1 == NL - 1 ? X[NL - 1] : X[i + 1]) - X[i];
+            X[i] = cc.x * dnext - cc.y * dprev;
+            dprev = dnext;
+        }
+        X[0] = x0;
+        X[NL - 1] = xl;
+#pragma unroll
+        for (int i = 0; i < NL; ++i) T[i] = fma(c, X[i], T[i]);
+    }
+}
+
 #ifdef HB_PHASE_CLOCKS
 __device__ unsigned long long hb_wt_clk[8];   // pre, place, rk4, gather, post, zone, -, sub-steps
 #define HB_WCLK(k) { const long long _t = clock64(); wclk[k] += _t - wlast; wlast = _t; }
@@ -158,14 +236,23 @@ __device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev&
     const int wflags = V.flags[sg];
     const bool nmf = END && ((wflags >> 10) & 1), nmb = END && ((wflags >> 11) & 1);
     const bool nmf2 = END && ((wflags >> 13) & 1), nmb2 = END && ((wflags >> 14) & 1);
-    double T[NL], A[NL], B[NL];
+    constexpr bool CSM = wt_coef_in_smem(NL, MODE);
+    constexpr int NC = CSM ? 1 : NL;   // coefficient registers (none when they live in shared memory)
+    double T[NL], A[NC], B[NC];
+    // this lane's column of the warp's coefficient pairs: ab[i * 32] = (A[i], B[i])
+    double2* const ab = reinterpret_cast<double2*>(reinterpret_cast<char*>(s_dyn) + (size_t)blockDim.x / 32 * s_rows * sizeof(SubWeather)) +
+                        (size_t)(threadIdx.x >> 5) * NL * 32 + lane;
     {
         const int64_t o = tile.node_offset + lane;
 #pragma unroll
         for (int i = 0; i < NL; ++i) {
             T[i] = V.nodeT[o + (int64_t)i * 32];
-            A[i] = V.coefA[o + (int64_t)i * 32];
-            B[i] = V.coefB[o + (int64_t)i * 32];
+            if constexpr (CSM) {
+                ab[i * 32] = make_double2(V.coefA[o + (int64_t)i * 32], V.coefB[o + (int64_t)i * 32]);
+            } else {
+                A[i] = V.coefA[o + (int64_t)i * 32];
+                B[i] = V.coefB[o + (int64_t)i * 32];
+            }
         }
     }
 
@@ -468,14 +555,19 @@ __device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev&
                     tb1 = __shfl_sync(FULL, tb1, base + G - 1);
                 }
             }
-            B[0] = first ? lf : B[0];
+            if constexpr (CSM) {
+                if (first) ab[0].y = lf;
+                if (last >= 0 && last < NL) ab[last * 32].x = lb;
+            } else {
+                B[0] = first ? lf : B[0];
+            }
             if constexpr (END) {
                 T[0] = (first && nmf) ? tf0 : T[0];
                 T[1] = (first && nmf2) ? tf1 : T[1];
             }
 #pragma unroll
             for (int i = 0; i < NL; ++i) {
-                A[i] = i == last ? lb : A[i];
+                if constexpr (!CSM) A[i] = i == last ? lb : A[i];
                 if constexpr (END) {
                     T[i] = (i == last && nmb) ? tb0 : T[i];
                     T[i] = (i == last - 1 && nmb2) ? tb1 : T[i];
@@ -484,7 +576,8 @@ __device__ __forceinline__ void wt_march_tile(const DevView& V, const SeriesDev&
             }
             HB_WCLK(1)
             // ================= node role: RK4 of the massive nodes =================
-            wt_rk4<G, NL>(T, A, B, first, gf, edge, gb);
+            if constexpr (CSM) wt_rk4_smem<G, NL>(T, ab, first, gf, edge, gb);
+            else wt_rk4<G, NL>(T, A, B, first, gf, edge, gb);
             HB_WCLK(2)
             // ================= node lanes → face lanes =================
             ts_f = T[0];

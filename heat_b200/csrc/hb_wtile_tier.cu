@@ -11,8 +11,16 @@ namespace hb {
 namespace {
 template <int G, int NL, int MODE, bool SIMPLE = true>
 cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
-    size_t dyn = (size_t)kWtWarps * s_max * sizeof(SubWeather);   // <= 16 KB
+    size_t dyn = (size_t)kWtWarps * wt_smem_per_warp(NL, MODE, s_max);   // <= 16 KB; NL > 16: + 0.5 KB per node slot and warp
     const int blocks = (n_tiles + kWtWarps - 1) / kWtWarps;
+    if (dyn > 48 * 1024 && !wt_isolated(MODE, s_max, n_tiles)) {
+        static size_t configured_for = 0;   // per instantiation
+        if (dyn > configured_for) {
+            cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (e != cudaSuccess) return e;
+            configured_for = dyn;
+        }
+    }
     if (wt_isolated(MODE, s_max, n_tiles)) {   // an SM per block (hb_dev.hpp)
         static const int kb = std::getenv("HB_WT_ISOLATE_KB") ? std::atoi(std::getenv("HB_WT_ISOLATE_KB")) : 225;
         dyn = (size_t)kb * 1024;
@@ -63,6 +71,11 @@ cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V,
 template <int G, int NL>
 cudaError_t launch_wt_mode(int mode, int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P,
                            const int32_t* ids) {
+    if constexpr (NL > 16) {   // (coefficients in shared memory) all-massive walls only, at most 4 lanes per wall
+        if constexpr (G <= 4)
+            if (mode == kFaceLean) return launch_wt<G, NL, kFaceLean>(n_tiles, s_max, st, V, P, ids);
+        return cudaErrorInvalidValue;
+    } else
     switch (mode) {
         case kFaceLean: return launch_wt<G, NL, kFaceLean>(n_tiles, s_max, st, V, P, ids);
         case kFaceLeanEnd: return launch_wt<G, NL, kFaceLeanEnd>(n_tiles, s_max, st, V, P, ids);
@@ -82,10 +95,8 @@ cudaError_t HB_CAT(launch_wtile_, HB_TIER)(int mode, int nl, int n_tiles, int s_
         case 10: return launch_wt_mode<G, 10>(mode, n_tiles, s_max, st, V, P, ids);
         case 12: return launch_wt_mode<G, 12>(mode, n_tiles, s_max, st, V, P, ids);
         case 16: return launch_wt_mode<G, 16>(mode, n_tiles, s_max, st, V, P, ids);
-#ifdef HB_WT_BIG_NL
-        case 20: return launch_wt_mode<G, 20>(mode, n_tiles, s_max, st, V, P, ids);
         case 24: return launch_wt_mode<G, 24>(mode, n_tiles, s_max, st, V, P, ids);
-#endif
+        case 32: return launch_wt_mode<G, 32>(mode, n_tiles, s_max, st, V, P, ids);
         default: return cudaErrorInvalidValue;
     }
 }

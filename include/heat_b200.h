@@ -273,7 +273,7 @@ hb_status hb_reset_energy(hb_handle* h);
  *   out_host  host memory, filled after a stream synchronize; may be NULL
  *   out_dev   DEVICE memory of the caller (sizeof(hb_ensemble_stats), 8-byte aligned), written by the kernel with no
  *             synchronize — ordered after the handle's earlier work; may be NULL (not both)
- * Limit: a batch of more than HB_REDUCE_NOALLOC_MAX_TILES tiles (about 2.3·10^5 walls of configs[2]) is rejected with
+ * Limit: a batch of more than HB_REDUCE_NOALLOC_MAX_TILES tiles (about 3.4·10^5 walls of configs[2]) is rejected with
  * HB_ERR_INVALID — use hb_reduce.  All calls, on all handles of a device, share the one array, which keeps the last
  * call's partials (every word a call reads it has written first: nothing needs clearing): calls that overlap on the
  * GPU — two handles, two host threads — race; serialise them. */

@@ -108,9 +108,9 @@ def test_reduce_noalloc_device_output_and_errors():
 def test_reduce_noalloc_rejects_batches_beyond_the_static_scratch():
     from heat_b200.model import ThermalBatch
 
-    b = ThermalBatch(cases.wall_ensemble(250_000, seed=3))   # 17 818 tiles > HB_REDUCE_NOALLOC_MAX_TILES
+    b = ThermalBatch(cases.wall_ensemble(400_000, seed=3))   # 19 045 tiles > HB_REDUCE_NOALLOC_MAX_TILES
     with pytest.raises(HeatB200Error, match="HB_REDUCE_NOALLOC_MAX_TILES = 16384") as e:
         b.reduce_noalloc()
     assert e.value.status == 1   # HB_ERR_INVALID
-    assert b.reduce().n_zones == 250_000   # the allocating entry point still serves it
+    assert b.reduce().n_zones == 400_000   # the allocating entry point still serves it
     b.close()
