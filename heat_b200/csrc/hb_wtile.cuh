@@ -30,13 +30,24 @@ namespace hb {
 #ifndef HB_WT_CSM16
 #define HB_WT_CSM16 1   // all-massive tiles of 16 nodes per lane: coefficients in shared memory, 168 registers
 #endif
+#ifndef HB_WT_CSM_ALL
+#define HB_WT_CSM_ALL 0   // experiment: every all-massive geometry with shared-memory coefficients, NL <= 12 at 128 registers
+#endif
+#ifndef HB_WT_CSM_END
+#define HB_WT_CSM_END 0   // experiment: walls with no-mass ends, 12 / 16 nodes per lane, with shared-memory coefficients (12: 168 registers)
+#endif
 __host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) {
+    if (HB_WT_CSM_ALL && MODE == kFaceLean && NL <= 12) return 128;
+    if (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8 && NL <= 12) return 168;
     return (NL <= 12 || (HB_WT_CSM16 && NL == 16)) && MODE == kFaceLean ? 168 : 255;
 }
 // Geometries of more than 16 nodes per lane keep only T and the RK4 increment in registers: the coefficients A, B live
 // in shared memory ([slot][lane] pairs, one 16-byte load per node and sweep, conflict-free) — half the registers per
 // node, so a face evaluation is shared by twice the nodes.
-__host__ __device__ constexpr bool wt_coef_in_smem(int NL, int MODE) { return NL > 16 || (HB_WT_CSM16 && NL == 16 && MODE == kFaceLean); }
+__host__ __device__ constexpr bool wt_coef_in_smem(int NL, int MODE) {
+    return NL > 16 || (HB_WT_CSM16 && NL == 16 && MODE == kFaceLean) || (HB_WT_CSM_ALL && MODE == kFaceLean) ||
+           (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8);
+}
 // bytes of shared memory per warp: the sub-step weather table + (NL > 16) the coefficient pairs
 __host__ __device__ constexpr size_t wt_smem_per_warp(int NL, int MODE, int s_rows) {
     return (size_t)s_rows * sizeof(SubWeather) + (wt_coef_in_smem(NL, MODE) ? (size_t)NL * 32 * sizeof(double2) : 0);

@@ -87,6 +87,23 @@ def test_deal_models_balances_tails_and_work():
         assert max(tails) - min(tails) <= 1
 
 
+def test_deal_models_by_kind():
+    """`kind` (e.g. walls with no-mass ends: other kernels) is the first sort key: every rank gets the same number (± 1)
+    of models of every kind in every sub-step class, and the partition / work balance hold as without it."""
+    rng = np.random.default_rng(4)
+    S = rng.choice([18, 54, 118], size=8_000, p=[.8, .15, .05])
+    N = rng.integers(2, 128, size=8_000)
+    K = (rng.random(8_000) < 0.02).astype(np.int64)
+    for world in (2, 8):
+        parts = [D.deal_models(S, N, r, world, kind=K) for r in range(world)]
+        assert np.array_equal(np.sort(np.concatenate(parts)), np.arange(S.size))
+        for s in (18, 54, 118):
+            counts = [int(((S[p] == s) & (K[p] == 1)).sum()) for p in parts]
+            assert max(counts) - min(counts) <= 1, (world, s, counts)
+        work = np.array([(S[p] * N[p]).sum() for p in parts], float)
+        assert work.max() / work.min() < 1.02
+
+
 def test_two_rank_gloo_equals_single_process():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
