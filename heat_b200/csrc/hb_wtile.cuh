@@ -33,8 +33,11 @@ namespace hb {
 #ifndef HB_WT_CSM_ALL
 #define HB_WT_CSM_ALL 0   // experiment: every all-massive geometry with shared-memory coefficients, NL <= 12 at 128 registers
 #endif
+#ifndef HB_WT_CSM_PANE
+#define HB_WT_CSM_PANE 1  // buildings, 12 / 16 nodes per lane: shared-memory coefficients (255 registers, no spills: +10 % on configs[3])
+#endif
 #ifndef HB_WT_CSM_END
-#define HB_WT_CSM_END 0   // experiment: walls with no-mass ends, 12 / 16 nodes per lane, with shared-memory coefficients (12: 168 registers)
+#define HB_WT_CSM_END 1   // walls with no-mass ends, 12 / 16 nodes per lane: shared-memory coefficients, 12 at 168 registers (+20 % on configs[4])
 #endif
 __host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) {
     if (HB_WT_CSM_ALL && MODE == kFaceLean && NL <= 12) return 128;
@@ -46,7 +49,7 @@ __host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) {
 // node, so a face evaluation is shared by twice the nodes.
 __host__ __device__ constexpr bool wt_coef_in_smem(int NL, int MODE) {
     return NL > 16 || (HB_WT_CSM16 && NL == 16 && MODE == kFaceLean) || (HB_WT_CSM_ALL && MODE == kFaceLean) ||
-           (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8);
+           (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8) || (HB_WT_CSM_PANE && MODE == kFacePane && NL > 8);
 }
 // bytes of shared memory per warp: the sub-step weather table + (NL > 16) the coefficient pairs
 __host__ __device__ constexpr size_t wt_smem_per_warp(int NL, int MODE, int s_rows) {
