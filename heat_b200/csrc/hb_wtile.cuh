@@ -33,6 +33,12 @@ namespace hb {
 #ifndef HB_WT_CSM_ALL
 #define HB_WT_CSM_ALL 0   // experiment: every all-massive geometry with shared-memory coefficients, NL <= 12 at 128 registers
 #endif
+#ifndef HB_WT_END16_168
+#define HB_WT_END16_168 1   // no-mass-end tiles of 16 nodes per lane at 168 registers too (590 bytes of spills, 3 warps: +3 % on configs[4])
+#endif
+#ifndef HB_WT_PANE_168
+#define HB_WT_PANE_168 1    // building tiles of 12 nodes per lane (G >= 2) at 168 registers (310-370 bytes of spills, 3 warps: +4 % on configs[3])
+#endif
 #ifndef HB_WT_CSM_PANE
 #define HB_WT_CSM_PANE 1  // buildings, 12 / 16 nodes per lane: shared-memory coefficients (255 registers, no spills: +10 % on configs[3])
 #endif
@@ -41,7 +47,8 @@ namespace hb {
 #endif
 __host__ __device__ constexpr int wt_max_regs(int G, int NL, int MODE) {
     if (HB_WT_CSM_ALL && MODE == kFaceLean && NL <= 12) return 128;
-    if (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8 && NL <= 12) return 168;
+    if (HB_WT_CSM_END && MODE == kFaceLeanEnd && NL > 8 && NL <= (HB_WT_END16_168 ? 16 : 12)) return 168;
+    if (HB_WT_CSM_PANE && HB_WT_PANE_168 && MODE == kFacePane && NL > 8 && NL <= 12 && G >= 2) return 168;
     return (NL <= 12 || (HB_WT_CSM16 && NL == 16)) && MODE == kFaceLean ? 168 : 255;
 }
 // Geometries of more than 16 nodes per lane keep only T and the RK4 increment in registers: the coefficients A, B live
