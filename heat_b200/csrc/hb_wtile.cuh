@@ -5,8 +5,10 @@
 // of a tile: three of a tile's four warps wait at the block barrier while one warp runs post → zone → pre
 // (profiles/r1j_summary.md: 2.9 warps stalled on the barrier per issued instruction, FP64 pipe 34 % busy), and the
 // register file admits only four such tiles per SM.  Here every warp is its own tile:
-//   * a wall is owned by G consecutive lanes (G = 1 … 32), each lane keeping NL (8, 12 or 16) NODES in registers —
-//     no ghost slots: the film links enter through the halo values of the first / last node (capacity n <= G·NL);
+//   * a wall is owned by G consecutive lanes (G = 1 … 32), each lane keeping the temperatures of NL (8 … 32) NODES in
+//     registers — no ghost slots: the film links enter through the halo values of the first / last node (capacity
+//     n <= G·NL); the tridiagonal coefficients sit beside them in registers (NL = 8; all-massive walls: NL <= 12) or
+//     in shared memory (wt_coef_in_smem: half the registers per node);
 //   * the FRONT face of a wall is evaluated by the first lane of its group, the BACK face (and, for a wall with its own
 //     zone, the zone) by the last lane (G = 1: both by the one lane) — the face results reach the node lanes through
 //     two warp shuffles, the end-node temperatures come back through a register mux + one shuffle;
