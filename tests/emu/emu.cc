@@ -1055,6 +1055,22 @@ long long emu_n_tiles(const hb_batch_desc* desc) {
     }
 }
 
+// (G, NL, W, flags, S) of up to `cap` tiles of that plan; returns the number of tiles
+long long emu_tile_table(const hb_batch_desc* desc, int* out, long long cap) {
+    try {
+        BatchPlan B;
+        plan_batch(desc, B);
+        for (size_t i = 0; i < B.tiles.size() && (long long)i < cap; ++i) {
+            const Tile& t = B.tiles[i];
+            out[5 * i + 0] = t.G; out[5 * i + 1] = t.NL; out[5 * i + 2] = t.W; out[5 * i + 3] = t.flags; out[5 * i + 4] = t.S;
+        }
+        return (long long)B.tiles.size();
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+
 long long emu_state_len(const hb_batch_desc* desc) {
     try {
         BatchPlan B;

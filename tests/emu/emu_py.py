@@ -28,6 +28,8 @@ def load():
         lib.emu_state_len.argtypes = [C.POINTER(_lib.BatchDescC)]
         lib.emu_n_tiles.restype = C.c_longlong
         lib.emu_n_tiles.argtypes = [C.POINTER(_lib.BatchDescC)]
+        lib.emu_tile_table.restype = C.c_longlong
+        lib.emu_tile_table.argtypes = [C.POINTER(_lib.BatchDescC), C.c_void_p, C.c_longlong]
         lib.emu_run.restype = C.c_int
         lib.emu_run.argtypes = [C.POINTER(_lib.BatchDescC), C.c_int] + [C.c_void_p] * 6 + [
             C.POINTER(_lib.SeriesC), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
@@ -66,6 +68,14 @@ class EmuBatch:
     @property
     def n_tiles(self) -> int:
         return int(self.lib.emu_n_tiles(C.byref(self._d)))
+
+    def tile_table(self) -> np.ndarray:
+        """[n_tiles][5] = (G, NL, W, flags, S) of the plan the library builds for this batch."""
+        n = self.n_tiles
+        out = np.zeros((max(n, 1), 5), np.int32)
+        got = self.lib.emu_tile_table(C.byref(self._d), out.ctypes.data, n)
+        assert got == n
+        return out[:n]
 
     def get_state(self):
         if self._state is None:

@@ -223,3 +223,34 @@ def test_read_epw_reference_file_matches_fixture():
     assert weather.shape == (8761, 3)
     assert np.array_equal(weather[:8760], h[:, [0, 3, 4]])
     assert np.array_equal(inputs[:, 0], h[:, 2]) and np.array_equal(inputs[:, 2], h[:, 1])
+
+
+def test_every_planned_warp_tile_has_a_kernel():
+    """The geometries the planner hands out against the instantiations of heat_b200/csrc/hb_wtile_tier.cu (a miss is a
+    launch error that only a GPU run would show): all-massive walls NL in {8, 12, 16, 24, 32} (24: G <= 4, 32: G = 1),
+    walls with no-mass ends and buildings NL in {8, 12, 16}, buildings G <= 8; G·W = 32 always."""
+    import re
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu"))
+    import emu_py
+
+    src = open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "heat_b200", "csrc", "hb_wtile_tier.cu")).read()
+    compiled = {int(m) for m in re.findall(r"case (\d+): return launch_wt_mode<G, \d+>", src)}
+    TILE_END, TILE_SIMPLE, TILE_WARP = 8, 64, 128
+    batches = [cases.wall_ensemble(6000, seed=42), cases.wall_ensemble(6000, seed=44, mixed_fraction=0.5),
+               cases.wall_ensemble(300, seed=5, mixed_fraction=0.5, max_nodes=500),
+               cases.shoebox_ensemble(400, seed=43)[0], cases.shoebox_ensemble(50, seed=43, glazing=cases.double_glazing())[0]]
+    seen = set()
+    for d in batches:
+        for G, NL, W, flags, S in emu_py.EmuBatch(d).tile_table():
+            if not flags & TILE_WARP:
+                continue
+            assert G * W == 32 and NL in compiled, (G, NL, W)
+            lean = (flags & TILE_SIMPLE) and not (flags & TILE_END)
+            if NL > 16:
+                assert lean and G <= 4 and (NL < 32 or G == 1), (G, NL, flags)
+            if not flags & TILE_SIMPLE:
+                assert G <= 8, (G, NL, flags)
+            seen.add((int(G), int(NL), bool(lean)))
+    assert {nl for _, nl, lean in seen if lean} >= {8, 12, 16, 24, 32}
+    assert {nl for _, nl, lean in seen if not lean} >= {8, 12, 16}
