@@ -13,22 +13,19 @@ template <int G, int NL, int MODE, bool SIMPLE = true>
 cudaError_t launch_wt(int n_tiles, int s_max, cudaStream_t st, const DevView& V, const SeriesDev& P, const int32_t* ids) {
     size_t dyn = (size_t)kWtWarps * wt_smem_per_warp(NL, MODE, s_max);   // <= 16 KB; NL > 16: + 0.5 KB per node slot and warp
     const int blocks = (n_tiles + kWtWarps - 1) / kWtWarps;
-    if (dyn > 48 * 1024 && !wt_isolated(MODE, s_max, n_tiles)) {
-        static size_t configured_for = 0;   // per instantiation
-        if (dyn > configured_for) {
-            cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-            if (e != cudaSuccess) return e;
-            configured_for = dyn;
-        }
-    }
     if (wt_isolated(MODE, s_max, n_tiles)) {   // an SM per block (hb_dev.hpp)
         static const int kb = std::getenv("HB_WT_ISOLATE_KB") ? std::atoi(std::getenv("HB_WT_ISOLATE_KB")) : 225;
         dyn = (size_t)kb * 1024;
-        static bool configured = false;   // per instantiation
-        if (!configured) {
-            cudaError_t e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    }
+    if (dyn > 48 * 1024) {   // opt in to more than 48 KB of dynamic shared memory: per instantiation AND per device, growing only
+        static size_t configured_for[64] = {};
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 0 || dev >= 64 || dyn > configured_for[dev]) {
+            e = cudaFuncSetAttribute(hb_wtile_kernel<G, NL, MODE, SIMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
-            configured = true;
+            if (dev >= 0 && dev < 64) configured_for[dev] = dyn;
         }
     }
     if (!ids) {   // preload (hb_create): resolve the function now — its first launch would wait for whatever is running
