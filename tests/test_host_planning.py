@@ -152,6 +152,22 @@ def test_errors_mirror_reference():
     assert "Space not found" in str(e.value)
 
 
+def test_planning_queries_reject_bad_arguments():
+    """hb_surface_rk4_number / hb_get_surface_info: index and argument errors are HB_ERR_INVALID with a message, and a
+    chunk beyond the 32-node limit of the no-mass solver is refused at hb_create, not mis-solved."""
+    from heat_b200 import HeatB200Error
+
+    b = plan(cases.validation_case("massive_full"))
+    assert b.surface_rk4_number(0) > 0.0
+    for call in (lambda: b.surface_rk4_number(5), lambda: b.surface_rk4_number(0, film=-1.0), lambda: b.surface_info(-1)):
+        with pytest.raises(HeatB200Error) as e:
+            call()
+        assert e.value.status == 1 and str(e.value)
+    thin = [("polyurethane", 0.004)] * 40   # one no-mass chunk of 41 nodes
+    with pytest.raises(HeatB200Error, match="no-mass chunk longer"):
+        plan(cases.single_zone_test_building(thin, steps_per_hour=4))
+
+
 def test_no_cpu_fallback():
     """A planning handle cannot march; there is no CPU path behind the C ABI."""
     from heat_b200 import HeatB200Error
